@@ -1,0 +1,171 @@
+"""Drives the UNMODIFIED reference (imported from /root/reference) -- TEST INFRASTRUCTURE ONLY.
+
+Used in the build container to (a) validate ``oracle/dreamer_oracle.py`` and (b) generate the golden
+fixtures under ``tests/golden/`` (``oracle/make_golden.py``).  ``/root/reference`` does not exist on
+the GPU box; nothing that runs there imports this module.
+
+Noise injection follows SURVEY.md section 8(c): ``torch.distributions.normal._standard_normal`` is
+patched to pop pre-generated tensors in the reference's own draw order; the categorical samplers
+are patched to the Gumbel-max formulation on injected Gumbel noise.
+"""
+from __future__ import annotations
+
+import contextlib
+import os
+import sys
+import types
+
+import torch
+
+REF_ROOT = os.environ.get("DREAMER_REFERENCE_ROOT", "/root/reference")
+
+
+def reference_available() -> bool:
+    return os.path.isdir(os.path.join(REF_ROOT, "dreamer")) and os.path.isdir(os.path.join(REF_ROOT, "rlpyt"))
+
+
+def import_reference():
+    """Put the reference on sys.path (read-only mount: no bytecode) and import its modules."""
+    if not reference_available():
+        raise RuntimeError(f"reference checkout not found at {REF_ROOT}")
+    sys.dont_write_bytecode = True
+    for p in (REF_ROOT, os.path.join(REF_ROOT, "rlpyt")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    for name in list(sys.modules):  # drop a drop-in alias of `dreamer.*` if one is installed
+        if name == "dreamer" or name.startswith("dreamer."):
+            mod = sys.modules[name]
+            if not str(getattr(mod, "__file__", "")).startswith(REF_ROOT):
+                del sys.modules[name]
+    import dreamer.models.agent as agent  # noqa
+    import dreamer.algos.dreamer_algo as algo  # noqa
+
+    torch.autograd.set_detect_anomaly(False)  # dreamer_algo.py:16 turns it on at import
+    torch.distributions.Distribution.set_default_validate_args(False)  # pcont path
+    return agent, algo
+
+
+@contextlib.contextmanager
+def injected_noise(normal_queue, gumbel_queue=None):
+    """normal_queue: list of tensors popped by every ``Normal.rsample``;
+    gumbel_queue: list of Gumbel(0,1) tensors popped by the categorical samplers."""
+    import torch.distributions.normal as tdn
+    import torch.distributions.one_hot_categorical as tdo
+    import torch.distributions.relaxed_categorical as tdr
+
+    nq = list(normal_queue)
+    gq = list(gumbel_queue or [])
+    orig_sn = tdn._standard_normal
+    orig_oh = tdo.OneHotCategorical.sample
+    orig_rx = tdr.ExpRelaxedCategorical.rsample
+
+    def fake_standard_normal(shape, dtype, device):
+        t = nq.pop(0)
+        assert tuple(t.shape) == tuple(shape), (tuple(t.shape), tuple(shape))
+        return t.to(dtype=dtype, device=device)
+
+    def fake_onehot_sample(self, sample_shape=torch.Size()):
+        g = gq.pop(0)
+        logits = self._categorical.logits
+        idx = torch.argmax(logits + g.to(logits), -1)
+        return torch.nn.functional.one_hot(idx, logits.shape[-1]).to(self._categorical.probs)
+
+    def fake_relaxed_rsample(self, sample_shape=torch.Size()):
+        g = gq.pop(0)
+        scores = (self.logits + g.to(self.logits)) / self.temperature
+        return scores - scores.logsumexp(dim=-1, keepdim=True)
+
+    tdn._standard_normal = fake_standard_normal
+    tdo.OneHotCategorical.sample = fake_onehot_sample
+    tdr.ExpRelaxedCategorical.rsample = fake_relaxed_rsample
+    try:
+        yield
+    finally:
+        tdn._standard_normal = orig_sn
+        tdo.OneHotCategorical.sample = orig_oh
+        tdr.ExpRelaxedCategorical.rsample = orig_rx
+    assert not nq and not gq, f"unused injected noise: {len(nq)} normal, {len(gq)} gumbel"
+
+
+def build_reference_model(weights, A, dist, use_pcont=False, dtype=torch.float32, **model_kwargs):
+    """Reference ``AtariDreamerModel`` loaded with ``weights`` (oracle.expand_aliases form not
+    required: missing conv tensors keep their default init)."""
+    agent, _ = import_reference()
+    from oracle.dreamer_oracle import expand_aliases
+
+    model = agent.AtariDreamerModel(action_shape=(A,), action_dist=dist, use_pcont=use_pcont, **model_kwargs)
+    sd = model.state_dict()
+    full = expand_aliases(weights)
+    for k in sd:
+        if k in full:
+            sd[k] = full[k].clone()
+    model.load_state_dict(sd)
+    model = model.to(dtype)
+    model.train()
+    return model
+
+
+def queues_for_loss(noise, T, H, dist):
+    """The reference's draw order inside ``Dreamer.loss``."""
+    nq, gq = [], []
+    for t in range(T):
+        nq.append(noise["eps_prior_obs"][t])
+        nq.append(noise["eps_post_obs"][t])
+    for h in range(H):
+        if dist == "tanh_normal":
+            nq.append(noise["noise_act"][h])
+        else:
+            gq.append(noise["noise_act"][h])
+        nq.append(noise["eps_prior_img"][h])
+    return nq, gq
+
+
+def reference_loss(model, all_observation, all_action, all_reward, done, noise, horizon, dist,
+                   use_pcont=False, kl_scale=1.0, **algo_kwargs):
+    """Run the reference's ``Dreamer.loss`` on a synthetic ``SamplesFromReplay``."""
+    _, algo_mod = import_reference()
+    from rlpyt.replays.sequence.n_step import SamplesFromReplay
+
+    T = all_action.shape[0] - 1
+    B = all_action.shape[1]
+    algo = algo_mod.Dreamer(batch_size=B, batch_length=T, horizon=horizon, use_pcont=use_pcont,
+                            kl_scale=kl_scale, log_video=False, type=all_action.dtype, **algo_kwargs)
+    algo.agent = types.SimpleNamespace(model=model, device=all_action.device)
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")  # duplicate transition params in the model optimizer (Q3)
+        algo.optim_initialize()
+    samples = SamplesFromReplay(all_observation=all_observation, all_action=all_action,
+                                all_reward=all_reward, return_=None, done=done, done_n=None,
+                                init_rnn_state=None)
+    nq, gq = queues_for_loss(noise, T, horizon, dist)
+    with injected_noise(nq, gq):
+        model_loss, actor_loss, value_loss, info = algo.loss(samples, 0, 0)
+    return algo, model_loss, actor_loss, value_loss, info
+
+
+def reference_rollouts(model, obs_embed, action, noise, horizon, dist, use_pcont=False):
+    """Reference ``rollout_representation`` + ``rollout_policy`` on a synthetic ``obs_embed``
+    (RSSM-only configuration: no conv)."""
+    import_reference()
+    from rlpyt.utils.buffer import buffer_method
+
+    T, B = action.shape[:2]
+    prev = model.representation.initial_state(B, device=action.device, dtype=action.dtype)
+    nq = []
+    for t in range(T):
+        nq += [noise["eps_prior_obs"][t], noise["eps_post_obs"][t]]
+    with injected_noise(nq):
+        prior, post = model.rollout.rollout_representation(T, obs_embed, action, prev)
+    with torch.no_grad():
+        if use_pcont:
+            flat = buffer_method(post[:-1, :], "reshape", (T - 1) * B, -1)
+        else:
+            flat = buffer_method(post, "reshape", T * B, -1)
+    nq, gq = [], []
+    for h in range(horizon):
+        (nq if dist == "tanh_normal" else gq).append(noise["noise_act"][h])
+        nq.append(noise["eps_prior_img"][h])
+    with injected_noise(nq, gq):
+        imag, actions = model.rollout.rollout_policy(horizon, model.policy, flat)
+    return prior, post, imag, actions
