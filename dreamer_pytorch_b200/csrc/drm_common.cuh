@@ -1,0 +1,211 @@
+// Shared device/host helpers for libdreamer_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include "../../include/dreamer_b200.h"
+
+namespace drm {
+
+constexpr int kThreads = 256;          // 8 warps per CTA for the row-tile kernels
+constexpr int kWarps = kThreads / 32;
+constexpr int kNumSM = 148;            // B200
+constexpr int kMaxSmem = 227 * 1024;   // usable dynamic shared memory per CTA
+
+__host__ __device__ inline int rup(int x, int m) { return (x + m - 1) / m * m; }
+__host__ __device__ inline size_t rup_sz(size_t x, size_t m) { return (x + m - 1) / m * m; }
+
+void set_error(const char* fmt, ...);
+int check_device();  // DRM_OK or DRM_E_ARCH / DRM_E_CUDA
+
+#define DRM_CUDA_OK(expr)                                                                    \
+    do {                                                                                     \
+        cudaError_t _e = (expr);                                                             \
+        if (_e != cudaSuccess) {                                                             \
+            drm::set_error("%s:%d %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e)); \
+            return DRM_E_CUDA;                                                               \
+        }                                                                                    \
+    } while (0)
+
+#define DRM_REQUIRE(cond, code, msg)                                     \
+    do {                                                                 \
+        if (!(cond)) {                                                   \
+            drm::set_error("%s:%d %s (%s)", __FILE__, __LINE__, msg, #cond); \
+            return code;                                                 \
+        }                                                                \
+    } while (0)
+
+// ------------------------------------------------------------------------------------------
+// pointwise math (fp32, matches torch's formulas)
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ float elu(float x) { return x > 0.f ? x : expm1f(x); }
+// derivative of ELU expressed through its OUTPUT y: 1 for y>0, y+1 (= e^x) otherwise
+__device__ __forceinline__ float elu_grad_from_out(float y) { return y > 0.f ? 1.f : y + 1.f; }
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + expf(-x)); }
+// torch softplus (beta=1, threshold=20)
+__device__ __forceinline__ float softplusf_(float x) { return x > 20.f ? x : log1pf(expf(x)); }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// ------------------------------------------------------------------------------------------
+// Weight packing: every Linear is re-laid once per call into a zero-padded matrix whose
+// reduction index is the ROW (padded to 4) and whose output index is the COLUMN (leading
+// dimension padded to 32), so the row-tile GEMM below streams it with coalesced, unguarded loads.
+//   transpose=1: dst[k][n] = src[(r0+n)*src_ld + c0 + k]   (forward:  y = x W^T, reduce over in-features)
+//   transpose=0: dst[n][k] = src[(r0+n)*src_ld + c0 + k]   (backward: dx = dy W, reduce over out-features)
+// ------------------------------------------------------------------------------------------
+struct PackJob {
+    const float* src;
+    float* dst;
+    int src_ld;
+    int r0, c0;      // origin of the block inside src
+    int nr, nc;      // block size: nr rows (out-features) x nc cols (in-features)
+    int transpose;
+    int dst_rows;    // padded reduction extent (multiple of 4)
+    int dst_ld;      // padded output extent (multiple of 32)
+};
+constexpr int kMaxPackJobs = 40;
+struct PackJobs {
+    PackJob j[kMaxPackJobs];
+    int n;
+};
+
+// Appends a job and returns the number of floats it occupies in the destination.
+inline size_t pack_size(int red, int out) { return (size_t)rup(red, 4) * (size_t)rup(out, 32); }
+
+struct Packer {
+    PackJobs jobs;
+    float* base;
+    size_t off;  // floats
+    Packer() : base(nullptr), off(0) { jobs.n = 0; }
+    explicit Packer(float* b) : base(b), off(0) { jobs.n = 0; }
+    // forward layout of block rows [r0,r0+nr) x cols [c0,c0+nc) of src: reduce over cols
+    const float* fwd(const float* src, int src_ld, int r0, int nr, int c0, int nc) {
+        return add(src, src_ld, r0, nr, c0, nc, 1, rup(nc, 4), rup(nr, 32));
+    }
+    // backward layout: reduce over rows
+    const float* bwd(const float* src, int src_ld, int r0, int nr, int c0, int nc) {
+        return add(src, src_ld, r0, nr, c0, nc, 0, rup(nr, 4), rup(nc, 32));
+    }
+    const float* add(const float* src, int src_ld, int r0, int nr, int c0, int nc, int tr, int drows, int dld) {
+        float* dst = base ? base + off : nullptr;
+        if (base && jobs.n < kMaxPackJobs) {
+            PackJob& j = jobs.j[jobs.n];
+            j.src = src; j.dst = dst; j.src_ld = src_ld; j.r0 = r0; j.c0 = c0; j.nr = nr; j.nc = nc;
+            j.transpose = tr; j.dst_rows = drows; j.dst_ld = dld;
+        }
+        jobs.n++;
+        off += (size_t)drows * dld;
+        return dst;
+    }
+};
+int launch_pack(const PackJobs& jobs, cudaStream_t stream);
+
+// ------------------------------------------------------------------------------------------
+// Row-tile GEMM primitive.  A CTA owns R rows (R compile-time) whose inputs sit in shared
+// memory; each warp produces 32 output columns at a time for ALL R rows, streaming the packed
+// weight matrix (L2-resident) exactly once per CTA.  Up to two K-segments accumulate into the
+// same outputs (e.g. [action | stoch], [x | h]).
+// ------------------------------------------------------------------------------------------
+struct Seg {
+    const float* W;  // packed [K4][ldw]
+    const float* X;  // shared memory [R][ldx], ldx % 4 == 0, 16-byte aligned
+    int K4;          // multiple of 4; 0 = unused segment
+    int ldx;
+};
+
+template <int R>
+__device__ __forceinline__ void seg_accumulate(float (&acc)[R], const Seg& s, int ldw, int col) {
+    const float* __restrict__ wp = s.W + col;
+    const float* __restrict__ xp = s.X;
+    const int ldx = s.ldx;
+#pragma unroll 2
+    for (int k = 0; k < s.K4; k += 4) {
+        const float w0 = __ldg(wp + (size_t)(k + 0) * ldw);
+        const float w1 = __ldg(wp + (size_t)(k + 1) * ldw);
+        const float w2 = __ldg(wp + (size_t)(k + 2) * ldw);
+        const float w3 = __ldg(wp + (size_t)(k + 3) * ldw);
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const float4 x = *reinterpret_cast<const float4*>(xp + r * ldx + k);
+            acc[r] = fmaf(x.x, w0, acc[r]);
+            acc[r] = fmaf(x.y, w1, acc[r]);
+            acc[r] = fmaf(x.z, w2, acc[r]);
+            acc[r] = fmaf(x.w, w3, acc[r]);
+        }
+    }
+}
+
+// epi(r, col, value) is called for every r < R and col < nout.
+template <int R, class Epi>
+__device__ __forceinline__ void cta_linear(const Seg& s0, const Seg& s1, int ldw, int nout, Epi epi) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int c0 = warp * 32; c0 < nout; c0 += kWarps * 32) {
+        const int col = c0 + lane;  // < ldw always (ldw is nout rounded up to 32)
+        float acc[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) acc[r] = 0.f;
+        seg_accumulate<R>(acc, s0, ldw, col);
+        if (s1.K4 > 0) seg_accumulate<R>(acc, s1, ldw, col);
+        if (col < nout) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) epi(r, col, acc[r]);
+        }
+    }
+}
+
+// Narrow outputs (nout < 32): one (row, col) dot product per warp iteration, lanes split K.
+// Here W is the ORIGINAL row-major [nout, ldw_orig] matrix block (k contiguous), not packed.
+template <class Epi>
+__device__ __forceinline__ void cta_linear_narrow(const float* __restrict__ W, int w_ld, int K,
+                                                  const float* X, int ldx, int nrows, int nout, Epi epi) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int idx = warp; idx < nrows * nout; idx += kWarps) {
+        const int r = idx / nout, c = idx - r * nout;
+        const float* wr = W + (size_t)c * w_ld;
+        const float* xr = X + r * ldx;
+        float s = 0.f;
+        for (int k = lane; k < K; k += 32) s = fmaf(xr[k], __ldg(wr + k), s);
+        s = warp_sum(s);
+        if (lane == 0) epi(r, c, s);
+    }
+}
+
+// Rows-per-CTA dispatch: instantiate kernels for these tile heights only.
+#define DRM_DISPATCH_R(Rv, ...)                                \
+    switch (Rv) {                                              \
+        case 4:  { constexpr int R = 4;  __VA_ARGS__; } break; \
+        case 8:  { constexpr int R = 8;  __VA_ARGS__; } break; \
+        case 12: { constexpr int R = 12; __VA_ARGS__; } break; \
+        case 16: { constexpr int R = 16; __VA_ARGS__; } break; \
+        case 20: { constexpr int R = 20; __VA_ARGS__; } break; \
+        case 24: { constexpr int R = 24; __VA_ARGS__; } break; \
+        case 32: { constexpr int R = 32; __VA_ARGS__; } break; \
+        default: drm::set_error("bad tile height %d", Rv); return DRM_E_SHAPE; \
+    }
+
+// Picks the tile height: the smallest supported R that covers ceil(n / kNumSM) rows (so one
+// wave of CTAs finishes the job), capped by what fits in shared memory.
+inline int pick_rows(int n, size_t smem_bytes_per_row, size_t smem_fixed) {
+    static const int opts[] = {4, 8, 12, 16, 20, 24, 32};
+    int want = (n + kNumSM - 1) / kNumSM;
+    int best = 0;
+    for (int i = 0; i < 7; ++i) {
+        int R = opts[i];
+        if (smem_fixed + (size_t)R * smem_bytes_per_row > (size_t)kMaxSmem) break;
+        best = R;
+        if (R >= want) break;
+    }
+    return best;  // 0: does not fit at all
+}
+
+}  // namespace drm

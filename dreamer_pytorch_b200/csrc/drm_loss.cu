@@ -1,0 +1,176 @@
+// Loss-section kernels: lambda-returns + actor/value losses with their analytic gradients
+// (dreamer_algo.py:314-337,398-422) and KL / free-nats / entropies (dreamer_algo.py:270-273,342-343).
+#include "drm_common.cuh"
+
+namespace drm {
+
+__device__ __forceinline__ float block_sum(float v, float* red) {
+    v = warp_sum(v);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    __syncthreads();
+    if (lane == 0) red[warp] = v;
+    __syncthreads();
+    float s = 0.f;
+    if (warp == 0) {
+        s = lane < (blockDim.x >> 5) ? red[lane] : 0.f;
+        s = warp_sum(s);
+    }
+    return s;  // valid in warp 0
+}
+
+// One thread per imagined trajectory (column n); arrays are [H,N] so accesses are coalesced.
+__global__ void __launch_bounds__(256) returns_loss_kernel(const drm_returns_loss_call c) {
+    __shared__ float red[8];
+    const int N = c.N, H = c.H, L = c.H - 1;
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    const float lam = c.lambda_;
+    const float cmean = -1.f / ((float)L * (float)N);
+    float sum_actor = 0.f, sum_value = 0.f;
+    if (n < N) {
+        auto dsc = [&](int h) -> float { return c.pcont ? sigmoidf_(c.pcont[(size_t)h * N + n]) : c.discount; };
+        // pass 1 (reverse): lambda-returns, compute_return (dreamer_algo.py:398-422)
+        float acc = c.value[(size_t)(H - 1) * N + n];  // bootstrap
+        for (int h = L - 1; h >= 0; --h) {
+            const float d = dsc(h);
+            const float vnext = c.value[(size_t)(h + 1) * N + n];
+            const float target = c.reward[(size_t)h * N + n] + d * vnext * (1.f - lam);
+            acc = target + d * lam * acc;
+            c.returns[(size_t)h * N + n] = acc;
+        }
+        // pass 2 (forward): cumulative discount, losses, adjoints of the return recursion
+        float disc = 1.f, gR = 0.f, dprev = 0.f;
+        c.d_value[n] = 0.f;
+        for (int h = 0; h < L; ++h) {
+            const float d = dsc(h);
+            if (h > 0) disc *= d;  // cumprod([1, d_1, ..., d_{H-2}])  (dreamer_algo.py:322-323)
+            const float Rh = c.returns[(size_t)h * N + n];
+            const float v = c.value[(size_t)h * N + n];
+            c.disc[(size_t)h * N + n] = disc;
+            sum_actor += disc * Rh;
+            const float diff = Rh - v;
+            sum_value += disc * (-0.5f * diff * diff - 0.9189385332046727f);  // Normal(v,1).log_prob(R)
+            c.d_value_pred[(size_t)h * N + n] = cmean * disc * diff;
+            gR = cmean * disc + gR * dprev * lam;  // adjoint of returns[h]
+            dprev = d;
+            const float vnext = c.value[(size_t)(h + 1) * N + n];
+            const float Rnext = (h + 1 < L) ? c.returns[(size_t)(h + 1) * N + n] : vnext;
+            c.d_reward[(size_t)h * N + n] = gR;
+            float dv = gR * d * (1.f - lam);
+            if (h == L - 1) dv += gR * d * lam;  // bootstrap = value[H-1]
+            c.d_value[(size_t)(h + 1) * N + n] = dv;
+            if (c.d_pcont) c.d_pcont[(size_t)h * N + n] = gR * (lam * Rnext + (1.f - lam) * vnext);  // d loss / d d_h (returns part)
+        }
+        c.d_reward[(size_t)L * N + n] = 0.f;
+        c.d_value_pred[(size_t)L * N + n] = 0.f;
+        if (c.d_pcont) {
+            c.d_pcont[(size_t)L * N + n] = 0.f;
+            // pass 3 (reverse): adjoint of the cumprod, then through the sigmoid
+            float carry = 0.f;
+            for (int h = L - 1; h >= 0; --h) {
+                const float d = dsc(h);
+                float gd = c.d_pcont[(size_t)h * N + n];
+                if (h >= 1) {
+                    const float gdisc = cmean * c.returns[(size_t)h * N + n] + carry;
+                    gd += gdisc * c.disc[(size_t)(h - 1) * N + n];
+                    carry = gdisc * d;
+                }
+                c.d_pcont[(size_t)h * N + n] = gd * d * (1.f - d);
+            }
+        }
+    }
+    const float sa = block_sum(sum_actor, red);
+    const float sv = block_sum(sum_value, red);
+    if (threadIdx.x == 0) {
+        atomicAdd(c.losses + 0, cmean * sa);
+        atomicAdd(c.losses + 1, cmean * sv);
+    }
+}
+
+__global__ void __launch_bounds__(256) kl_fwd_kernel(const drm_kl_call c) {
+    __shared__ float red[8];
+    const size_t total = (size_t)c.M * c.S;
+    float kl = 0.f, ep = 0.f, eq = 0.f;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const float mq = c.post_mean[i], sq = c.post_std[i], mp = c.prior_mean[i], sp = c.prior_std[i];
+        const float ratio = sq / sp;
+        const float vr = ratio * ratio;
+        const float t1 = (mq - mp) / sp;
+        kl += 0.5f * (vr + t1 * t1 - 1.f - logf(vr));
+        ep += 1.4189385332046727f + logf(sp);  // 0.5 + 0.5 ln(2 pi) + ln(sigma)
+        eq += 1.4189385332046727f + logf(sq);
+    }
+    const float inv = 1.f / (float)c.M;
+    const float a = block_sum(kl, red), b = block_sum(ep, red), d = block_sum(eq, red);
+    if (threadIdx.x == 0) {
+        atomicAdd(c.out + 1, a * inv);
+        atomicAdd(c.out + 2, b * inv);
+        atomicAdd(c.out + 3, d * inv);
+    }
+}
+__global__ void kl_finalize_kernel(float* out, float free_nats) { out[0] = fmaxf(out[1], free_nats); }
+
+__global__ void __launch_bounds__(256) kl_bwd_kernel(const drm_kl_call c) {
+    const size_t total = (size_t)c.M * c.S;
+    const bool active = c.out[1] > c.free_nats;  // torch.max(div, free_nats): gradient only above the clamp
+    const float inv = active ? 1.f / (float)c.M : 0.f;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const float mq = c.post_mean[i], sq = c.post_std[i], mp = c.prior_mean[i], sp = c.prior_std[i];
+        const float isp2 = 1.f / (sp * sp);
+        const float dm = (mq - mp) * isp2;
+        if (c.d_post_mean) c.d_post_mean[i] = inv * dm;
+        if (c.d_prior_mean) c.d_prior_mean[i] = -inv * dm;
+        if (c.d_post_std) c.d_post_std[i] = inv * (sq * isp2 - 1.f / sq);
+        if (c.d_prior_std) c.d_prior_std[i] = inv * (1.f / sp - (sq * sq + (mq - mp) * (mq - mp)) * isp2 / sp);
+    }
+}
+
+}  // namespace drm
+
+using namespace drm;
+
+extern "C" {
+
+int drm_returns_loss(const drm_returns_loss_call* c, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    DRM_REQUIRE(c != nullptr, DRM_E_ARG, "null call");
+    DRM_REQUIRE(c->H >= 2 && c->N >= 1, DRM_E_SHAPE, "need H >= 2 and N >= 1");
+    DRM_REQUIRE(c->reward && c->value && c->returns && c->disc && c->losses && c->d_reward && c->d_value &&
+                    c->d_value_pred, DRM_E_ARG, "null pointer");
+    DRM_REQUIRE((c->pcont == nullptr) == (c->d_pcont == nullptr), DRM_E_ARG, "pcont and d_pcont must come together");
+    int rc = check_device(); if (rc) return rc;
+    const int grid = (c->N + 255) / 256;
+    returns_loss_kernel<<<grid, 256, 0, stream>>>(*c);
+    DRM_CUDA_OK(cudaGetLastError());
+    return DRM_OK;
+}
+
+int drm_kl_fwd(const drm_kl_call* c, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    DRM_REQUIRE(c != nullptr, DRM_E_ARG, "null call");
+    DRM_REQUIRE(c->M >= 1 && c->S >= 1, DRM_E_SHAPE, "bad dims");
+    DRM_REQUIRE(c->post_mean && c->post_std && c->prior_mean && c->prior_std && c->out, DRM_E_ARG, "null pointer");
+    int rc = check_device(); if (rc) return rc;
+    const size_t total = (size_t)c->M * c->S;
+    int grid = (int)((total + 255) / 256);
+    if (grid > 2 * kNumSM) grid = 2 * kNumSM;
+    kl_fwd_kernel<<<grid, 256, 0, stream>>>(*c);
+    kl_finalize_kernel<<<1, 1, 0, stream>>>(c->out, c->free_nats);
+    DRM_CUDA_OK(cudaGetLastError());
+    return DRM_OK;
+}
+
+int drm_kl_bwd(const drm_kl_call* c, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    DRM_REQUIRE(c != nullptr, DRM_E_ARG, "null call");
+    DRM_REQUIRE(c->M >= 1 && c->S >= 1, DRM_E_SHAPE, "bad dims");
+    DRM_REQUIRE(c->post_mean && c->post_std && c->prior_mean && c->prior_std && c->out, DRM_E_ARG, "null pointer");
+    int rc = check_device(); if (rc) return rc;
+    const size_t total = (size_t)c->M * c->S;
+    int grid = (int)((total + 255) / 256);
+    if (grid > 4 * kNumSM) grid = 4 * kNumSM;
+    kl_bwd_kernel<<<grid, 256, 0, stream>>>(*c);
+    DRM_CUDA_OK(cudaGetLastError());
+    return DRM_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,398 @@
+"""torch.autograd bridge over the C ABI (``include/dreamer_b200.h``).
+
+Each Function unpacks tensors into raw device pointers, calls one ``drm_*`` entry point on the
+current CUDA stream and wraps the outputs; ``backward`` calls the matching ``*_bwd`` entry point
+and honours ``ctx.needs_input_grad`` -- that is how the reference's ``FreezeParameters``
+(dreamer/utils/module.py:17-38, which flips ``requires_grad`` *before* the forward call) is
+respected.  No PyTorch math happens here: if the CUDA library is missing the call raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import List, Optional, Sequence
+
+import torch
+from torch.autograd.function import once_differentiable
+
+from . import _lib
+from ._lib import MAXL
+
+RSSM_KEYS = _lib._RSSM_W  # order of the RSSM weight tensors in every Function signature
+RAW_INIT_STD = math.log(math.exp(5.0) - 1.0)
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _buf(nbytes: int, device) -> torch.Tensor:
+    return torch.empty((max(int(nbytes), 16) + 3) // 4, dtype=torch.float32, device=device)
+
+
+def _f32c(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError("dreamer_pytorch_b200 ops need CUDA tensors (there is no CPU fallback)")
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+def _count(n=1):
+    _lib.launch_count += n
+
+
+# ------------------------------------------------------------------------------------------------
+# struct builders
+# ------------------------------------------------------------------------------------------------
+def _fill_mlp(m: _lib.drm_mlp, weights: Sequence[torch.Tensor], in_dim: int):
+    n_linear = len(weights) // 2
+    if n_linear < 1 or n_linear > MAXL:
+        raise RuntimeError(f"MLP with {n_linear} Linear layers is not supported (1..{MAXL})")
+    m.n_linear = n_linear
+    m.in_dim = in_dim
+    m.hidden = weights[0].shape[0] if n_linear > 1 else 0
+    m.out_dim = weights[2 * (n_linear - 1)].shape[0]
+    for l in range(n_linear):
+        w, b = weights[2 * l], weights[2 * l + 1]
+        exp_in = in_dim if l == 0 else m.hidden
+        exp_out = m.out_dim if l == n_linear - 1 else m.hidden
+        if tuple(w.shape) != (exp_out, exp_in) or tuple(b.shape) != (exp_out,):
+            raise RuntimeError(f"MLP layer {l}: unexpected shapes {tuple(w.shape)} / {tuple(b.shape)}")
+        m.W[l] = _lib.ptr(w)
+        m.b[l] = _lib.ptr(b)
+
+
+def _fill_rssm(s: _lib.drm_rssm, dims, rssm: Sequence[Optional[torch.Tensor]]):
+    s.A, s.S, s.D, s.Hd, s.E = dims
+    for k, t in zip(RSSM_KEYS, rssm):
+        setattr(s, k, _lib.ptr(t))
+
+
+class RolloutCfg:
+    """Static description of a rollout (not a tensor)."""
+
+    def __init__(self, mode, steps, n, dims, act_dist="tanh_normal", n_actor=0, mean_scale=5.0,
+                 raw_init_std=RAW_INIT_STD, act_min_std=1e-4, temperature=0.1, min_std=0.1):
+        self.mode, self.steps, self.n, self.dims = mode, int(steps), int(n), tuple(int(d) for d in dims)
+        self.act_dist, self.n_actor = act_dist, n_actor
+        self.mean_scale, self.raw_init_std, self.act_min_std = mean_scale, raw_init_std, act_min_std
+        self.temperature, self.min_std = temperature, min_std
+
+
+def _build_rollout(cfg: RolloutCfg, t: dict, rssm, actor, training: bool) -> _lib.drm_rollout:
+    r = _lib.drm_rollout()
+    r.mode, r.steps, r.n = cfg.mode, cfg.steps, cfg.n
+    r.act_dist = _lib.DIST[cfg.act_dist]
+    r.precision = _lib.FP32
+    r.training = 1 if training else 0
+    r.act_mean_scale, r.act_raw_init_std, r.act_min_std = cfg.mean_scale, cfg.raw_init_std, cfg.act_min_std
+    r.act_temperature, r.min_std = cfg.temperature, cfg.min_std
+    _fill_rssm(r.rssm, cfg.dims, rssm)
+    if cfg.mode == _lib.MODE_POLICY:
+        _fill_mlp(r.actor, actor, cfg.dims[1] + cfg.dims[2])
+    for k in ("start_stoch", "start_deter", "action_in", "obs_embed", "eps_prior", "eps_post", "noise_act",
+              "prior_mean", "prior_std", "prior_stoch", "deter", "post_mean", "post_std", "post_stoch", "action_out"):
+        setattr(r, k, _lib.ptr(t.get(k)))
+    return r
+
+
+def _check_shape(name, t, shape):
+    if t is None or tuple(t.shape) != tuple(shape):
+        raise RuntimeError(f"{name}: expected shape {tuple(shape)}, got {None if t is None else tuple(t.shape)}")
+
+
+class RolloutFn(torch.autograd.Function):
+    """One persistent-kernel rollout.
+
+    apply(cfg, start_stoch, start_deter, action_in, obs_embed, eps_prior, eps_post, noise_act,
+          *rssm(14), *actor(2*n_actor)) ->
+        POLICY:          (mean, std, stoch, deter, action)
+        TRANSITION:      (mean, std, stoch, deter)
+        REPRESENTATION:  (prior_mean, prior_std, prior_stoch, deter, post_mean, post_std, post_stoch)
+    """
+
+    @staticmethod
+    def forward(ctx, cfg: RolloutCfg, start_stoch, start_deter, action_in, obs_embed, eps_prior, eps_post, noise_act,
+                *weights):
+        lib = _lib.load()
+        A, S, D, Hd, E = cfg.dims
+        T, n = cfg.steps, cfg.n
+        rssm = [_f32c(w) for w in weights[:14]]
+        actor = [_f32c(w) for w in weights[14:]]
+        dev = start_stoch.device
+        t = dict(start_stoch=_f32c(start_stoch), start_deter=_f32c(start_deter), action_in=_f32c(action_in),
+                 obs_embed=_f32c(obs_embed), eps_prior=_f32c(eps_prior), eps_post=_f32c(eps_post),
+                 noise_act=_f32c(noise_act))
+        _check_shape("start_stoch", t["start_stoch"], (n, S))
+        _check_shape("start_deter", t["start_deter"], (n, D))
+        _check_shape("eps_prior", t["eps_prior"], (T, n, S))
+        if cfg.mode == _lib.MODE_POLICY:
+            _check_shape("noise_act", t["noise_act"], (T, n, A))
+        else:
+            _check_shape("action", t["action_in"], (T, n, A))
+        if cfg.mode == _lib.MODE_REPRESENTATION:
+            _check_shape("obs_embed", t["obs_embed"], (T, n, E))
+            _check_shape("eps_post", t["eps_post"], (T, n, S))
+        new = lambda w: torch.empty(T, n, w, dtype=torch.float32, device=dev)
+        t.update(prior_mean=new(S), prior_std=new(S), prior_stoch=new(S), deter=new(D))
+        if cfg.mode == _lib.MODE_REPRESENTATION:
+            t.update(post_mean=new(S), post_std=new(S), post_stoch=new(S))
+        if cfg.mode == _lib.MODE_POLICY:
+            t.update(action_out=new(A))
+        training = torch.is_grad_enabled() and any(ctx.needs_input_grad)
+        r = _build_rollout(cfg, t, rssm, actor, training)
+        ws = _buf(lib.drm_rollout_workspace_bytes(C.byref(r)), dev)
+        save = _buf(lib.drm_rollout_save_bytes(C.byref(r)), dev) if training else None
+        r.workspace, r.workspace_bytes = ws.data_ptr(), ws.numel() * 4
+        if save is not None:
+            r.save, r.save_bytes = save.data_ptr(), save.numel() * 4
+        _lib.check(lib.drm_rollout_fwd(C.byref(r), _stream()), "drm_rollout_fwd")
+        _count()
+        ctx.cfg = cfg
+        ctx.n_w = len(weights)
+        keys = ("start_stoch", "start_deter", "action_in", "obs_embed", "eps_prior", "eps_post", "noise_act",
+                "prior_mean", "prior_std", "prior_stoch", "deter", "post_mean", "post_std", "post_stoch", "action_out")
+        ctx.keys = keys
+        ctx.save_for_backward(*[t.get(k) for k in keys], save, *rssm, *actor)
+        if cfg.mode == _lib.MODE_POLICY:
+            outs = (t["prior_mean"], t["prior_std"], t["prior_stoch"], t["deter"], t["action_out"])
+        elif cfg.mode == _lib.MODE_TRANSITION:
+            outs = (t["prior_mean"], t["prior_std"], t["prior_stoch"], t["deter"])
+        else:
+            outs = (t["prior_mean"], t["prior_std"], t["prior_stoch"], t["deter"], t["post_mean"], t["post_std"],
+                    t["post_stoch"])
+        return outs
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, *gouts):
+        lib = _lib.load()
+        cfg: RolloutCfg = ctx.cfg
+        A, S, D, Hd, E = cfg.dims
+        saved = ctx.saved_tensors
+        nk = len(ctx.keys)
+        t = dict(zip(ctx.keys, saved[:nk]))
+        save = saved[nk]
+        rssm = list(saved[nk + 1: nk + 15])
+        actor = list(saved[nk + 15:])
+        dev = t["start_stoch"].device
+        if save is None:
+            raise RuntimeError("rollout was run without grad; cannot backpropagate")
+        r = _build_rollout(cfg, t, rssm, actor, True)
+        ws = _buf(lib.drm_rollout_workspace_bytes(C.byref(r)), dev)
+        r.workspace, r.workspace_bytes = ws.data_ptr(), ws.numel() * 4
+        r.save, r.save_bytes = save.data_ptr(), save.numel() * 4
+        g = _lib.drm_rollout_grad()
+        gouts = [_f32c(x) for x in gouts]
+        if cfg.mode == _lib.MODE_POLICY:
+            names = ("g_prior_mean", "g_prior_std", "g_prior_stoch", "g_deter", "g_action_out")
+        elif cfg.mode == _lib.MODE_TRANSITION:
+            names = ("g_prior_mean", "g_prior_std", "g_prior_stoch", "g_deter")
+        else:
+            names = ("g_prior_mean", "g_prior_std", "g_prior_stoch", "g_deter", "g_post_mean", "g_post_std",
+                     "g_post_stoch")
+        for k, x in zip(names, gouts):
+            setattr(g, k, _lib.ptr(x))
+        need = ctx.needs_input_grad  # index 0 is cfg
+        policy = cfg.mode == _lib.MODE_POLICY
+        res: List[Optional[torch.Tensor]] = [None] * (8 + ctx.n_w)
+        if not policy:
+            if need[1]:
+                res[1] = torch.empty_like(t["start_stoch"]); g.d_start_stoch = res[1].data_ptr()
+            if need[2]:
+                res[2] = torch.empty_like(t["start_deter"]); g.d_start_deter = res[2].data_ptr()
+            if need[3]:
+                res[3] = torch.empty_like(t["action_in"]); g.d_action_in = res[3].data_ptr()
+            if need[4] and cfg.mode == _lib.MODE_REPRESENTATION:
+                res[4] = torch.empty_like(t["obs_embed"]); g.d_obs_embed = res[4].data_ptr()
+        n_rssm = 14 if cfg.mode == _lib.MODE_REPRESENTATION else 10
+        want_rssm = any(need[8 + i] for i in range(n_rssm))
+        g.want_rssm_grad = 1 if want_rssm else 0
+        if want_rssm:
+            for i in range(n_rssm):
+                gt = torch.empty_like(rssm[i])
+                res[8 + i] = gt
+                setattr(g.rssm, _lib._RSSM_G[i], gt.data_ptr())
+        want_actor = policy and any(need[8 + 14 + i] for i in range(len(actor)))
+        g.want_actor_grad = 1 if want_actor else 0
+        if want_actor:
+            for l in range(len(actor) // 2):
+                gw, gb = torch.empty_like(actor[2 * l]), torch.empty_like(actor[2 * l + 1])
+                res[8 + 14 + 2 * l], res[8 + 14 + 2 * l + 1] = gw, gb
+                g.actor.dW[l], g.actor.db[l] = gw.data_ptr(), gb.data_ptr()
+        _lib.check(lib.drm_rollout_bwd(C.byref(r), C.byref(g), _stream()), "drm_rollout_bwd")
+        _count()
+        # inputs that did not ask for a gradient get None
+        for i in range(len(res)):
+            if i < len(need) and not need[i]:
+                res[i] = None
+        return tuple(res)
+
+
+# ------------------------------------------------------------------------------------------------
+# batched MLP
+# ------------------------------------------------------------------------------------------------
+def _build_mlp_call(x0, x1, weights, M, training) -> _lib.drm_mlp_call:
+    c = _lib.drm_mlp_call()
+    k0 = x0.shape[1]
+    k1 = x1.shape[1] if x1 is not None else 0
+    _fill_mlp(c.mlp, weights, k0 + k1)
+    c.M, c.k0, c.k1 = M, k0, k1
+    c.precision = _lib.FP32
+    c.training = 1 if training else 0
+    c.x0, c.ld0 = _lib.ptr(x0), k0
+    c.x1, c.ld1 = (_lib.ptr(x1), k1) if x1 is not None else (None, 0)
+    return c
+
+
+def mlp_forward_raw(x0, x1, weights, training):
+    """Runs drm_mlp_fwd; returns (y [M,out], save tensor or None)."""
+    lib = _lib.load()
+    M = x0.shape[0]
+    c = _build_mlp_call(x0, x1, weights, M, training)
+    dev = x0.device
+    y = torch.empty(M, c.mlp.out_dim, dtype=torch.float32, device=dev)
+    c.y = y.data_ptr()
+    ws = _buf(lib.drm_mlp_workspace_bytes(C.byref(c)), dev)
+    c.workspace, c.workspace_bytes = ws.data_ptr(), ws.numel() * 4
+    save = None
+    if training:
+        save = _buf(lib.drm_mlp_save_bytes(C.byref(c)), dev)
+        c.save, c.save_bytes = save.data_ptr(), save.numel() * 4
+    _lib.check(lib.drm_mlp_fwd(C.byref(c), _stream()), "drm_mlp_fwd")
+    _count()
+    return y, save
+
+
+def mlp_backward_raw(x0, x1, weights, save, dy, dy_scale=None, dx0=None, dx1=None, accumulate_dx=False,
+                     want_wgrad=False):
+    """Runs drm_mlp_bwd; returns the list of weight grads [dW0, db0, dW1, ...] (or None)."""
+    lib = _lib.load()
+    M = x0.shape[0]
+    b = _lib.drm_mlp_bwd_call()
+    c = _build_mlp_call(x0, x1, weights, M, True)
+    dev = x0.device
+    ws = _buf(lib.drm_mlp_workspace_bytes(C.byref(c)), dev)
+    c.workspace, c.workspace_bytes = ws.data_ptr(), ws.numel() * 4
+    if save is not None:
+        c.save, c.save_bytes = save.data_ptr(), save.numel() * 4
+    b.fwd = c
+    b.dy = _lib.ptr(dy)
+    b.dy_scale = _lib.ptr(dy_scale)
+    b.dx0 = _lib.ptr(dx0)
+    b.dx1 = _lib.ptr(dx1)
+    b.accumulate_dx = 1 if accumulate_dx else 0
+    b.want_wgrad = 1 if want_wgrad else 0
+    grads = None
+    if want_wgrad:
+        grads = [torch.empty_like(w) for w in weights]
+        for l in range(len(weights) // 2):
+            b.grad.dW[l], b.grad.db[l] = grads[2 * l].data_ptr(), grads[2 * l + 1].data_ptr()
+    _lib.check(lib.drm_mlp_bwd(C.byref(b), _stream()), "drm_mlp_bwd")
+    _count()
+    return grads
+
+
+class MlpFn(torch.autograd.Function):
+    """y = MLP([x0 | x1]) with ELU between the Linear layers.  apply(x0, x1_or_None, *weights)."""
+
+    @staticmethod
+    def forward(ctx, x0, x1, *weights):
+        x0 = _f32c(x0)
+        x1 = _f32c(x1)
+        weights = [_f32c(w) for w in weights]
+        training = torch.is_grad_enabled() and any(ctx.needs_input_grad)
+        y, save = mlp_forward_raw(x0, x1, weights, training)
+        ctx.save_for_backward(x0, x1, save, *weights)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        x0, x1, save, *weights = ctx.saved_tensors
+        need = ctx.needs_input_grad
+        dy = _f32c(dy)
+        dx0 = torch.empty_like(x0) if need[0] else None
+        dx1 = torch.empty_like(x1) if (x1 is not None and need[1]) else None
+        want_w = any(need[2:])
+        grads = mlp_backward_raw(x0, x1, weights, save, dy, None, dx0, dx1, False, want_w)
+        res = [dx0, dx1] + (grads if grads is not None else [None] * len(weights))
+        for i in range(len(res)):
+            if not need[i]:
+                res[i] = None
+        return tuple(res)
+
+
+# ------------------------------------------------------------------------------------------------
+# KL / entropies
+# ------------------------------------------------------------------------------------------------
+class KLFn(torch.autograd.Function):
+    """(div_clamped, div_raw, prior_entropy, post_entropy) = KLFn.apply(post_mean, post_std, prior_mean,
+    prior_std, free_nats); only div_clamped is differentiable."""
+
+    @staticmethod
+    def forward(ctx, post_mean, post_std, prior_mean, prior_std, free_nats: float):
+        lib = _lib.load()
+        ts = [_f32c(x) for x in (post_mean, post_std, prior_mean, prior_std)]
+        S = ts[0].shape[-1]
+        M = ts[0].numel() // S
+        c = _lib.drm_kl_call()
+        c.M, c.S, c.free_nats = M, S, float(free_nats)
+        c.post_mean, c.post_std, c.prior_mean, c.prior_std = [_lib.ptr(x) for x in ts]
+        out = torch.zeros(4, dtype=torch.float32, device=ts[0].device)
+        c.out = out.data_ptr()
+        _lib.check(lib.drm_kl_fwd(C.byref(c), _stream()), "drm_kl_fwd")
+        _count()
+        ctx.save_for_backward(out, *ts)
+        ctx.free_nats = float(free_nats)
+        ctx.mark_non_differentiable(*[])
+        return out[0], out[1].detach(), out[2].detach(), out[3].detach()
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g_div, *_unused):
+        lib = _lib.load()
+        out, *ts = ctx.saved_tensors
+        S = ts[0].shape[-1]
+        c = _lib.drm_kl_call()
+        c.M, c.S, c.free_nats = ts[0].numel() // S, S, ctx.free_nats
+        c.post_mean, c.post_std, c.prior_mean, c.prior_std = [_lib.ptr(x) for x in ts]
+        c.out = out.data_ptr()
+        need = ctx.needs_input_grad
+        grads = [torch.empty_like(x) if need[i] else None for i, x in enumerate(ts)]
+        c.d_post_mean, c.d_post_std, c.d_prior_mean, c.d_prior_std = [_lib.ptr(x) for x in grads]
+        _lib.check(lib.drm_kl_bwd(C.byref(c), _stream()), "drm_kl_bwd")
+        _count()
+        grads = [None if x is None else x * g_div for x in grads]
+        return (*grads, None)
+
+
+# ------------------------------------------------------------------------------------------------
+# lambda-returns + actor / value losses (forward and analytic gradients in one launch)
+# ------------------------------------------------------------------------------------------------
+def returns_loss_raw(reward, value, pcont, discount, lambda_):
+    """reward/value/pcont: [H,N] contiguous.  Returns dict(losses[2], returns, disc, d_reward, d_value,
+    d_pcont, d_value_pred)."""
+    lib = _lib.load()
+    H, N = reward.shape
+    dev = reward.device
+    c = _lib.drm_returns_loss_call()
+    c.H, c.N, c.discount, c.lambda_ = H, N, float(discount), float(lambda_)
+    out = dict(
+        losses=torch.zeros(2, dtype=torch.float32, device=dev),
+        returns=torch.empty(H - 1, N, dtype=torch.float32, device=dev),
+        disc=torch.empty(H - 1, N, dtype=torch.float32, device=dev),
+        d_reward=torch.empty(H, N, dtype=torch.float32, device=dev),
+        d_value=torch.empty(H, N, dtype=torch.float32, device=dev),
+        d_value_pred=torch.empty(H, N, dtype=torch.float32, device=dev),
+        d_pcont=torch.empty(H, N, dtype=torch.float32, device=dev) if pcont is not None else None,
+    )
+    c.reward, c.value, c.pcont = _lib.ptr(reward), _lib.ptr(value), _lib.ptr(pcont)
+    for k in ("returns", "disc", "losses", "d_reward", "d_value", "d_pcont", "d_value_pred"):
+        setattr(c, k, _lib.ptr(out[k]))
+    _lib.check(lib.drm_returns_loss(C.byref(c), _stream()), "drm_returns_loss")
+    _count()
+    return out

@@ -1,0 +1,221 @@
+/*
+ * dreamer_b200.h -- C ABI of libdreamer_b200.so: the RSSM rollout hot path of
+ * juliusfrost/dreamer-pytorch as hand-written CUDA for sm_100a (B200).
+ *
+ * Every entry point is launch-only and asynchronous on the caller's stream, never allocates,
+ * frees or retains a pointer past the call, and returns 0 or a negative drm_status.  All
+ * pointers are DEVICE pointers to fp32 data unless stated otherwise.  Tensors are contiguous,
+ * time-major [time, batch, feature] exactly as the reference lays them out.
+ *
+ * Reference interfaces replaced (paths relative to the reference checkout):
+ *   drm_rollout_fwd / drm_rollout_bwd
+ *       DRM_MODE_POLICY          RSSMRollout.rollout_policy          dreamer/models/rnns.py:224-244
+ *                                + AgentModel.policy                 dreamer/models/agent.py:101-117
+ *                                + ActionDecoder.forward             dreamer/models/action.py:51-66
+ *       DRM_MODE_TRANSITION      RSSMRollout.rollout_transition      dreamer/models/rnns.py:207-222
+ *                                (T=1: RSSMTransition.forward        dreamer/models/rnns.py:98-107)
+ *       DRM_MODE_REPRESENTATION  RSSMRollout.rollout_representation  dreamer/models/rnns.py:179-205
+ *                                (T=1: RSSMRepresentation.forward    dreamer/models/rnns.py:149-159)
+ *   drm_mlp_fwd / drm_mlp_bwd    DenseModel.forward (the nn.Sequential) dreamer/models/dense.py:28-43
+ *                                ActionDecoder.feedforward_model        dreamer/models/action.py:37-52
+ *   drm_returns_loss             Dreamer.compute_return + actor/value loss
+ *                                dreamer/algos/dreamer_algo.py:314-337,398-422
+ *   drm_kl_loss                  KL(post||prior), free nats, entropies
+ *                                dreamer/algos/dreamer_algo.py:270-273,342-343
+ */
+#ifndef DREAMER_B200_H
+#define DREAMER_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DRM_ABI_VERSION 1
+#define DRM_MAX_LINEAR 8 /* Linear layers per MLP (reference uses 4) */
+
+typedef enum drm_status {
+    DRM_OK = 0,
+    DRM_E_SHAPE = -1,     /* unsupported / inconsistent dimensions */
+    DRM_E_ALIGN = -2,     /* pointer not 16-byte aligned */
+    DRM_E_ARCH = -3,      /* device is not sm_100 */
+    DRM_E_WORKSPACE = -4, /* workspace / save buffer too small or NULL */
+    DRM_E_CUDA = -5,      /* CUDA runtime error, see drm_last_error() */
+    DRM_E_ARG = -6        /* NULL or inconsistent argument */
+} drm_status;
+
+typedef enum drm_mode { DRM_MODE_POLICY = 0, DRM_MODE_TRANSITION = 1, DRM_MODE_REPRESENTATION = 2 } drm_mode;
+typedef enum drm_act_dist { DRM_DIST_TANH_NORMAL = 0, DRM_DIST_ONE_HOT = 1, DRM_DIST_RELAXED_ONE_HOT = 2 } drm_act_dist;
+typedef enum drm_precision { DRM_FP32 = 0, DRM_BF16 = 1 } drm_precision;
+
+/* An MLP: n_linear Linear layers, ELU (alpha=1) between them, none after the last.
+ * W[i] is row-major [out_i, in_i] (torch nn.Linear.weight), b[i] is [out_i]. */
+typedef struct drm_mlp {
+    int32_t n_linear;
+    int32_t in_dim;
+    int32_t hidden;
+    int32_t out_dim;
+    const float* W[DRM_MAX_LINEAR];
+    const float* b[DRM_MAX_LINEAR];
+} drm_mlp;
+
+/* Gradient sinks for an MLP: fresh buffers, OVERWRITTEN (not accumulated). NULL = not wanted. */
+typedef struct drm_mlp_grad {
+    float* dW[DRM_MAX_LINEAR];
+    float* db[DRM_MAX_LINEAR];
+} drm_mlp_grad;
+
+/* RSSM weights (rnns.py:72-88,134-139).  A=action, S=stoch, D=deter, Hd=hidden, E=obs embed. */
+typedef struct drm_rssm {
+    int32_t A, S, D, Hd, E;
+    const float* W_in;  /* _rnn_input_model.0.weight        [Hd, A+S]  */
+    const float* b_in;  /*                                  [Hd]       */
+    const float* W_ih;  /* _cell.weight_ih                  [3D, Hd]   gate order r,z,n */
+    const float* W_hh;  /* _cell.weight_hh                  [3D, D]    */
+    const float* b_ih;  /*                                  [3D]       */
+    const float* b_hh;  /*                                  [3D]       */
+    const float* W_p1;  /* _stochastic_prior_model.0.weight [Hd, D]    */
+    const float* b_p1;
+    const float* W_p2;  /* _stochastic_prior_model.2.weight [2S, Hd]   */
+    const float* b_p2;
+    const float* W_q1;  /* _stochastic_posterior_model.0.weight [Hd, D+E] (REPRESENTATION only) */
+    const float* b_q1;
+    const float* W_q2;  /* _stochastic_posterior_model.2.weight [2S, Hd] */
+    const float* b_q2;
+} drm_rssm;
+
+typedef struct drm_rssm_grad { /* OVERWRITTEN; NULL = not wanted; all-or-nothing per group */
+    float *dW_in, *db_in, *dW_ih, *dW_hh, *db_ih, *db_hh, *dW_p1, *db_p1, *dW_p2, *db_p2;
+    float *dW_q1, *db_q1, *dW_q2, *db_q2;
+} drm_rssm_grad;
+
+/* One rollout of `steps` sequential steps over `n` independent rows. */
+typedef struct drm_rollout {
+    int32_t mode;      /* drm_mode */
+    int32_t steps;     /* T or H */
+    int32_t n;         /* rows: B (observation rollout) or N = B*T (imagination) */
+    int32_t act_dist;  /* drm_act_dist (POLICY) */
+    int32_t precision; /* drm_precision */
+    int32_t training;  /* 1: fill `save` for drm_rollout_bwd */
+    float act_mean_scale;   /* 5.0      action.py:22,56 */
+    float act_raw_init_std; /* ln(e^5-1) action.py:35   */
+    float act_min_std;      /* 1e-4     action.py:20,57 */
+    float act_temperature;  /* 0.1      action.py:65    */
+    float min_std;          /* 0.1      rnns.py:104,155 */
+    drm_rssm rssm;
+    drm_mlp actor; /* POLICY: in_dim=S+D, out_dim=2A (tanh_normal) or A */
+    /* inputs */
+    const float* start_stoch; /* [n,S] */
+    const float* start_deter; /* [n,D] */
+    const float* action_in;   /* [steps,n,A]  TRANSITION / REPRESENTATION */
+    const float* obs_embed;   /* [steps,n,E]  REPRESENTATION */
+    const float* eps_prior;   /* [steps,n,S]  N(0,1) */
+    const float* eps_post;    /* [steps,n,S]  REPRESENTATION */
+    const float* noise_act;   /* [steps,n,A]  POLICY: N(0,1) (tanh_normal) or Gumbel(0,1) */
+    /* outputs */
+    float* prior_mean;  /* [steps,n,S] */
+    float* prior_std;   /* [steps,n,S] */
+    float* prior_stoch; /* [steps,n,S] */
+    float* deter;       /* [steps,n,D]  shared by prior and posterior */
+    float* post_mean;   /* [steps,n,S]  REPRESENTATION */
+    float* post_std;
+    float* post_stoch;
+    float* action_out;  /* [steps,n,A]  POLICY */
+    /* scratch owned by the caller */
+    void* save;         /* drm_rollout_save_bytes(); written by fwd when training, read by bwd */
+    size_t save_bytes;
+    void* workspace;    /* drm_rollout_workspace_bytes(); contents undefined after the call */
+    size_t workspace_bytes;
+} drm_rollout;
+
+/* Upstream gradients (NULL = zero) and gradient sinks (NULL = not wanted) of a rollout. */
+typedef struct drm_rollout_grad {
+    const float *g_prior_mean, *g_prior_std, *g_prior_stoch, *g_deter; /* [steps,n,.] */
+    const float *g_post_mean, *g_post_std, *g_post_stoch;
+    const float* g_action_out;
+    float* d_start_stoch; /* [n,S]  (NULL for POLICY: the start state is detached, rnns.py:236) */
+    float* d_start_deter; /* [n,D] */
+    float* d_action_in;   /* [steps,n,A] */
+    float* d_obs_embed;   /* [steps,n,E] */
+    drm_rssm_grad rssm;
+    int32_t want_rssm_grad;  /* 0: weights frozen (FreezeParameters), skip all RSSM weight grads */
+    int32_t want_actor_grad;
+    drm_mlp_grad actor;
+} drm_rollout_grad;
+
+/* Batched MLP over M rows; the input is the concatenation of two column segments
+ * (e.g. stoch [M,S] and deter [M,D]) so that `feat` never has to be materialised. */
+typedef struct drm_mlp_call {
+    drm_mlp mlp;
+    int32_t M;
+    int32_t k0, k1;            /* k0 + k1 == mlp.in_dim; k1 may be 0 */
+    int32_t precision;
+    int32_t training;          /* fwd: keep hidden activations in `save` */
+    const float* x0; int64_t ld0; /* [M,k0], row stride ld0 elements */
+    const float* x1; int64_t ld1;
+    float* y;                  /* [M,out_dim] */
+    void* save; size_t save_bytes;           /* drm_mlp_save_bytes() */
+    void* workspace; size_t workspace_bytes; /* drm_mlp_workspace_bytes() */
+} drm_mlp_call;
+
+typedef struct drm_mlp_bwd_call {
+    drm_mlp_call fwd;          /* same description as the forward call (y unused) */
+    const float* dy;           /* [M,out_dim] */
+    const float* dy_scale;     /* device scalar multiplied into dy, or NULL (=1) */
+    float* dx0; float* dx1;    /* [M,k0] / [M,k1] with the forward's strides; NULL = not wanted */
+    int32_t accumulate_dx;     /* 1: dx += , 0: dx = */
+    int32_t want_wgrad;
+    drm_mlp_grad grad;
+} drm_mlp_bwd_call;
+
+/* lambda-returns + actor loss + value loss over imagined heads, forward AND the gradients of
+ * both scalar losses w.r.t. the head outputs (dreamer_algo.py:314-337,398-422). */
+typedef struct drm_returns_loss_call {
+    int32_t H, N;
+    float discount, lambda_;
+    const float* reward;  /* [H,N] reward head mean */
+    const float* value;   /* [H,N] value head mean  */
+    const float* pcont;   /* [H,N] pcont logits or NULL (constant discount) */
+    float* returns;       /* [H-1,N] */
+    float* disc;          /* [H-1,N] cumulative discount */
+    float* losses;        /* [2]: actor_loss, value_loss  (must be zero-filled by the caller) */
+    float* d_reward;      /* [H,N] d actor_loss / d reward */
+    float* d_value;       /* [H,N] d actor_loss / d value  */
+    float* d_pcont;       /* [H,N] d actor_loss / d pcont logits, or NULL */
+    float* d_value_pred;  /* [H,N] d value_loss / d value_pred (row H-1 zero) */
+} drm_returns_loss_call;
+
+/* KL(post || prior) mean, free-nats clamp and entropies, forward and gradient. */
+typedef struct drm_kl_call {
+    int32_t M, S;         /* M = T*B rows */
+    float free_nats;
+    const float *post_mean, *post_std, *prior_mean, *prior_std; /* [M,S] */
+    float* out;           /* [4]: div (clamped), raw mean KL, prior entropy, post entropy; zero-filled by caller */
+    /* gradient of the clamped div (unit upstream), written by drm_kl_bwd; NULL = not wanted */
+    float *d_post_mean, *d_post_std, *d_prior_mean, *d_prior_std;
+} drm_kl_call;
+
+int drm_version(void);
+const char* drm_last_error(void);
+size_t drm_sizeof(const char* struct_name); /* ABI self-check for FFI bindings */
+
+size_t drm_rollout_save_bytes(const drm_rollout* r);
+size_t drm_rollout_workspace_bytes(const drm_rollout* r);
+int drm_rollout_fwd(const drm_rollout* r, void* stream);
+int drm_rollout_bwd(const drm_rollout* r, const drm_rollout_grad* g, void* stream);
+
+size_t drm_mlp_save_bytes(const drm_mlp_call* c);
+size_t drm_mlp_workspace_bytes(const drm_mlp_call* c);
+int drm_mlp_fwd(const drm_mlp_call* c, void* stream);
+int drm_mlp_bwd(const drm_mlp_bwd_call* c, void* stream);
+
+int drm_returns_loss(const drm_returns_loss_call* c, void* stream);
+int drm_kl_fwd(const drm_kl_call* c, void* stream);
+int drm_kl_bwd(const drm_kl_call* c, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DREAMER_B200_H */
