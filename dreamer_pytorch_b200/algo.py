@@ -1,0 +1,175 @@
+"""Fused loss section of ``Dreamer.loss`` (dreamer/algos/dreamer_algo.py:270-337,398-422).
+
+``imagination_losses`` is the B200-native replacement of the actor / value block: one persistent
+imagination kernel (actor MLP -> action sample -> RSSM transition, H steps), three fused head MLP
+kernels over all H*N imagined states, one kernel for lambda-returns + both losses + their analytic
+gradients, and hand-written backward kernels.  The math is the reference's; the freezing pattern of
+``FreezeParameters`` (world model frozen for the actor loss, everything but the value model frozen
+for the value loss) is built in.
+
+``dreamer_loss`` mirrors the whole of ``Dreamer.loss`` on top of it for callers that do not go
+through the unchanged ``dreamer_algo.py`` (which also works, via the drop-in modules).
+"""
+from __future__ import annotations
+
+from collections import namedtuple
+from typing import Optional
+
+import torch
+
+from . import _lib, noise
+from .dropin.dense import mlp_weights
+from .dropin.rnns import RSSMState, get_feat
+from .functional import (KLFn, RolloutCfg, _f32c, mlp_backward_raw, mlp_forward_raw, returns_loss_raw,
+                         rollout_backward_raw, rollout_forward_raw)
+
+ImagInfo = namedtuple("ImagInfo", ["imag", "actions", "reward", "value", "returns", "discount"])
+
+
+class _ActorLossFn(torch.autograd.Function):
+    """actor_loss = -mean(discount * lambda_returns) over an H-step imagined rollout.
+
+    Differentiable w.r.t. the actor weights only (dreamer_algo.py:293-324: the world model, the
+    value model and pcont are frozen; the start state is detached, rnns.py:236).
+    Also returns, as non-differentiable by-products, everything the value loss needs.
+    """
+
+    @staticmethod
+    def forward(ctx, pack, *actor_w):
+        (cfg, t, rssm, reward_w, value_w, pcont_w, discount, lambda_) = pack
+        actor = [_f32c(w) for w in actor_w]
+        training = torch.is_grad_enabled() and any(ctx.needs_input_grad)
+        save = rollout_forward_raw(cfg, t, rssm, actor, training)
+        H, N = cfg.steps, cfg.n
+        S, D = cfg.dims[1], cfg.dims[2]
+        x0 = t["prior_stoch"].view(H * N, S)
+        x1 = t["deter"].view(H * N, D)
+        # heads over all imagined states; hidden activations are kept: the actor path needs their
+        # data-gradients, the value loss the value head's weight-gradients
+        reward, rsave = mlp_forward_raw(x0, x1, reward_w, training)
+        value, vsave = mlp_forward_raw(x0, x1, value_w, True)
+        pc, psave = (mlp_forward_raw(x0, x1, pcont_w, training) if pcont_w else (None, None))
+        out = returns_loss_raw(reward.view(H, N), value.view(H, N), None if pc is None else pc.view(H, N), discount,
+                               lambda_)
+        ctx.pack = (cfg, t, rssm, actor, save, reward_w, value_w, pcont_w, rsave, vsave, psave, out, x0, x1)
+        aux = (t["prior_mean"], t["prior_std"], t["prior_stoch"], t["deter"], t["action_out"], reward.view(H, N, 1),
+               value.view(H, N, 1), out["returns"].view(H - 1, N, 1), out["disc"].view(H - 1, N, 1),
+               out["losses"][1].clone(), out["d_value_pred"], vsave if vsave is not None else torch.empty(0))
+        ctx.mark_non_differentiable(*aux)
+        return (out["losses"][0].clone(), *aux)
+
+    @staticmethod
+    def backward(ctx, g_loss, *_):
+        (cfg, t, rssm, actor, save, reward_w, value_w, pcont_w, rsave, vsave, psave, out, x0, x1) = ctx.pack
+        H, N = cfg.steps, cfg.n
+        g_loss = _f32c(g_loss)
+        g_stoch = torch.empty_like(t["prior_stoch"])
+        g_deter = torch.empty_like(t["deter"])
+        gs, gd = g_stoch.view(H * N, -1), g_deter.view(H * N, -1)
+        mlp_backward_raw(x0, x1, reward_w, rsave, out["d_reward"].view(H * N, 1), g_loss, gs, gd, False, False)
+        mlp_backward_raw(x0, x1, value_w, vsave, out["d_value"].view(H * N, 1), g_loss, gs, gd, True, False)
+        if pcont_w:
+            mlp_backward_raw(x0, x1, pcont_w, psave, out["d_pcont"].view(H * N, 1), g_loss, gs, gd, True, False)
+        _, _, gactor = rollout_backward_raw(cfg, t, rssm, actor, save, dict(g_prior_stoch=g_stoch, g_deter=g_deter),
+                                            want_actor=True)
+        ctx.pack = None
+        return (None, *gactor)
+
+
+class _ValueLossFn(torch.autograd.Function):
+    """value_loss = -mean(discount * Normal(value_model(feat[:-1]), 1).log_prob(returns))
+    (dreamer_algo.py:331-337).  The forward values were already produced by the imagination pass
+    (same weights, same detached features), so only the weight-gradient pass runs here."""
+
+    @staticmethod
+    def forward(ctx, pack, *value_w):
+        (x0, x1, vsave, d_value_pred, loss) = pack
+        ctx.pack = (x0, x1, vsave, d_value_pred, [_f32c(w) for w in value_w])
+        return loss.clone()
+
+    @staticmethod
+    def backward(ctx, g_loss):
+        x0, x1, vsave, d_value_pred, value_w = ctx.pack
+        grads = mlp_backward_raw(x0, x1, value_w, vsave, d_value_pred.view(-1, 1), _f32c(g_loss), None, None, False,
+                                 True)
+        ctx.pack = None
+        return (None, *grads)
+
+
+def imagination_losses(model, start_state: RSSMState, horizon: int, discount: float = 0.99,
+                       discount_lambda: float = 0.95, use_pcont: bool = False):
+    """Actor and value losses of ``Dreamer.loss`` from (detached) start states [N, .].
+
+    Returns (actor_loss, value_loss, ImagInfo).  ``actor_loss.backward()`` fills the action
+    decoder's gradients, ``value_loss.backward()`` the value model's -- exactly the pattern of
+    dreamer_algo.py:174-180.
+    """
+    dec = model.action_decoder
+    if not model.can_fuse_policy():
+        raise RuntimeError("imagination_losses needs a policy the fused kernel covers (tanh_normal in train() mode, "
+                           "one_hot or relaxed_one_hot)")
+    stoch = _f32c(start_state.stoch.detach())
+    deter = _f32c(start_state.deter.detach())
+    N, dev = stoch.shape[0], stoch.device
+    A, S = int(model.action_size), model.stochastic_size
+    cfg = RolloutCfg(_lib.MODE_POLICY, horizon, N, model.transition.dims(), act_dist=model.action_dist,
+                     mean_scale=float(dec.mean_scale), raw_init_std=float(dec.raw_init_std),
+                     act_min_std=float(dec.min_std))
+    if model.action_dist == "tanh_normal":
+        noise_act = noise.normal("noise_act", (horizon, N, A), dev)
+    else:
+        noise_act = noise.gumbel("noise_act", (horizon, N, A), dev)
+    eps = noise.normal("eps_prior", (horizon, N, S), dev)
+    t = dict(start_stoch=stoch, start_deter=deter, eps_prior=eps, noise_act=noise_act)
+    frozen = lambda ws: [_f32c(w.detach()) for w in ws]
+    rssm = frozen(model.transition.weights()) + [None] * 4
+    reward_w = frozen(mlp_weights(model.reward_model.model))
+    value_params = mlp_weights(model.value_model.model)
+    pcont_w = frozen(mlp_weights(model.pcont.model)) if use_pcont else []
+    pack = (cfg, t, rssm, reward_w, frozen(value_params), pcont_w, discount, discount_lambda)
+    (actor_loss, mean, std, st, dt, actions, reward, value, returns, disc, vloss, d_value_pred,
+     vsave) = _ActorLossFn.apply(pack, *dec.weights())
+    x0, x1 = st.view(horizon * N, -1), dt.view(horizon * N, -1)
+    value_loss = _ValueLossFn.apply((x0, x1, vsave, d_value_pred, vloss), *value_params)
+    info = ImagInfo(RSSMState(mean, std, st, dt), actions, reward, value, returns, disc)
+    return actor_loss, value_loss, info
+
+
+LossInfo = namedtuple("LossInfo", ["model_loss", "actor_loss", "value_loss", "prior_entropy", "post_entropy", "divergence",
+                                   "reward_loss", "image_loss", "pcont_loss"])
+
+
+def dreamer_loss(model, observation, action, reward, done=None, horizon=15, discount=0.99, discount_lambda=0.95,
+                 free_nats=3.0, kl_scale=1.0, use_pcont=False, pcont_scale=10.0, obs_embed: Optional[torch.Tensor] = None):
+    """``Dreamer.loss`` (dreamer_algo.py:213-371) on the fused kernels.
+
+    observation: float [T,B,C,H,W] already normalised (or None with ``obs_embed`` [T,B,E] given, the
+    RSSM-only configuration); action [T,B,A]; reward [T,B,1]; done [T,B,1].
+    Returns (model_loss, actor_loss, value_loss, LossInfo).
+    """
+    T, B = action.shape[:2]
+    embed = model.observation_encoder(observation) if obs_embed is None else obs_embed
+    prev = model.representation.initial_state(B, device=action.device, dtype=action.dtype)
+    prior, post = model.rollout.rollout_representation(T, embed, action, prev)
+    feat = get_feat(post)
+    reward_pred = model.reward_model(feat)
+    reward_loss = -torch.mean(reward_pred.log_prob(reward))
+    if obs_embed is None:
+        image_pred = model.observation_decoder(feat)
+        image_loss = -torch.mean(image_pred.log_prob(observation))
+    else:
+        image_loss = reward_loss.new_zeros(())
+    pcont_loss = reward_loss.new_zeros(())
+    if use_pcont:
+        pcont_pred = model.pcont(feat)
+        pcont_loss = -torch.mean(pcont_pred.log_prob(discount * (1 - done.float())))
+    div, _, prior_ent, post_ent = KLFn.apply(post.mean, post.std, prior.mean, prior.std, free_nats)
+    model_loss = kl_scale * div + reward_loss + image_loss
+    if use_pcont:
+        model_loss = model_loss + pcont_scale * pcont_loss
+    with torch.no_grad():
+        src = post[:-1] if use_pcont else post
+        flat = RSSMState(*(f.reshape(-1, f.shape[-1]) for f in src))
+    actor_loss, value_loss, _ = imagination_losses(model, flat, horizon, discount, discount_lambda, use_pcont)
+    info = LossInfo(model_loss, actor_loss, value_loss, prior_ent, post_ent, div, reward_loss, image_loss, pcont_loss)
+    return model_loss, actor_loss, value_loss, info

@@ -104,11 +104,104 @@ def _check_shape(name, t, shape):
         raise RuntimeError(f"{name}: expected shape {tuple(shape)}, got {None if t is None else tuple(t.shape)}")
 
 
+IO_KEYS = ("start_stoch", "start_deter", "action_in", "obs_embed", "eps_prior", "eps_post", "noise_act",
+           "prior_mean", "prior_std", "prior_stoch", "deter", "post_mean", "post_std", "post_stoch", "action_out")
+OUT_KEYS = {
+    _lib.MODE_POLICY: ("prior_mean", "prior_std", "prior_stoch", "deter", "action_out"),
+    _lib.MODE_TRANSITION: ("prior_mean", "prior_std", "prior_stoch", "deter"),
+    _lib.MODE_REPRESENTATION: ("prior_mean", "prior_std", "prior_stoch", "deter", "post_mean", "post_std",
+                               "post_stoch"),
+}
+
+
+def rollout_forward_raw(cfg: RolloutCfg, t: dict, rssm, actor, training: bool):
+    """Validates shapes, allocates the outputs into ``t`` and runs drm_rollout_fwd.
+    Returns the save buffer (None unless training)."""
+    lib = _lib.load()
+    A, S, D, Hd, E = cfg.dims
+    T, n = cfg.steps, cfg.n
+    dev = t["start_stoch"].device
+    _check_shape("start_stoch", t["start_stoch"], (n, S))
+    _check_shape("start_deter", t["start_deter"], (n, D))
+    _check_shape("eps_prior", t["eps_prior"], (T, n, S))
+    if cfg.mode == _lib.MODE_POLICY:
+        _check_shape("noise_act", t["noise_act"], (T, n, A))
+    else:
+        _check_shape("action", t["action_in"], (T, n, A))
+    if cfg.mode == _lib.MODE_REPRESENTATION:
+        _check_shape("obs_embed", t["obs_embed"], (T, n, E))
+        _check_shape("eps_post", t["eps_post"], (T, n, S))
+    new = lambda w: torch.empty(T, n, w, dtype=torch.float32, device=dev)
+    t.update(prior_mean=new(S), prior_std=new(S), prior_stoch=new(S), deter=new(D))
+    if cfg.mode == _lib.MODE_REPRESENTATION:
+        t.update(post_mean=new(S), post_std=new(S), post_stoch=new(S))
+    if cfg.mode == _lib.MODE_POLICY:
+        t.update(action_out=new(A))
+    r = _build_rollout(cfg, t, rssm, actor, training)
+    ws = _buf(lib.drm_rollout_workspace_bytes(C.byref(r)), dev)
+    save = _buf(lib.drm_rollout_save_bytes(C.byref(r)), dev) if training else None
+    r.workspace, r.workspace_bytes = ws.data_ptr(), ws.numel() * 4
+    if save is not None:
+        r.save, r.save_bytes = save.data_ptr(), save.numel() * 4
+    _lib.check(lib.drm_rollout_fwd(C.byref(r), _stream()), "drm_rollout_fwd")
+    _count()
+    return save
+
+
+def rollout_backward_raw(cfg: RolloutCfg, t: dict, rssm, actor, save, gouts: dict, want_inputs=(False,) * 4,
+                         want_rssm=False, want_actor=False):
+    """Runs drm_rollout_bwd.  gouts: name ('g_prior_mean', ...) -> tensor or None.
+    want_inputs: (start_stoch, start_deter, action_in, obs_embed).
+    Returns (input grads [4], rssm grads list or None, actor grads list or None)."""
+    lib = _lib.load()
+    dev = t["start_stoch"].device
+    if save is None:
+        raise RuntimeError("rollout was run without grad; cannot backpropagate")
+    r = _build_rollout(cfg, t, rssm, actor, True)
+    ws = _buf(lib.drm_rollout_workspace_bytes(C.byref(r)), dev)
+    r.workspace, r.workspace_bytes = ws.data_ptr(), ws.numel() * 4
+    r.save, r.save_bytes = save.data_ptr(), save.numel() * 4
+    g = _lib.drm_rollout_grad()
+    keep = []
+    for k, x in gouts.items():
+        x = _f32c(x)
+        keep.append(x)
+        setattr(g, k, _lib.ptr(x))
+    policy = cfg.mode == _lib.MODE_POLICY
+    din: List[Optional[torch.Tensor]] = [None] * 4
+    if not policy:
+        if want_inputs[0]:
+            din[0] = torch.empty_like(t["start_stoch"]); g.d_start_stoch = din[0].data_ptr()
+        if want_inputs[1]:
+            din[1] = torch.empty_like(t["start_deter"]); g.d_start_deter = din[1].data_ptr()
+        if want_inputs[2]:
+            din[2] = torch.empty_like(t["action_in"]); g.d_action_in = din[2].data_ptr()
+        if want_inputs[3] and cfg.mode == _lib.MODE_REPRESENTATION:
+            din[3] = torch.empty_like(t["obs_embed"]); g.d_obs_embed = din[3].data_ptr()
+    n_rssm = 14 if cfg.mode == _lib.MODE_REPRESENTATION else 10
+    g.want_rssm_grad = 1 if want_rssm else 0
+    grssm = None
+    if want_rssm:
+        grssm = [torch.empty_like(rssm[i]) for i in range(n_rssm)] + [None] * (14 - n_rssm)
+        for i in range(n_rssm):
+            setattr(g.rssm, _lib._RSSM_G[i], grssm[i].data_ptr())
+    want_actor = policy and want_actor
+    g.want_actor_grad = 1 if want_actor else 0
+    gactor = None
+    if want_actor:
+        gactor = [torch.empty_like(w) for w in actor]
+        for l in range(len(actor) // 2):
+            g.actor.dW[l], g.actor.db[l] = gactor[2 * l].data_ptr(), gactor[2 * l + 1].data_ptr()
+    _lib.check(lib.drm_rollout_bwd(C.byref(r), C.byref(g), _stream()), "drm_rollout_bwd")
+    _count()
+    return din, grssm, gactor
+
+
 class RolloutFn(torch.autograd.Function):
     """One persistent-kernel rollout.
 
     apply(cfg, start_stoch, start_deter, action_in, obs_embed, eps_prior, eps_post, noise_act,
-          *rssm(14), *actor(2*n_actor)) ->
+          *rssm(14), *actor(2*n_linear)) ->
         POLICY:          (mean, std, stoch, deter, action)
         TRANSITION:      (mean, std, stoch, deter)
         REPRESENTATION:  (prior_mean, prior_std, prior_stoch, deter, post_mean, post_std, post_stoch)
@@ -117,117 +210,40 @@ class RolloutFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, cfg: RolloutCfg, start_stoch, start_deter, action_in, obs_embed, eps_prior, eps_post, noise_act,
                 *weights):
-        lib = _lib.load()
-        A, S, D, Hd, E = cfg.dims
-        T, n = cfg.steps, cfg.n
         rssm = [_f32c(w) for w in weights[:14]]
         actor = [_f32c(w) for w in weights[14:]]
-        dev = start_stoch.device
         t = dict(start_stoch=_f32c(start_stoch), start_deter=_f32c(start_deter), action_in=_f32c(action_in),
                  obs_embed=_f32c(obs_embed), eps_prior=_f32c(eps_prior), eps_post=_f32c(eps_post),
                  noise_act=_f32c(noise_act))
-        _check_shape("start_stoch", t["start_stoch"], (n, S))
-        _check_shape("start_deter", t["start_deter"], (n, D))
-        _check_shape("eps_prior", t["eps_prior"], (T, n, S))
-        if cfg.mode == _lib.MODE_POLICY:
-            _check_shape("noise_act", t["noise_act"], (T, n, A))
-        else:
-            _check_shape("action", t["action_in"], (T, n, A))
-        if cfg.mode == _lib.MODE_REPRESENTATION:
-            _check_shape("obs_embed", t["obs_embed"], (T, n, E))
-            _check_shape("eps_post", t["eps_post"], (T, n, S))
-        new = lambda w: torch.empty(T, n, w, dtype=torch.float32, device=dev)
-        t.update(prior_mean=new(S), prior_std=new(S), prior_stoch=new(S), deter=new(D))
-        if cfg.mode == _lib.MODE_REPRESENTATION:
-            t.update(post_mean=new(S), post_std=new(S), post_stoch=new(S))
-        if cfg.mode == _lib.MODE_POLICY:
-            t.update(action_out=new(A))
         training = torch.is_grad_enabled() and any(ctx.needs_input_grad)
-        r = _build_rollout(cfg, t, rssm, actor, training)
-        ws = _buf(lib.drm_rollout_workspace_bytes(C.byref(r)), dev)
-        save = _buf(lib.drm_rollout_save_bytes(C.byref(r)), dev) if training else None
-        r.workspace, r.workspace_bytes = ws.data_ptr(), ws.numel() * 4
-        if save is not None:
-            r.save, r.save_bytes = save.data_ptr(), save.numel() * 4
-        _lib.check(lib.drm_rollout_fwd(C.byref(r), _stream()), "drm_rollout_fwd")
-        _count()
+        save = rollout_forward_raw(cfg, t, rssm, actor, training)
         ctx.cfg = cfg
         ctx.n_w = len(weights)
-        keys = ("start_stoch", "start_deter", "action_in", "obs_embed", "eps_prior", "eps_post", "noise_act",
-                "prior_mean", "prior_std", "prior_stoch", "deter", "post_mean", "post_std", "post_stoch", "action_out")
-        ctx.keys = keys
-        ctx.save_for_backward(*[t.get(k) for k in keys], save, *rssm, *actor)
-        if cfg.mode == _lib.MODE_POLICY:
-            outs = (t["prior_mean"], t["prior_std"], t["prior_stoch"], t["deter"], t["action_out"])
-        elif cfg.mode == _lib.MODE_TRANSITION:
-            outs = (t["prior_mean"], t["prior_std"], t["prior_stoch"], t["deter"])
-        else:
-            outs = (t["prior_mean"], t["prior_std"], t["prior_stoch"], t["deter"], t["post_mean"], t["post_std"],
-                    t["post_stoch"])
-        return outs
+        ctx.save_for_backward(*[t.get(k) for k in IO_KEYS], save, *rssm, *actor)
+        return tuple(t[k] for k in OUT_KEYS[cfg.mode])
 
     @staticmethod
     @once_differentiable
     def backward(ctx, *gouts):
-        lib = _lib.load()
         cfg: RolloutCfg = ctx.cfg
-        A, S, D, Hd, E = cfg.dims
         saved = ctx.saved_tensors
-        nk = len(ctx.keys)
-        t = dict(zip(ctx.keys, saved[:nk]))
+        nk = len(IO_KEYS)
+        t = dict(zip(IO_KEYS, saved[:nk]))
         save = saved[nk]
         rssm = list(saved[nk + 1: nk + 15])
         actor = list(saved[nk + 15:])
-        dev = t["start_stoch"].device
-        if save is None:
-            raise RuntimeError("rollout was run without grad; cannot backpropagate")
-        r = _build_rollout(cfg, t, rssm, actor, True)
-        ws = _buf(lib.drm_rollout_workspace_bytes(C.byref(r)), dev)
-        r.workspace, r.workspace_bytes = ws.data_ptr(), ws.numel() * 4
-        r.save, r.save_bytes = save.data_ptr(), save.numel() * 4
-        g = _lib.drm_rollout_grad()
-        gouts = [_f32c(x) for x in gouts]
-        if cfg.mode == _lib.MODE_POLICY:
-            names = ("g_prior_mean", "g_prior_std", "g_prior_stoch", "g_deter", "g_action_out")
-        elif cfg.mode == _lib.MODE_TRANSITION:
-            names = ("g_prior_mean", "g_prior_std", "g_prior_stoch", "g_deter")
-        else:
-            names = ("g_prior_mean", "g_prior_std", "g_prior_stoch", "g_deter", "g_post_mean", "g_post_std",
-                     "g_post_stoch")
-        for k, x in zip(names, gouts):
-            setattr(g, k, _lib.ptr(x))
         need = ctx.needs_input_grad  # index 0 is cfg
-        policy = cfg.mode == _lib.MODE_POLICY
-        res: List[Optional[torch.Tensor]] = [None] * (8 + ctx.n_w)
-        if not policy:
-            if need[1]:
-                res[1] = torch.empty_like(t["start_stoch"]); g.d_start_stoch = res[1].data_ptr()
-            if need[2]:
-                res[2] = torch.empty_like(t["start_deter"]); g.d_start_deter = res[2].data_ptr()
-            if need[3]:
-                res[3] = torch.empty_like(t["action_in"]); g.d_action_in = res[3].data_ptr()
-            if need[4] and cfg.mode == _lib.MODE_REPRESENTATION:
-                res[4] = torch.empty_like(t["obs_embed"]); g.d_obs_embed = res[4].data_ptr()
+        names = ["g_" + k if k != "action_out" else "g_action_out" for k in OUT_KEYS[cfg.mode]]
         n_rssm = 14 if cfg.mode == _lib.MODE_REPRESENTATION else 10
         want_rssm = any(need[8 + i] for i in range(n_rssm))
-        g.want_rssm_grad = 1 if want_rssm else 0
-        if want_rssm:
-            for i in range(n_rssm):
-                gt = torch.empty_like(rssm[i])
-                res[8 + i] = gt
-                setattr(g.rssm, _lib._RSSM_G[i], gt.data_ptr())
-        want_actor = policy and any(need[8 + 14 + i] for i in range(len(actor)))
-        g.want_actor_grad = 1 if want_actor else 0
-        if want_actor:
-            for l in range(len(actor) // 2):
-                gw, gb = torch.empty_like(actor[2 * l]), torch.empty_like(actor[2 * l + 1])
-                res[8 + 14 + 2 * l], res[8 + 14 + 2 * l + 1] = gw, gb
-                g.actor.dW[l], g.actor.db[l] = gw.data_ptr(), gb.data_ptr()
-        _lib.check(lib.drm_rollout_bwd(C.byref(r), C.byref(g), _stream()), "drm_rollout_bwd")
-        _count()
-        # inputs that did not ask for a gradient get None
+        want_actor = any(need[8 + 14 + i] for i in range(len(actor)))
+        din, grssm, gactor = rollout_backward_raw(cfg, t, rssm, actor, save, dict(zip(names, gouts)),
+                                                  (need[1], need[2], need[3], need[4]), want_rssm, want_actor)
+        res: List[Optional[torch.Tensor]] = [None] + din + [None, None, None]
+        res += grssm if grssm is not None else [None] * 14
+        res += gactor if gactor is not None else [None] * len(actor)
         for i in range(len(res)):
-            if i < len(need) and not need[i]:
+            if not need[i]:
                 res[i] = None
         return tuple(res)
 
@@ -348,8 +364,9 @@ class KLFn(torch.autograd.Function):
         _count()
         ctx.save_for_backward(out, *ts)
         ctx.free_nats = float(free_nats)
-        ctx.mark_non_differentiable(*[])
-        return out[0], out[1].detach(), out[2].detach(), out[3].detach()
+        res = [out[i].clone() for i in range(4)]
+        ctx.mark_non_differentiable(res[1], res[2], res[3])
+        return tuple(res)
 
     @staticmethod
     @once_differentiable
