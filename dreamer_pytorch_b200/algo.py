@@ -38,7 +38,7 @@ class _ActorLossFn(torch.autograd.Function):
     def forward(ctx, pack, *actor_w):
         (cfg, t, rssm, reward_w, value_w, pcont_w, discount, lambda_) = pack
         actor = [_f32c(w) for w in actor_w]
-        training = torch.is_grad_enabled() and any(ctx.needs_input_grad)
+        training = any(ctx.needs_input_grad)
         save = rollout_forward_raw(cfg, t, rssm, actor, training)
         H, N = cfg.steps, cfg.n
         S, D = cfg.dims[1], cfg.dims[2]

@@ -50,5 +50,8 @@ class DenseModel(nn.Module):
         if self._dist == "normal":
             return td.independent.Independent(td.Normal(reshaped, 1), len(self._output_shape))
         if self._dist == "binary":
-            return td.independent.Independent(td.Bernoulli(logits=reshaped), len(self._output_shape))
+            # validate_args=False: the reference feeds the soft target discount*(1-done) to log_prob
+            # (dreamer_algo.py:266-269), which torch >= 1.8 rejects under argument validation
+            return td.independent.Independent(td.Bernoulli(logits=reshaped, validate_args=False),
+                                              len(self._output_shape), validate_args=False)
         raise NotImplementedError(self._dist)

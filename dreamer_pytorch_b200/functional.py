@@ -215,7 +215,7 @@ class RolloutFn(torch.autograd.Function):
         t = dict(start_stoch=_f32c(start_stoch), start_deter=_f32c(start_deter), action_in=_f32c(action_in),
                  obs_embed=_f32c(obs_embed), eps_prior=_f32c(eps_prior), eps_post=_f32c(eps_post),
                  noise_act=_f32c(noise_act))
-        training = torch.is_grad_enabled() and any(ctx.needs_input_grad)
+        training = any(ctx.needs_input_grad)
         save = rollout_forward_raw(cfg, t, rssm, actor, training)
         ctx.cfg = cfg
         ctx.n_w = len(weights)
@@ -320,7 +320,7 @@ class MlpFn(torch.autograd.Function):
         x0 = _f32c(x0)
         x1 = _f32c(x1)
         weights = [_f32c(w) for w in weights]
-        training = torch.is_grad_enabled() and any(ctx.needs_input_grad)
+        training = any(ctx.needs_input_grad)
         y, save = mlp_forward_raw(x0, x1, weights, training)
         ctx.save_for_backward(x0, x1, save, *weights)
         return y
