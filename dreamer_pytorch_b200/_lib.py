@@ -97,6 +97,9 @@ SYMBOLS = {
     "drm_version": (C.c_int, []),
     "drm_last_error": (C.c_char_p, []),
     "drm_sizeof": (C.c_size_t, [C.c_char_p]),
+    "drm_launch_count": (C.c_ulonglong, []),
+    "drm_prof_enable": (None, [C.c_int]),
+    "drm_prof_read": (C.c_int, [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]),
     "drm_rollout_save_bytes": (C.c_size_t, [C.POINTER(drm_rollout)]),
     "drm_rollout_workspace_bytes": (C.c_size_t, [C.POINTER(drm_rollout)]),
     "drm_rollout_fwd": (C.c_int, [C.POINTER(drm_rollout), P]),

@@ -18,6 +18,16 @@ __host__ __device__ inline size_t rup_sz(size_t x, size_t m) { return (x + m - 1
 void set_error(const char* fmt, ...);
 int check_device();  // DRM_OK or DRM_E_ARCH / DRM_E_CUDA
 
+// Diagnostics (drm_launch_count / drm_prof_*): every kernel launch site bumps the counter and,
+// when profiling is on, is bracketed by a cudaEvent pair on the launching stream.
+enum ProfSlot { PROF_PACK = 0, PROF_ROLLOUT_FWD, PROF_ROLLOUT_BWD, PROF_MLP_FWD, PROF_MLP_BWD, PROF_WGRAD,
+                PROF_LOSS, PROF_N };
+struct ProfScope {
+    int slot; cudaStream_t stream; int idx;
+    ProfScope(int slot, cudaStream_t stream);
+    ~ProfScope();
+};
+
 #define DRM_CUDA_OK(expr)                                                                    \
     do {                                                                                     \
         cudaError_t _e = (expr);                                                             \

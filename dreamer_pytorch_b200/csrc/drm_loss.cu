@@ -139,6 +139,7 @@ int drm_returns_loss(const drm_returns_loss_call* c, void* stream_) {
     DRM_REQUIRE((c->pcont == nullptr) == (c->d_pcont == nullptr), DRM_E_ARG, "pcont and d_pcont must come together");
     int rc = check_device(); if (rc) return rc;
     const int grid = (c->N + 255) / 256;
+    ProfScope prof(PROF_LOSS, stream);
     returns_loss_kernel<<<grid, 256, 0, stream>>>(*c);
     DRM_CUDA_OK(cudaGetLastError());
     return DRM_OK;
@@ -153,6 +154,7 @@ int drm_kl_fwd(const drm_kl_call* c, void* stream_) {
     const size_t total = (size_t)c->M * c->S;
     int grid = (int)((total + 255) / 256);
     if (grid > 2 * kNumSM) grid = 2 * kNumSM;
+    ProfScope prof(PROF_LOSS, stream);
     kl_fwd_kernel<<<grid, 256, 0, stream>>>(*c);
     kl_finalize_kernel<<<1, 1, 0, stream>>>(c->out, c->free_nats);
     DRM_CUDA_OK(cudaGetLastError());
@@ -168,6 +170,7 @@ int drm_kl_bwd(const drm_kl_call* c, void* stream_) {
     const size_t total = (size_t)c->M * c->S;
     int grid = (int)((total + 255) / 256);
     if (grid > 4 * kNumSM) grid = 4 * kNumSM;
+    ProfScope prof(PROF_LOSS, stream);
     kl_bwd_kernel<<<grid, 256, 0, stream>>>(*c);
     DRM_CUDA_OK(cudaGetLastError());
     return DRM_OK;

@@ -223,6 +223,7 @@ int launch_wgrad(const float* dY, int64_t ldy, const float* X, int64_t ldx, int 
     int mps = rup((M + splits - 1) / splits, WG_M);
     splits = (M + mps - 1) / mps;
     dim3 grid(tn, tk, splits);
+    ProfScope prof(PROF_WGRAD, stream);
     wgrad_kernel<<<grid, 256, 0, stream>>>(dY, ldy, X, ldx, M, Nout, K, dW, ld_dw, koff, db, mps);
     DRM_CUDA_OK(cudaGetLastError());
     return DRM_OK;
@@ -296,6 +297,7 @@ static int launch_mlp_kernel(const MlpDev& p, bool backward, cudaStream_t stream
     const size_t smem = per_row * Rv;
     const int tiles = (p.M + Rv - 1) / Rv;
     const int grid = tiles < 2 * kNumSM ? tiles : 2 * kNumSM;
+    ProfScope prof(backward ? PROF_MLP_BWD : PROF_MLP_FWD, stream);
     if (!backward) {
         DRM_DISPATCH_R(Rv, {
             DRM_CUDA_OK(cudaFuncSetAttribute(mlp_fwd_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -278,6 +278,7 @@ int launch_rollout_bwd(const RollDev& p, cudaStream_t stream) {
     const size_t smem = per_row * Rv;
     const int tiles = (p.n + Rv - 1) / Rv;
     const int grid = tiles < kNumSM ? tiles : kNumSM;
+    ProfScope prof(PROF_ROLLOUT_BWD, stream);
     DRM_DISPATCH_R(Rv, {
         DRM_CUDA_OK(cudaFuncSetAttribute(rollout_bwd_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         rollout_bwd_kernel<R><<<grid, kThreads, smem, stream>>>(p);

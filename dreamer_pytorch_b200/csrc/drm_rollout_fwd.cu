@@ -273,6 +273,7 @@ int launch_rollout_fwd(const RollDev& p, cudaStream_t stream) {
     const size_t smem = per_row * Rv;
     const int tiles = (p.n + Rv - 1) / Rv;
     const int grid = tiles < kNumSM ? tiles : kNumSM;
+    ProfScope prof(PROF_ROLLOUT_FWD, stream);
     DRM_DISPATCH_R(Rv, {
         DRM_CUDA_OK(cudaFuncSetAttribute(rollout_fwd_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         rollout_fwd_kernel<R><<<grid, kThreads, smem, stream>>>(p);

@@ -32,6 +32,33 @@ int check_device() {
     return DRM_OK;
 }
 
+// ---------------------------------------------------------------------------------------------
+// launch counter + optional per-kernel CUDA-event timing
+// ---------------------------------------------------------------------------------------------
+static unsigned long long g_launches = 0;
+static int g_prof_on = 0;
+constexpr int kProfCap = 8192;
+struct ProfRec { cudaEvent_t a, b; int slot; };
+static ProfRec g_prof[kProfCap];
+static int g_prof_n = 0;       // records in use
+static int g_prof_made = 0;    // events created so far (reused across enable/reset)
+
+ProfScope::ProfScope(int slot_, cudaStream_t stream_) : slot(slot_), stream(stream_), idx(-1) {
+    ++g_launches;
+    if (!g_prof_on || g_prof_n >= kProfCap) return;
+    idx = g_prof_n++;
+    if (idx >= g_prof_made) {
+        cudaEventCreate(&g_prof[idx].a);
+        cudaEventCreate(&g_prof[idx].b);
+        g_prof_made = idx + 1;
+    }
+    g_prof[idx].slot = slot;
+    cudaEventRecord(g_prof[idx].a, stream);
+}
+ProfScope::~ProfScope() {
+    if (idx >= 0) cudaEventRecord(g_prof[idx].b, stream);
+}
+
 __global__ void pack_kernel(PackJobs jobs) {
     const PackJob j = jobs.j[blockIdx.y];
     const int total = j.dst_rows * j.dst_ld;
@@ -50,6 +77,7 @@ int launch_pack(const PackJobs& jobs, cudaStream_t stream) {
     if (jobs.n == 0) return DRM_OK;
     DRM_REQUIRE(jobs.n <= kMaxPackJobs, DRM_E_SHAPE, "too many pack jobs");
     dim3 grid(16, jobs.n);
+    ProfScope prof(PROF_PACK, stream);
     pack_kernel<<<grid, 256, 0, stream>>>(jobs);
     DRM_CUDA_OK(cudaGetLastError());
     return DRM_OK;
@@ -61,6 +89,30 @@ extern "C" {
 
 int drm_version(void) { return DRM_ABI_VERSION; }
 const char* drm_last_error(void) { return drm::g_err; }
+
+unsigned long long drm_launch_count(void) { return drm::g_launches; }
+
+void drm_prof_enable(int on) {
+    drm::g_prof_on = on ? 1 : 0;
+    drm::g_prof_n = 0;
+}
+
+int drm_prof_read(int slot, double* total_ms, int* count) {
+    if (slot < 0 || slot >= drm::PROF_N || !total_ms || !count) return DRM_E_ARG;
+    double tot = 0.0;
+    int n = 0;
+    for (int i = 0; i < drm::g_prof_n; ++i) {
+        if (drm::g_prof[i].slot != slot) continue;
+        if (cudaEventSynchronize(drm::g_prof[i].b) != cudaSuccess) return DRM_E_CUDA;
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, drm::g_prof[i].a, drm::g_prof[i].b) != cudaSuccess) return DRM_E_CUDA;
+        tot += ms;
+        ++n;
+    }
+    *total_ms = tot;
+    *count = n;
+    return DRM_OK;
+}
 
 size_t drm_sizeof(const char* name) {
     if (!name) return 0;

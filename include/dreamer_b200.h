@@ -201,6 +201,15 @@ int drm_version(void);
 const char* drm_last_error(void);
 size_t drm_sizeof(const char* struct_name); /* ABI self-check for FFI bindings */
 
+/* Diagnostics.  drm_launch_count: kernels launched by this library since load.
+ * drm_prof_enable(1) resets and starts bracketing every kernel launch with a cudaEvent pair on
+ * the launching stream; drm_prof_read sums the elapsed time of one slot (it synchronises on the
+ * recorded events).  Slots: 0 weight pack, 1 rollout fwd, 2 rollout bwd, 3 MLP fwd, 4 MLP bwd,
+ * 5 weight-gradient GEMM, 6 loss kernels. */
+unsigned long long drm_launch_count(void);
+void drm_prof_enable(int on);
+int drm_prof_read(int slot, double* total_ms, int* count);
+
 size_t drm_rollout_save_bytes(const drm_rollout* r);
 size_t drm_rollout_workspace_bytes(const drm_rollout* r);
 int drm_rollout_fwd(const drm_rollout* r, void* stream);
