@@ -240,7 +240,7 @@ static int validate(const drm_mlp_call* c) {
     DRM_REQUIRE(m.n_linear == 1 || (m.hidden > 0 && m.hidden % 4 == 0), DRM_E_SHAPE,
                 "hidden size must be a positive multiple of 4");
     DRM_REQUIRE(c->k0 > 0 && c->k1 >= 0 && c->k0 + c->k1 == m.in_dim, DRM_E_SHAPE, "k0 + k1 != in_dim");
-    DRM_REQUIRE(c->precision == DRM_FP32, DRM_E_SHAPE, "only DRM_FP32 is implemented for the batched MLP");
+    DRM_REQUIRE(c->precision == DRM_FP32 || c->precision == DRM_BF16, DRM_E_SHAPE, "unknown precision");
     return DRM_OK;
 }
 
@@ -358,7 +358,12 @@ size_t drm_mlp_workspace_bytes(const drm_mlp_call* c) {
     if (!c) return 0;
     size_t f = fwd_pack_floats(c);
     size_t b = bwd_pack_floats(c) + dysave_floats(c);
-    return (f > b ? f : b) * sizeof(float) + 256;
+    size_t bytes = (f > b ? f : b) * sizeof(float) + 256;
+    if (c->precision == DRM_BF16) {
+        const size_t t = tc::mlp_tc_fwd_workspace_bytes(c) + 256;
+        if (t > bytes) bytes = t;
+    }
+    return bytes;
 }
 
 int drm_mlp_fwd(const drm_mlp_call* c, void* stream_) {
@@ -371,6 +376,7 @@ int drm_mlp_fwd(const drm_mlp_call* c, void* stream_) {
     DRM_REQUIRE(c->workspace && c->workspace_bytes >= drm_mlp_workspace_bytes(c), DRM_E_WORKSPACE, "workspace too small");
     const bool save = c->training && m.n_linear > 1;
     if (save) DRM_REQUIRE(c->save && c->save_bytes >= drm_mlp_save_bytes(c), DRM_E_WORKSPACE, "save buffer too small");
+    if (c->precision == DRM_BF16) return tc::mlp_tc_fwd(c, stream);
     MlpDev p; fill_common(p, c);
     Packer pk((float*)c->workspace);
     for (int l = 0; l < m.n_linear; ++l) {

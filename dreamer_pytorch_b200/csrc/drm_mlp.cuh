@@ -18,4 +18,10 @@ int launch_linear_nobias(const float* x, int64_t ldx, int M, int K, const float*
 int launch_linear_dx(const float* dy, int M, int nout, const float* W, int w_ld, int w_c0, int K, float* dx,
                      int64_t lddx, float* pack_ws, cudaStream_t stream);
 
+// bf16 tensor-core path (drm_mlp_tc.cu)
+namespace tc {
+size_t mlp_tc_fwd_workspace_bytes(const drm_mlp_call* c);
+int mlp_tc_fwd(const drm_mlp_call* c, cudaStream_t stream);
+}  // namespace tc
+
 }  // namespace drm

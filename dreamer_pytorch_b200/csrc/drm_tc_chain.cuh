@@ -1,0 +1,221 @@
+// Warp-specialised "GEMM chain" engine shared by the bf16 tensor-core kernels (batched MLP forward /
+// backward, imagination rollout forward / backward).
+//
+// A CTA owns a tile of 128 rows.  Per repetition (one row tile of an MLP, or one time step of a rollout)
+// it executes a fixed PROGRAM of phases; a phase is a group of tcgen05 GEMM ops
+//     D[128 x n] (TMEM columns d_col..) (+)= A[128 x K] (shared, chunk-major bf16) * W[n x K]^T
+// followed by an epilogue that reads the accumulators and (typically) writes the next A operand.
+//
+// Roles:   warps 0..EPI_WARPS-1  epilogue (kernel specific code)
+//          warp  EPI_WARPS       weight producer: streams the pre-packed bf16 weight images of the whole
+//                                program, in consumption order, through a ring of shared-memory stages
+//                                with 1-D bulk copies (TMA engine) -- weights stay L2 resident
+//          warp  EPI_WARPS+1     MMA issuer (one elected thread)
+// Barriers: full[s]/empty[s] per stage (producer <-> MMA), acc_full (MMA -> epilogue, one per phase),
+//          a_ready (epilogue -> MMA: "A operands of the next phase are in shared memory and the
+//          accumulators of the previous phase have been consumed").
+#pragma once
+#include "drm_common.cuh"
+#include "drm_tc.cuh"
+
+namespace drm {
+namespace tc {
+
+constexpr int kTileRows = 128;
+constexpr int kEpiWarps = 8;
+constexpr int kEpiThreads = kEpiWarps * 32;
+constexpr int kChainThreads = kEpiThreads + 64;
+constexpr int kMaxOps = 24;
+constexpr int kMaxPhases = 12;
+constexpr int kChunkBytes = kTileRows * 16;  // one 8-wide K chunk of a 128-row A operand
+constexpr int kTmemCols = 512;
+
+struct TcOp {
+    uint32_t a_off[2];     // byte offset (from the dynamic smem base) of up to two A segments
+    uint16_t a_chunks[2];  // 8-wide K chunks in each segment; a_chunks[0] even, sum even
+    uint16_t n;            // MMA N: multiple of 16, 16..256
+    uint16_t d_col;        // first TMEM column of the accumulator
+    uint16_t accumulate;   // 1: accumulate onto what the columns already hold
+    uint16_t phase_end;    // 1: last op of its phase
+};
+
+struct TcProgram {
+    int n_ops;
+    int n_phases;
+    int n_stages;
+    int stage_bytes;
+    uint32_t stage_off;  // byte offset of stage 0 in dynamic smem (1024-aligned)
+    TcOp op[kMaxOps];
+};
+
+// chunks of one weight slab for an op with MMA N = n (even, >= 2)
+__host__ __device__ inline int slab_chunks(int stage_bytes, int n) {
+    int kc = stage_bytes / (n * 16);
+    kc &= ~1;
+    return kc < 2 ? 2 : kc;
+}
+// bytes of the whole program's weight stream (one repetition)
+inline size_t program_weight_bytes(const TcProgram& pg) {
+    size_t b = 0;
+    for (int i = 0; i < pg.n_ops; ++i) b += (size_t)(pg.op[i].a_chunks[0] + pg.op[i].a_chunks[1]) * pg.op[i].n * 16;
+    return b;
+}
+
+struct ChainBars {
+    uint64_t full[8];
+    uint64_t empty[8];
+    uint64_t acc_full;
+    uint64_t a_ready;
+    uint32_t tmem_slot;
+    uint32_t pad;
+};
+
+// Called by every thread at kernel start.  Returns the TMEM base address.
+__device__ __forceinline__ uint32_t chain_setup(ChainBars* bars, const TcProgram& pg) {
+    const int warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < pg.n_stages; ++s) {
+            mbar_init(&bars->full[s], 1);
+            mbar_init(&bars->empty[s], 1);
+        }
+        mbar_init(&bars->acc_full, 1);
+        mbar_init(&bars->a_ready, kEpiThreads);
+        fence_barrier_init();
+    }
+    if (warp == kEpiWarps) tmem_alloc(&bars->tmem_slot, kTmemCols);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    return bars->tmem_slot;
+}
+
+__device__ __forceinline__ void chain_teardown(uint32_t tmem_base) {
+    tc_fence_before_sync();
+    __syncthreads();
+    if ((threadIdx.x >> 5) == kEpiWarps) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+// Producer warp: stream the weight images of `reps` repetitions of the program.
+__device__ __forceinline__ void chain_producer(const TcProgram& pg, ChainBars* bars, uint8_t* smem,
+                                               const uint8_t* __restrict__ wstream, int reps) {
+    if ((threadIdx.x & 31) != 0) return;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int rep = 0; rep < reps; ++rep) {
+        const uint8_t* src = wstream;
+        for (int i = 0; i < pg.n_ops; ++i) {
+            const int n = pg.op[i].n;
+            int chunks = pg.op[i].a_chunks[0] + pg.op[i].a_chunks[1];
+            const int kc = slab_chunks(pg.stage_bytes, n);
+            while (chunks > 0) {
+                const int c = chunks < kc ? chunks : kc;
+                const uint32_t bytes = (uint32_t)c * n * 16;
+                mbar_wait(&bars->empty[stage], phase ^ 1);
+                mbar_expect_tx(&bars->full[stage], bytes);
+                bulk_g2s(smem + pg.stage_off + (size_t)stage * pg.stage_bytes, src, bytes, &bars->full[stage]);
+                src += bytes;
+                chunks -= c;
+                if (++stage == pg.n_stages) { stage = 0; phase ^= 1; }
+            }
+        }
+    }
+}
+
+// MMA warp: issue the ops of `reps` repetitions.
+__device__ __forceinline__ void chain_mma(const TcProgram& pg, ChainBars* bars, uint8_t* smem, uint32_t tmem_base, int reps) {
+    if ((threadIdx.x & 31) != 0) return;
+    const uint32_t smem_base = smem_u32(smem);
+    int stage = 0;
+    uint32_t phase = 0, ready_phase = 0;
+    bool phase_start = true;
+    for (int rep = 0; rep < reps; ++rep) {
+        for (int i = 0; i < pg.n_ops; ++i) {
+            const TcOp op = pg.op[i];
+            if (phase_start) {
+                mbar_wait(&bars->a_ready, ready_phase);
+                ready_phase ^= 1;
+                tc_fence_after_sync();
+                phase_start = false;
+            }
+            const int n = op.n;
+            const int total = op.a_chunks[0] + op.a_chunks[1];
+            const int kc = slab_chunks(pg.stage_bytes, n);
+            const uint32_t idesc = make_idesc_bf16(kTileRows, n);
+            const uint32_t b_lbo = (uint32_t)n * 16;
+            int in_slab = 0;
+            for (int c = 0; c < total; c += 2) {
+                if (in_slab == 0) {
+                    mbar_wait(&bars->full[stage], phase);
+                    tc_fence_after_sync();
+                }
+                const uint32_t a_addr = c < op.a_chunks[0] ? smem_base + op.a_off[0] + (uint32_t)c * kChunkBytes
+                                                           : smem_base + op.a_off[1] + (uint32_t)(c - op.a_chunks[0]) * kChunkBytes;
+                const uint32_t b_addr = smem_base + pg.stage_off + (uint32_t)stage * pg.stage_bytes + (uint32_t)in_slab * b_lbo;
+                umma_bf16(tmem_base + op.d_col, make_desc(a_addr, kChunkBytes, 128), make_desc(b_addr, b_lbo, 128), idesc,
+                          op.accumulate || c > 0);
+                in_slab += 2;
+                if (in_slab >= kc || c + 2 >= total) {
+                    umma_commit(&bars->empty[stage]);  // slab consumed once these MMAs retire
+                    in_slab = 0;
+                    if (++stage == pg.n_stages) { stage = 0; phase ^= 1; }
+                }
+            }
+            if (op.phase_end) {
+                umma_commit(&bars->acc_full);
+                phase_start = true;
+            }
+        }
+    }
+}
+
+// Epilogue-side handshakes.
+struct EpiSync {
+    ChainBars* bars;
+    uint32_t acc_phase;
+    __device__ __forceinline__ explicit EpiSync(ChainBars* b) : bars(b), acc_phase(0) {}
+    // wait for the accumulators of the next phase
+    __device__ __forceinline__ void wait_acc() {
+        mbar_wait(&bars->acc_full, acc_phase);
+        acc_phase ^= 1;
+        tc_fence_after_sync();
+    }
+    // A operands written (generic proxy) + accumulators consumed -> let the MMA warp go on
+    __device__ __forceinline__ void release() {
+        fence_proxy_async_smem();
+        tc_fence_before_sync();
+        mbar_arrive(&bars->a_ready);
+    }
+};
+
+// Row / column ownership of an epilogue thread: TMEM lane quadrant = warp % 4, column group = warp / 4.
+__device__ __forceinline__ int epi_row() { return 32 * ((threadIdx.x >> 5) & 3) + (threadIdx.x & 31); }
+__device__ __forceinline__ int epi_group() { return (threadIdx.x >> 5) >> 2; }
+constexpr int kEpiGroups = kEpiWarps / 4;
+__device__ __forceinline__ uint32_t epi_taddr(uint32_t tmem_base, int col) {
+    return tmem_base + ((uint32_t)(32 * ((threadIdx.x >> 5) & 3)) << 16) + (uint32_t)col;
+}
+
+// ---------------------------------------------------------------------------------------------- weight images
+// One job packs a [n_pad x 8*k_chunks] bf16 image (chunk-major) from an fp32 matrix:
+//   image(n, k) = src[(n0 + n) * ld + col(k)]            (transposed = 0: N indexes src rows)
+//               = src[row(k) * ld + (n0 + n)]            (transposed = 1: N indexes src columns)
+// where k runs through up to three K segments; a segment maps K range [kstart, kstart + len) to source
+// indices src0 .. src0 + len - 1.  Everything else is zero.
+struct PackTcJob {
+    const float* src;
+    __nv_bfloat16* dst;
+    int ld, transposed;
+    int n0, n_valid, n_pad;
+    int k_chunks;
+    int nseg;
+    int seg_kstart[3], seg_len[3], seg_src0[3];
+};
+constexpr int kMaxPackTcJobs = 28;
+struct PackTcJobs {
+    PackTcJob j[kMaxPackTcJobs];
+    int n;
+};
+int launch_pack_tc(const PackTcJobs& jobs, cudaStream_t stream);
+
+}  // namespace tc
+}  // namespace drm

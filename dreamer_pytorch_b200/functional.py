@@ -16,6 +16,7 @@ import torch
 from torch.autograd.function import once_differentiable
 
 from . import _lib
+from .precision import get_precision
 from ._lib import MAXL
 
 RSSM_KEYS = _lib._RSSM_W  # order of the RSSM weight tensors in every Function signature
@@ -251,24 +252,28 @@ class RolloutFn(torch.autograd.Function):
 # ------------------------------------------------------------------------------------------------
 # batched MLP
 # ------------------------------------------------------------------------------------------------
-def _build_mlp_call(x0, x1, weights, M, training) -> _lib.drm_mlp_call:
+def _prec(mode):
+    return _lib.BF16 if (mode or get_precision()) == "bf16" else _lib.FP32
+
+
+def _build_mlp_call(x0, x1, weights, M, training, precision=None) -> _lib.drm_mlp_call:
     c = _lib.drm_mlp_call()
     k0 = x0.shape[1]
     k1 = x1.shape[1] if x1 is not None else 0
     _fill_mlp(c.mlp, weights, k0 + k1)
     c.M, c.k0, c.k1 = M, k0, k1
-    c.precision = _lib.FP32
+    c.precision = _prec(precision)
     c.training = 1 if training else 0
     c.x0, c.ld0 = _lib.ptr(x0), k0
     c.x1, c.ld1 = (_lib.ptr(x1), k1) if x1 is not None else (None, 0)
     return c
 
 
-def mlp_forward_raw(x0, x1, weights, training):
+def mlp_forward_raw(x0, x1, weights, training, precision=None):
     """Runs drm_mlp_fwd; returns (y [M,out], save tensor or None)."""
     lib = _lib.load()
     M = x0.shape[0]
-    c = _build_mlp_call(x0, x1, weights, M, training)
+    c = _build_mlp_call(x0, x1, weights, M, training, precision)
     dev = x0.device
     y = torch.empty(M, c.mlp.out_dim, dtype=torch.float32, device=dev)
     c.y = y.data_ptr()
@@ -283,13 +288,13 @@ def mlp_forward_raw(x0, x1, weights, training):
     return y, save
 
 
-def mlp_backward_raw(x0, x1, weights, save, dy, dy_scale=None, dx0=None, dx1=None, accumulate_dx=False,
+def mlp_backward_raw(x0, x1, weights, save, dy, dy_scale=None, dx0=None, dx1=None, accumulate_dx=False, precision="fp32",
                      want_wgrad=False):
     """Runs drm_mlp_bwd; returns the list of weight grads [dW0, db0, dW1, ...] (or None)."""
     lib = _lib.load()
     M = x0.shape[0]
     b = _lib.drm_mlp_bwd_call()
-    c = _build_mlp_call(x0, x1, weights, M, True)
+    c = _build_mlp_call(x0, x1, weights, M, True, precision)
     dev = x0.device
     ws = _buf(lib.drm_mlp_workspace_bytes(C.byref(c)), dev)
     c.workspace, c.workspace_bytes = ws.data_ptr(), ws.numel() * 4
