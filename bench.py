@@ -172,6 +172,9 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     lib = _lib.load()
+    from dreamer_pytorch_b200.precision import set_precision
+
+    set_precision(args.precision)
     w = dict(WORKLOADS[args.workload])
     if args.n_states:
         w["n_states"] = args.n_states

@@ -19,6 +19,7 @@ import torch
 
 from . import _lib, noise
 from .dropin.dense import mlp_weights
+from .precision import get_precision
 from .dropin.rnns import RSSMState, get_feat
 from .functional import (KLFn, RolloutCfg, _f32c, mlp_backward_raw, mlp_forward_raw, returns_loss_raw,
                          rollout_backward_raw, rollout_forward_raw)
@@ -46,12 +47,13 @@ class _ActorLossFn(torch.autograd.Function):
         x1 = t["deter"].view(H * N, D)
         # heads over all imagined states; hidden activations are kept: the actor path needs their
         # data-gradients, the value loss the value head's weight-gradients
-        reward, rsave = mlp_forward_raw(x0, x1, reward_w, training)
-        value, vsave = mlp_forward_raw(x0, x1, value_w, True)
-        pc, psave = (mlp_forward_raw(x0, x1, pcont_w, training) if pcont_w else (None, None))
+        prec = get_precision()
+        reward, rsave = mlp_forward_raw(x0, x1, reward_w, training, prec)
+        value, vsave = mlp_forward_raw(x0, x1, value_w, True, prec)
+        pc, psave = (mlp_forward_raw(x0, x1, pcont_w, training, prec) if pcont_w else (None, None))
         out = returns_loss_raw(reward.view(H, N), value.view(H, N), None if pc is None else pc.view(H, N), discount,
                                lambda_)
-        ctx.pack = (cfg, t, rssm, actor, save, reward_w, value_w, pcont_w, rsave, vsave, psave, out, x0, x1)
+        ctx.pack = (cfg, t, rssm, actor, save, reward_w, value_w, pcont_w, rsave, vsave, psave, out, x0, x1, prec)
         aux = (t["prior_mean"], t["prior_std"], t["prior_stoch"], t["deter"], t["action_out"], reward.view(H, N, 1),
                value.view(H, N, 1), out["returns"].view(H - 1, N, 1), out["disc"].view(H - 1, N, 1),
                out["losses"][1].clone(), out["d_value_pred"], vsave if vsave is not None else torch.empty(0))
@@ -60,16 +62,16 @@ class _ActorLossFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g_loss, *_):
-        (cfg, t, rssm, actor, save, reward_w, value_w, pcont_w, rsave, vsave, psave, out, x0, x1) = ctx.pack
+        (cfg, t, rssm, actor, save, reward_w, value_w, pcont_w, rsave, vsave, psave, out, x0, x1, prec) = ctx.pack
         H, N = cfg.steps, cfg.n
         g_loss = _f32c(g_loss)
         g_stoch = torch.empty_like(t["prior_stoch"])
         g_deter = torch.empty_like(t["deter"])
         gs, gd = g_stoch.view(H * N, -1), g_deter.view(H * N, -1)
-        mlp_backward_raw(x0, x1, reward_w, rsave, out["d_reward"].view(H * N, 1), g_loss, gs, gd, False, False)
-        mlp_backward_raw(x0, x1, value_w, vsave, out["d_value"].view(H * N, 1), g_loss, gs, gd, True, False)
+        mlp_backward_raw(x0, x1, reward_w, rsave, out["d_reward"].view(H * N, 1), g_loss, gs, gd, False, False, prec)
+        mlp_backward_raw(x0, x1, value_w, vsave, out["d_value"].view(H * N, 1), g_loss, gs, gd, True, False, prec)
         if pcont_w:
-            mlp_backward_raw(x0, x1, pcont_w, psave, out["d_pcont"].view(H * N, 1), g_loss, gs, gd, True, False)
+            mlp_backward_raw(x0, x1, pcont_w, psave, out["d_pcont"].view(H * N, 1), g_loss, gs, gd, True, False, prec)
         _, _, gactor = rollout_backward_raw(cfg, t, rssm, actor, save, dict(g_prior_stoch=g_stoch, g_deter=g_deter),
                                             want_actor=True)
         ctx.pack = None
@@ -83,15 +85,15 @@ class _ValueLossFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, pack, *value_w):
-        (x0, x1, vsave, d_value_pred, loss) = pack
-        ctx.pack = (x0, x1, vsave, d_value_pred, [_f32c(w) for w in value_w])
+        (x0, x1, vsave, d_value_pred, loss, prec) = pack
+        ctx.pack = (x0, x1, vsave, d_value_pred, [_f32c(w) for w in value_w], prec)
         return loss.clone()
 
     @staticmethod
     def backward(ctx, g_loss):
-        x0, x1, vsave, d_value_pred, value_w = ctx.pack
+        x0, x1, vsave, d_value_pred, value_w, prec = ctx.pack
         grads = mlp_backward_raw(x0, x1, value_w, vsave, d_value_pred.view(-1, 1), _f32c(g_loss), None, None, False,
-                                 True)
+                                 True, prec)
         ctx.pack = None
         return (None, *grads)
 
@@ -130,7 +132,7 @@ def imagination_losses(model, start_state: RSSMState, horizon: int, discount: fl
     (actor_loss, mean, std, st, dt, actions, reward, value, returns, disc, vloss, d_value_pred,
      vsave) = _ActorLossFn.apply(pack, *dec.weights())
     x0, x1 = st.view(horizon * N, -1), dt.view(horizon * N, -1)
-    value_loss = _ValueLossFn.apply((x0, x1, vsave, d_value_pred, vloss), *value_params)
+    value_loss = _ValueLossFn.apply((x0, x1, vsave, d_value_pred, vloss, get_precision()), *value_params)
     info = ImagInfo(RSSMState(mean, std, st, dt), actions, reward, value, returns, disc)
     return actor_loss, value_loss, info
 

@@ -350,6 +350,7 @@ using namespace drm;
 extern "C" {
 
 size_t drm_mlp_save_bytes(const drm_mlp_call* c) {
+    if (c && c->precision == DRM_BF16) return tc::mlp_tc_save_bytes(c) + 256;
     if (!c || c->mlp.n_linear < 2) return 16;
     return rup_sz((size_t)(c->mlp.n_linear - 1) * c->M * c->mlp.hidden * sizeof(float), 16) + 16;
 }
@@ -360,7 +361,7 @@ size_t drm_mlp_workspace_bytes(const drm_mlp_call* c) {
     size_t b = bwd_pack_floats(c) + dysave_floats(c);
     size_t bytes = (f > b ? f : b) * sizeof(float) + 256;
     if (c->precision == DRM_BF16) {
-        const size_t t = tc::mlp_tc_fwd_workspace_bytes(c) + 256;
+        const size_t t = tc::mlp_tc_workspace_bytes(c) + 256;
         if (t > bytes) bytes = t;
     }
     return bytes;
@@ -374,9 +375,9 @@ int drm_mlp_fwd(const drm_mlp_call* c, void* stream_) {
     const drm_mlp& m = c->mlp;
     DRM_REQUIRE(c->x0 && c->y && (c->k1 == 0 || c->x1), DRM_E_ARG, "null io pointer");
     DRM_REQUIRE(c->workspace && c->workspace_bytes >= drm_mlp_workspace_bytes(c), DRM_E_WORKSPACE, "workspace too small");
+    if (c->precision == DRM_BF16) return tc::mlp_tc_fwd(c, stream);
     const bool save = c->training && m.n_linear > 1;
     if (save) DRM_REQUIRE(c->save && c->save_bytes >= drm_mlp_save_bytes(c), DRM_E_WORKSPACE, "save buffer too small");
-    if (c->precision == DRM_BF16) return tc::mlp_tc_fwd(c, stream);
     MlpDev p; fill_common(p, c);
     Packer pk((float*)c->workspace);
     for (int l = 0; l < m.n_linear; ++l) {
@@ -417,6 +418,7 @@ int drm_mlp_bwd(const drm_mlp_bwd_call* bc, void* stream_) {
         }
     }
     if (c->M == 0) return DRM_OK;
+    if (c->precision == DRM_BF16) return tc::mlp_tc_bwd(bc, stream);
     MlpDev p; fill_common(p, c);
     Packer pk((float*)c->workspace);
     for (int l = 0; l < m.n_linear; ++l) {

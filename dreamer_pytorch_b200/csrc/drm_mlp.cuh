@@ -20,8 +20,10 @@ int launch_linear_dx(const float* dy, int M, int nout, const float* W, int w_ld,
 
 // bf16 tensor-core path (drm_mlp_tc.cu)
 namespace tc {
-size_t mlp_tc_fwd_workspace_bytes(const drm_mlp_call* c);
+size_t mlp_tc_workspace_bytes(const drm_mlp_call* c);
+size_t mlp_tc_save_bytes(const drm_mlp_call* c);
 int mlp_tc_fwd(const drm_mlp_call* c, cudaStream_t stream);
+int mlp_tc_bwd(const drm_mlp_bwd_call* bc, cudaStream_t stream);
 }  // namespace tc
 
 }  // namespace drm

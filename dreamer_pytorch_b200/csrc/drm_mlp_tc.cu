@@ -1,6 +1,7 @@
 // bf16 tensor-core (tcgen05) path of the batched MLP: DenseModel / ActionDecoder feed-forward stacks
 // (reference: dreamer/models/dense.py:28-43, dreamer/models/action.py:37-52).  Operands are bf16, the
 // accumulators fp32 in TMEM, bias / ELU / everything pointwise fp32.  See drm_tc_chain.cuh for the engine.
+#include <string.h>
 #include "drm_mlp.cuh"
 #include "drm_tc_chain.cuh"
 
@@ -43,29 +44,32 @@ int launch_pack_tc(const PackTcJobs& jobs, cudaStream_t stream) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// forward
+// device-side description
 // ------------------------------------------------------------------------------------------------
 struct MlpTcDev {
     int M, k0, k1, c0, c1, cin;  // input segments: widths and 8-wide chunk counts (cin = c0 + c1 rounded up to even)
-    int n_linear, hidden, ch, out_dim;
+    int n_linear, hidden, ch, out_dim, cout;  // ch / cout: chunks of a hidden layer / of the output (even)
     const float* x0; int64_t ld0;
     const float* x1; int64_t ld1;
     float* y;
     const float* b[DRM_MAX_LINEAR];
     const uint8_t* wstream;
-    __nv_bfloat16* save_h;  // [n_linear-1][M][ldh] or nullptr
-    int ldh;
-    uint32_t act_off;       // shared-memory offset of the activation buffer
+    __nv_bfloat16* sx;                    // TCM image of the input, cin chunks per tile (or nullptr)
+    __nv_bfloat16* sh[DRM_MAX_LINEAR];    // TCM images of the hidden activations, ch chunks per tile
+    uint32_t act_off;                     // shared-memory offset of the activation buffer
     // backward only
     const float* dy; const float* dy_scale;
     float* dx0; float* dx1; int accumulate_dx;
-    __nv_bfloat16* dysave[DRM_MAX_LINEAR];  // [M][ld_l] bf16 or nullptr
-    int ld_dys[DRM_MAX_LINEAR];
+    __nv_bfloat16* dys[DRM_MAX_LINEAR];   // TCM images of dY_l (ch chunks; cout for the last layer) or nullptr
+    float* db_last;                       // bias gradient of the last Linear, reduced in fp32 from the exact dY
     TcProgram pg;
 };
 
 __device__ __forceinline__ float elu_fast(float x) { return x > 0.f ? x : __expf(x) - 1.f; }
 
+// ------------------------------------------------------------------------------------------------
+// forward
+// ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kChainThreads, 1) mlp_fwd_tc_kernel(const __grid_constant__ MlpTcDev p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     ChainBars* bars = reinterpret_cast<ChainBars*>(smem);
@@ -84,7 +88,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_fwd_tc_kernel(const __gr
         const int last = p.n_linear - 1;
         for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
             const int row0 = tile * kTileRows;
-            // ---- stage the input tile: fp32 global -> bf16 chunk-major shared
+            // ---- stage the input tile: fp32 global -> bf16 chunk-major shared [+ TCM copy for the wgrad]
             for (int idx = threadIdx.x; idx < p.cin * kTileRows; idx += kEpiThreads) {
                 const int chunk = idx / kTileRows, r = idx - chunk * kTileRows;
                 const int grow = row0 + r;
@@ -104,17 +108,19 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_fwd_tc_kernel(const __gr
                     }
                 }
                 st_chunk_bf16(act + (size_t)idx * 16, v);
+                if (p.sx) st_chunk_bf16(p.sx + ((size_t)tile * p.cin * kTileRows + idx) * 8, v);
             }
             es.release();
+            const int grow = row0 + row;
+            const bool live = grow < p.M;
             for (int l = 0; l <= last; ++l) {
                 es.wait_acc();
                 const float* bias = p.b[l];
                 if (l < last) {
-                    // hidden layer: h = ELU(acc + b) -> bf16 A operand of the next layer (in place) [+ save]
+                    // hidden layer: h = ELU(acc + b) -> bf16 A operand of the next layer (in place) [+ TCM save]
                     const int per = (p.ch + kEpiGroups - 1) / kEpiGroups;
                     const int cbeg = grp * per, cend = min(p.ch, cbeg + per);
-                    __nv_bfloat16* sv = p.save_h ? p.save_h + (size_t)l * p.M * p.ldh : nullptr;
-                    const int grow = row0 + row;
+                    __nv_bfloat16* sv = p.sh[l];
                     for (int c = cbeg; c < cend; c += 2) {
                         float v0[8], v1[8];
                         tmem_ld8(epi_taddr(tmem_base, c * 8), v0);
@@ -124,30 +130,29 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_fwd_tc_kernel(const __gr
 #pragma unroll
                         for (int i = 0; i < 8; ++i) {
                             const int col = c * 8 + i;
-                            v0[i] = col < p.hidden ? elu_fast(v0[i] + __ldg(bias + col)) : 0.f;
+                            v0[i] = (live && col < p.hidden) ? elu_fast(v0[i] + __ldg(bias + col)) : 0.f;
                         }
                         st_chunk_bf16(act + ((size_t)c * kTileRows + row) * 16, v0);
-                        if (sv && grow < p.M) st_chunk_bf16(sv + (size_t)grow * p.ldh + c * 8, v0);
+                        if (sv) st_chunk_bf16(tcm_at(sv, p.ch, tile, c, row), v0);
                         if (two) {
 #pragma unroll
                             for (int i = 0; i < 8; ++i) {
                                 const int col = c * 8 + 8 + i;
-                                v1[i] = col < p.hidden ? elu_fast(v1[i] + __ldg(bias + col)) : 0.f;
+                                v1[i] = (live && col < p.hidden) ? elu_fast(v1[i] + __ldg(bias + col)) : 0.f;
                             }
                             st_chunk_bf16(act + ((size_t)(c + 1) * kTileRows + row) * 16, v1);
-                            if (sv && grow < p.M) st_chunk_bf16(sv + (size_t)grow * p.ldh + c * 8 + 8, v1);
+                            if (sv) st_chunk_bf16(tcm_at(sv, p.ch, tile, c + 1, row), v1);
                         }
                     }
                     es.release();
                 } else {
                     // output layer: y = acc + b (fp32, row-major)
                     const int oc = (p.out_dim + 7) / 8;
-                    const int grow = row0 + row;
                     for (int c = grp; c < oc; c += kEpiGroups) {
                         float v[8];
                         tmem_ld8(epi_taddr(tmem_base, c * 8), v);
                         tmem_ld_wait();
-                        if (grow < p.M) {
+                        if (live) {
 #pragma unroll
                             for (int i = 0; i < 8; ++i) {
                                 const int col = c * 8 + i;
@@ -156,6 +161,101 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_fwd_tc_kernel(const __gr
                         }
                     }
                     // the next tile's input staging is followed by release(), which also covers these loads
+                }
+            }
+        }
+    }
+    chain_teardown(tmem_base);
+}
+
+// ------------------------------------------------------------------------------------------------
+// backward: data gradients.  dH_{l-1} = (dH_l . W_l) * ELU'(h_{l-1}), dX = dH_0 . W_0; every dH_l is also
+// written to global memory as a TCM image for the weight-gradient GEMMs.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kChainThreads, 1) mlp_bwd_tc_kernel(const __grid_constant__ MlpTcDev p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    ChainBars* bars = reinterpret_cast<ChainBars*>(smem);
+    const uint32_t tmem_base = chain_setup(bars, p.pg);
+    const int warp = threadIdx.x >> 5;
+    const int tiles = (p.M + kTileRows - 1) / kTileRows;
+    const int reps = blockIdx.x < tiles ? (tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    if (warp == kEpiWarps) {
+        chain_producer(p.pg, bars, smem, p.wstream, reps);
+    } else if (warp == kEpiWarps + 1) {
+        chain_mma(p.pg, bars, smem, tmem_base, reps);
+    } else {
+        EpiSync es(bars);
+        uint8_t* act = smem + p.act_off;
+        const int row = epi_row(), grp = epi_group();
+        const int last = p.n_linear - 1;
+        const float scale = p.dy_scale ? __ldg(p.dy_scale) : 1.f;
+        const bool want_dx = p.dx0 != nullptr || p.dx1 != nullptr;
+        for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+            const int row0 = tile * kTileRows;
+            // ---- stage dY of the last Linear (scaled) as the first A operand [+ TCM copy for its wgrad]
+            for (int idx = threadIdx.x; idx < p.cout * kTileRows; idx += kEpiThreads) {
+                const int chunk = idx / kTileRows, r = idx - chunk * kTileRows;
+                const int grow = row0 + r;
+                float v[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int col = chunk * 8 + i;
+                    v[i] = (grow < p.M && col < p.out_dim) ? p.dy[(size_t)grow * p.out_dim + col] * scale : 0.f;
+                }
+                st_chunk_bf16(act + (size_t)idx * 16, v);
+                if (p.dys[last]) st_chunk_bf16(p.dys[last] + ((size_t)tile * p.cout * kTileRows + idx) * 8, v);
+                if (p.db_last && chunk * 8 < p.out_dim) {
+                    // a warp holds 32 consecutive rows of this chunk: fp32 column sums, one atomic per column
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const float s = warp_sum(v[i]);
+                        if ((threadIdx.x & 31) == 0 && chunk * 8 + i < p.out_dim) atomicAdd(p.db_last + chunk * 8 + i, s);
+                    }
+                }
+            }
+            es.release();
+            const int grow = row0 + row;
+            const bool live = grow < p.M;
+            for (int l = last; l >= 1; --l) {
+                es.wait_acc();
+                const int per = (p.ch + kEpiGroups - 1) / kEpiGroups;
+                const int cbeg = grp * per, cend = min(p.ch, cbeg + per);
+                const __nv_bfloat16* hs = p.sh[l - 1];
+                __nv_bfloat16* dsv = p.dys[l - 1];
+                for (int c = cbeg; c < cend; ++c) {
+                    float v[8], h[8];
+                    tmem_ld8(epi_taddr(tmem_base, c * 8), v);
+                    ld_chunk_bf16(tcm_at(hs, p.ch, tile, c, row), h);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int col = c * 8 + i;
+                        v[i] = (live && col < p.hidden) ? v[i] * (h[i] > 0.f ? 1.f : h[i] + 1.f) : 0.f;
+                    }
+                    st_chunk_bf16(act + ((size_t)c * kTileRows + row) * 16, v);
+                    if (dsv) st_chunk_bf16(tcm_at(dsv, p.ch, tile, c, row), v);
+                }
+                if (l > 1 || want_dx) es.release();
+            }
+            if (want_dx) {
+                es.wait_acc();
+                const int nin = p.k0 + p.k1;
+                const int cin = (nin + 7) / 8;
+                for (int c = grp; c < cin; c += kEpiGroups) {
+                    float v[8];
+                    tmem_ld8(epi_taddr(tmem_base, c * 8), v);
+                    tmem_ld_wait();
+                    if (live) {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int col = c * 8 + i;
+                            if (col >= nin) continue;
+                            float* dst;
+                            if (col < p.k0) { if (!p.dx0) continue; dst = p.dx0 + (size_t)grow * p.ld0 + col; }
+                            else { if (!p.dx1) continue; dst = p.dx1 + (size_t)grow * p.ld1 + (col - p.k0); }
+                            *dst = p.accumulate_dx ? *dst + v[i] : v[i];
+                        }
+                    }
                 }
             }
         }
@@ -177,60 +277,59 @@ struct MlpTcPlan {
     PackTcJobs jobs;
     size_t wbytes;
     size_t smem_bytes;
+    int tiles;
 };
 
-// Lays out the forward program, its weight images (at wbase, may be null for sizing) and shared memory.
-static int plan_fwd(const drm_mlp_call* c, uint8_t* wbase, MlpTcPlan& pl) {
+static int plan_dims(const drm_mlp_call* c, MlpTcPlan& pl) {
     const drm_mlp& m = c->mlp;
     MlpTcDev& d = pl.dev;
     memset(&d, 0, sizeof(d));
     d.M = c->M; d.k0 = c->k0; d.k1 = c->k1;
     d.c0 = (c->k0 + 7) / 8; d.c1 = (c->k1 + 7) / 8; d.cin = rup(d.c0 + d.c1, 2);
     d.n_linear = m.n_linear; d.hidden = m.n_linear > 1 ? m.hidden : 0; d.ch = rup((d.hidden + 7) / 8, 2);
-    d.out_dim = m.out_dim;
-    d.ldh = rup(d.hidden > 0 ? d.hidden : 8, 8);
-    DRM_REQUIRE(d.ch * 8 <= 512 && rup(m.out_dim, 16) <= 512, DRM_E_SHAPE, "layer wider than 512 is not supported by the bf16 path");
-    TcProgram& pg = pl.dev.pg;
-    pg.n_ops = 0; pg.n_phases = m.n_linear;
+    d.out_dim = m.out_dim; d.cout = rup((m.out_dim + 7) / 8, 2);
+    pl.tiles = (c->M + kTileRows - 1) / kTileRows;
+    DRM_REQUIRE(d.ch * 8 <= 512 && rup(m.out_dim, 16) <= 512 && rup(m.in_dim, 16) <= 512, DRM_E_SHAPE,
+                "layer wider than 512 is not supported by the bf16 path");
+    pl.dev.pg.n_ops = 0;
     pl.jobs.n = 0;
-    size_t woff = 0;
-    for (int l = 0; l < m.n_linear; ++l) {
-        const bool lastl = l == m.n_linear - 1;
-        const int nout = lastl ? m.out_dim : m.hidden;
-        const int npad = lastl ? rup(nout, 16) : d.ch * 8;
-        const int kchunks = l == 0 ? d.cin : d.ch;
-        int part[2];
-        const int np = n_parts(npad, part);
-        int n0 = 0;
-        for (int q = 0; q < np; ++q) {
-            DRM_REQUIRE(pg.n_ops < kMaxOps && pl.jobs.n < kMaxPackTcJobs, DRM_E_SHAPE, "MLP too deep for the bf16 path");
-            TcOp& op = pg.op[pg.n_ops++];
-            op.a_off[0] = 0; op.a_off[1] = 0;  // patched below once act_off is known
-            op.a_chunks[0] = (uint16_t)kchunks; op.a_chunks[1] = 0;
-            op.n = (uint16_t)part[q]; op.d_col = (uint16_t)n0; op.accumulate = 0;
-            op.phase_end = (q == np - 1) ? 1 : 0;
-            PackTcJob& j = pl.jobs.j[pl.jobs.n++];
-            j.src = m.W[l]; j.dst = wbase ? reinterpret_cast<__nv_bfloat16*>(wbase + woff) : nullptr;
-            j.ld = l == 0 ? m.in_dim : m.hidden; j.transposed = 0;
-            j.n0 = n0; j.n_valid = nout - n0 < part[q] ? (nout - n0 > 0 ? nout - n0 : 0) : part[q]; j.n_pad = part[q];
-            j.k_chunks = kchunks;
-            if (l == 0) {
-                j.nseg = c->k1 > 0 ? 2 : 1;
-                j.seg_kstart[0] = 0; j.seg_len[0] = c->k0; j.seg_src0[0] = 0;
-                j.seg_kstart[1] = d.c0 * 8; j.seg_len[1] = c->k1; j.seg_src0[1] = c->k0;
-            } else {
-                j.nseg = 1; j.seg_kstart[0] = 0; j.seg_len[0] = m.hidden; j.seg_src0[0] = 0;
-            }
-            woff += (size_t)kchunks * part[q] * 16;
-            n0 += part[q];
-        }
+    pl.wbytes = 0;
+    return DRM_OK;
+}
+
+// Appends one GEMM phase  D[128 x npad] = A(act buffer, kchunks) * image^T  and its weight-image jobs.
+static int add_phase(MlpTcPlan& pl, uint8_t* wbase, int kchunks, int npad, const float* src, int ld, int transposed,
+                     int n_valid_total, int nseg, const int* seg_kstart, const int* seg_len, const int* seg_src0) {
+    TcProgram& pg = pl.dev.pg;
+    int part[2];
+    const int np = n_parts(npad, part);
+    int n0 = 0;
+    for (int q = 0; q < np; ++q) {
+        DRM_REQUIRE(pg.n_ops < kMaxOps && pl.jobs.n < kMaxPackTcJobs, DRM_E_SHAPE, "MLP too deep for the bf16 path");
+        TcOp& op = pg.op[pg.n_ops++];
+        op.a_off[0] = 0; op.a_off[1] = 0;  // patched once act_off is known
+        op.a_chunks[0] = (uint16_t)kchunks; op.a_chunks[1] = 0;
+        op.n = (uint16_t)part[q]; op.d_col = (uint16_t)n0; op.accumulate = 0;
+        op.phase_end = (q == np - 1) ? 1 : 0;
+        PackTcJob& j = pl.jobs.j[pl.jobs.n++];
+        j.src = src; j.dst = wbase ? reinterpret_cast<__nv_bfloat16*>(wbase + pl.wbytes) : nullptr;
+        j.ld = ld; j.transposed = transposed;
+        int nv = n_valid_total - n0; if (nv < 0) nv = 0; if (nv > part[q]) nv = part[q];
+        j.n0 = n0; j.n_valid = nv; j.n_pad = part[q];
+        j.k_chunks = kchunks; j.nseg = nseg;
+        for (int s = 0; s < nseg; ++s) { j.seg_kstart[s] = seg_kstart[s]; j.seg_len[s] = seg_len[s]; j.seg_src0[s] = seg_src0[s]; }
+        pl.wbytes += (size_t)kchunks * part[q] * 16;
+        n0 += part[q];
     }
-    pl.wbytes = woff;
-    // shared memory: [bars 256 B][pad to 1024][activation buffer][stages]
-    const int act_chunks = d.cin > d.ch ? d.cin : d.ch;
+    pg.n_phases++;
+    return DRM_OK;
+}
+
+static int finish_plan(MlpTcPlan& pl, int act_chunks) {
+    MlpTcDev& d = pl.dev;
+    TcProgram& pg = d.pg;
     d.act_off = 1024;
-    const size_t act_bytes = (size_t)act_chunks * kChunkBytes;
-    pg.stage_off = (uint32_t)rup_sz(d.act_off + act_bytes, 1024);
+    pg.stage_off = (uint32_t)rup_sz(d.act_off + (size_t)act_chunks * kChunkBytes, 1024);
     pg.stage_bytes = 32 * 1024;
     int stages = (int)(((size_t)kMaxSmem - pg.stage_off) / pg.stage_bytes);
     if (stages > 4) stages = 4;
@@ -241,10 +340,75 @@ static int plan_fwd(const drm_mlp_call* c, uint8_t* wbase, MlpTcPlan& pl) {
     return DRM_OK;
 }
 
-size_t mlp_tc_fwd_workspace_bytes(const drm_mlp_call* c) {
+static int plan_fwd(const drm_mlp_call* c, uint8_t* wbase, MlpTcPlan& pl) {
+    const drm_mlp& m = c->mlp;
+    int rc = plan_dims(c, pl); if (rc) return rc;
+    MlpTcDev& d = pl.dev;
+    d.pg.n_phases = 0;
+    for (int l = 0; l < m.n_linear; ++l) {
+        const bool lastl = l == m.n_linear - 1;
+        const int nout = lastl ? m.out_dim : m.hidden;
+        const int npad = lastl ? rup(nout, 16) : d.ch * 8;
+        if (l == 0) {
+            const int ks[2] = {0, d.c0 * 8}, len[2] = {c->k0, c->k1}, s0[2] = {0, c->k0};
+            rc = add_phase(pl, wbase, d.cin, npad, m.W[0], m.in_dim, 0, nout, c->k1 > 0 ? 2 : 1, ks, len, s0);
+        } else {
+            const int ks[1] = {0}, len[1] = {m.hidden}, s0[1] = {0};
+            rc = add_phase(pl, wbase, d.ch, npad, m.W[l], m.hidden, 0, nout, 1, ks, len, s0);
+        }
+        if (rc) return rc;
+    }
+    return finish_plan(pl, d.cin > d.ch ? d.cin : d.ch);
+}
+
+static int plan_bwd(const drm_mlp_call* c, bool want_dx, uint8_t* wbase, MlpTcPlan& pl) {
+    const drm_mlp& m = c->mlp;
+    int rc = plan_dims(c, pl); if (rc) return rc;
+    MlpTcDev& d = pl.dev;
+    d.pg.n_phases = 0;
+    const int last = m.n_linear - 1;
+    for (int l = last; l >= 1; --l) {
+        const int nout = l == last ? m.out_dim : m.hidden;
+        const int ks[1] = {0}, len[1] = {nout}, s0[1] = {0};
+        rc = add_phase(pl, wbase, l == last ? d.cout : d.ch, d.ch * 8, m.W[l], m.hidden, 1, m.hidden, 1, ks, len, s0);
+        if (rc) return rc;
+    }
+    if (want_dx) {
+        const int rows0 = m.n_linear == 1 ? m.out_dim : m.hidden;
+        const int ks[1] = {0}, len[1] = {rows0}, s0[1] = {0};
+        rc = add_phase(pl, wbase, m.n_linear == 1 ? d.cout : d.ch, rup(m.in_dim, 16), m.W[0], m.in_dim, 1, m.in_dim, 1, ks, len, s0);
+        if (rc) return rc;
+    }
+    return finish_plan(pl, d.cout > d.ch ? d.cout : d.ch);
+}
+
+// save buffer of the bf16 path: [input image: tiles x cin][hidden images: (n_linear-1) x tiles x ch] chunks
+size_t mlp_tc_save_bytes(const drm_mlp_call* c) {
     MlpTcPlan pl;
-    if (plan_fwd(c, nullptr, pl) != DRM_OK) return 0;
-    return rup_sz(pl.wbytes, 256) + 256;
+    if (plan_dims(c, pl) != DRM_OK) return 0;
+    return tcm_bytes(pl.tiles, pl.dev.cin) + (size_t)(c->mlp.n_linear - 1) * tcm_bytes(pl.tiles, pl.dev.ch) + 256;
+}
+
+static size_t dys_bytes(const MlpTcPlan& pl, int n_linear) {
+    return (size_t)(n_linear - 1) * tcm_bytes(pl.tiles, pl.dev.ch) + tcm_bytes(pl.tiles, pl.dev.cout);
+}
+
+size_t mlp_tc_workspace_bytes(const drm_mlp_call* c) {
+    MlpTcPlan pf, pb;
+    if (plan_fwd(c, nullptr, pf) != DRM_OK || plan_bwd(c, true, nullptr, pb) != DRM_OK) return 0;
+    const size_t f = rup_sz(pf.wbytes, 256);
+    const size_t b = rup_sz(pb.wbytes, 256) + dys_bytes(pb, c->mlp.n_linear);
+    return (f > b ? f : b) + 512;
+}
+
+static void carve_save(const drm_mlp_call* c, const MlpTcPlan& pl, MlpTcDev& d) {
+    uint8_t* s = reinterpret_cast<uint8_t*>(rup_sz((size_t)c->save, 256));
+    d.sx = reinterpret_cast<__nv_bfloat16*>(s);
+    s += tcm_bytes(pl.tiles, d.cin);
+    for (int l = 0; l < c->mlp.n_linear - 1; ++l) {
+        d.sh[l] = reinterpret_cast<__nv_bfloat16*>(s);
+        s += tcm_bytes(pl.tiles, d.ch);
+    }
 }
 
 int mlp_tc_fwd(const drm_mlp_call* c, cudaStream_t stream) {
@@ -252,20 +416,79 @@ int mlp_tc_fwd(const drm_mlp_call* c, cudaStream_t stream) {
     MlpTcPlan pl;
     uint8_t* ws = reinterpret_cast<uint8_t*>(rup_sz((size_t)c->workspace, 256));
     int rc = plan_fwd(c, ws, pl); if (rc) return rc;
-    DRM_REQUIRE(c->workspace_bytes >= mlp_tc_fwd_workspace_bytes(c), DRM_E_WORKSPACE, "workspace too small (bf16 path)");
+    DRM_REQUIRE(c->workspace_bytes >= mlp_tc_workspace_bytes(c), DRM_E_WORKSPACE, "workspace too small (bf16 path)");
     MlpTcDev& d = pl.dev;
     d.x0 = c->x0; d.ld0 = c->ld0; d.x1 = c->x1; d.ld1 = c->ld1; d.y = c->y;
     for (int l = 0; l < m.n_linear; ++l) d.b[l] = m.b[l];
     d.wstream = ws;
-    const bool save = c->training && m.n_linear > 1;
-    d.save_h = save ? reinterpret_cast<__nv_bfloat16*>(c->save) : nullptr;
+    if (c->training) {
+        DRM_REQUIRE(c->save && c->save_bytes >= mlp_tc_save_bytes(c), DRM_E_WORKSPACE, "save buffer too small (bf16 path)");
+        carve_save(c, pl, d);
+    }
     rc = launch_pack_tc(pl.jobs, stream); if (rc) return rc;
-    const int tiles = (c->M + kTileRows - 1) / kTileRows;
-    const int grid = tiles < kNumSM ? tiles : kNumSM;
+    const int grid = pl.tiles < kNumSM ? pl.tiles : kNumSM;
     DRM_CUDA_OK(cudaFuncSetAttribute(mlp_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
     ProfScope prof(PROF_MLP_FWD, stream);
     mlp_fwd_tc_kernel<<<grid, kChainThreads, pl.smem_bytes, stream>>>(d);
     DRM_CUDA_OK(cudaGetLastError());
+    return DRM_OK;
+}
+
+int mlp_tc_bwd(const drm_mlp_bwd_call* bc, cudaStream_t stream) {
+    const drm_mlp_call* c = &bc->fwd;
+    const drm_mlp& m = c->mlp;
+    const int last = m.n_linear - 1;
+    const bool want_dx = bc->dx0 || bc->dx1;
+    MlpTcPlan pl;
+    uint8_t* ws = reinterpret_cast<uint8_t*>(rup_sz((size_t)c->workspace, 256));
+    int rc = plan_bwd(c, want_dx, ws, pl); if (rc) return rc;
+    DRM_REQUIRE(c->workspace_bytes >= mlp_tc_workspace_bytes(c), DRM_E_WORKSPACE, "workspace too small (bf16 path)");
+    DRM_REQUIRE(c->save && c->save_bytes >= mlp_tc_save_bytes(c), DRM_E_WORKSPACE, "save buffer missing (bf16 path)");
+    MlpTcDev& d = pl.dev;
+    d.ld0 = c->ld0; d.ld1 = c->ld1;
+    d.wstream = ws;
+    carve_save(c, pl, d);
+    d.dy = bc->dy; d.dy_scale = bc->dy_scale; d.dx0 = bc->dx0; d.dx1 = bc->dx1; d.accumulate_dx = bc->accumulate_dx;
+    if (bc->want_wgrad) {
+        d.db_last = bc->grad.db[last];
+        uint8_t* s = ws + rup_sz(pl.wbytes, 256);
+        for (int l = 0; l <= last; ++l) {
+            d.dys[l] = reinterpret_cast<__nv_bfloat16*>(s);
+            s += tcm_bytes(pl.tiles, l == last ? d.cout : d.ch);
+        }
+    }
+    if (!want_dx && !bc->want_wgrad) return DRM_OK;
+    rc = launch_pack_tc(pl.jobs, stream); if (rc) return rc;
+    {
+        const int grid = pl.tiles < kNumSM ? pl.tiles : kNumSM;
+        DRM_CUDA_OK(cudaFuncSetAttribute(mlp_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
+        ProfScope prof(PROF_MLP_BWD, stream);
+        mlp_bwd_tc_kernel<<<grid, kChainThreads, pl.smem_bytes, stream>>>(d);
+        DRM_CUDA_OK(cudaGetLastError());
+    }
+    if (bc->want_wgrad) {
+        WgParams w;
+        memset(&w, 0, sizeof(w));
+        w.n_layers = m.n_linear; w.row_tiles = pl.tiles;
+        for (int l = 0; l <= last; ++l) {
+            WgLayer& L = w.L[l];
+            L.dy = d.dys[l]; L.dy_cpt = l == last ? d.cout : d.ch;
+            L.nout = l == last ? m.out_dim : m.hidden;
+            if (l == 0) {
+                L.nseg = c->k1 > 0 ? 2 : 1;
+                L.seg[0] = WgSeg{d.sx, d.cin, 0, d.c0, 0, c->k0};
+                L.seg[1] = WgSeg{d.sx, d.cin, d.c0, d.c1, c->k0, c->k1};
+                L.ld_dw = m.in_dim;
+            } else {
+                L.nseg = 1;
+                L.seg[0] = WgSeg{d.sh[l - 1], d.ch, 0, (m.hidden + 7) / 8, 0, m.hidden};
+                L.ld_dw = m.hidden;
+            }
+            L.dW = bc->grad.dW[l]; L.db = l == last ? nullptr : bc->grad.db[l];
+        }
+        wgrad_tc_plan(w);
+        rc = launch_wgrad_tc(w, stream); if (rc) return rc;
+    }
     return DRM_OK;
 }
 

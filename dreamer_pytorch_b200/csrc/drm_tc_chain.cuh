@@ -195,6 +195,59 @@ __device__ __forceinline__ uint32_t epi_taddr(uint32_t tmem_base, int col) {
     return tmem_base + ((uint32_t)(32 * ((threadIdx.x >> 5) & 3)) << 16) + (uint32_t)col;
 }
 
+// ---------------------------------------------------------------------------------------------- TCM images
+// "Tiled chunk-major" global image of a [rows x F] bf16 matrix: [tile of 128 rows][chunk of 8 features][128][8].
+// It is byte-for-byte the shared-memory A-operand image of each row tile, so the epilogue threads store
+// it fully coalesced (32 lanes = 32 consecutive rows = 512 contiguous bytes), the backward kernels read it
+// back the same way, and the weight-gradient kernel pulls whole tiles with 1-D bulk copies and uses them
+// directly as MN-major tcgen05 operands (features = M/N, rows = K).  Rows past the end are zero.
+__host__ __device__ inline size_t tcm_bytes(size_t tiles, int chunks) { return tiles * (size_t)chunks * kChunkBytes; }
+__device__ __forceinline__ __nv_bfloat16* tcm_at(__nv_bfloat16* base, int chunks_per_tile, int tile, int chunk, int row) {
+    return base + (((size_t)tile * chunks_per_tile + chunk) * kTileRows + row) * 8;
+}
+__device__ __forceinline__ const __nv_bfloat16* tcm_at(const __nv_bfloat16* base, int chunks_per_tile, int tile, int chunk, int row) {
+    return base + (((size_t)tile * chunks_per_tile + chunk) * kTileRows + row) * 8;
+}
+__device__ __forceinline__ void ld_chunk_bf16(const __nv_bfloat16* src, float (&v)[8]) {
+    const uint4 q = *reinterpret_cast<const uint4*>(src);
+    const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        v[2 * i] = __uint_as_float(w[i] << 16);
+        v[2 * i + 1] = __uint_as_float(w[i] & 0xFFFF0000u);
+    }
+}
+
+// Weight-gradient GEMMs of a group of Linear layers in ONE launch (drm_wgrad_tc.cu):
+//   dW_l[n][col(f)] (+)= sum_rows dY_l[row][n] * X_l[row][f],   db_l[n] (+)= sum_rows dY_l[row][n]
+// dY_l and the (up to two) feature segments of X_l are TCM images over the same row tiles.
+struct WgSeg {
+    const __nv_bfloat16* base;  // TCM image
+    int cpt;                    // chunks per tile of that image
+    int chunk0, nchunks;        // chunk range used
+    int col0, kvalid;           // dW column of the segment's first feature; number of real features
+};
+struct WgLayer {
+    const __nv_bfloat16* dy;    // TCM image, dy_cpt chunks per tile
+    int dy_cpt, nout;
+    WgSeg seg[2];
+    int nseg;
+    float* dW; int ld_dw;
+    float* db;                  // may be null
+    int n_tiles_n;              // 128-feature tiles of nout
+    int n_parts, part_chunks;   // X feature chunks (incl. the ones chunk) split into parts of <= 32 chunks
+    int splits;                 // row-tile splits
+    int cta0;                   // first CTA of this layer
+};
+constexpr int kMaxWgLayers = 10;
+struct WgParams {
+    int n_layers, row_tiles, total_ctas;
+    WgLayer L[kMaxWgLayers];
+};
+// fills n_tiles_n / parts / splits / cta0 / total_ctas from the rest
+void wgrad_tc_plan(WgParams& w);
+int launch_wgrad_tc(const WgParams& w, cudaStream_t stream);
+
 // ---------------------------------------------------------------------------------------------- weight images
 // One job packs a [n_pad x 8*k_chunks] bf16 image (chunk-major) from an fp32 matrix:
 //   image(n, k) = src[(n0 + n) * ld + col(k)]            (transposed = 0: N indexes src rows)

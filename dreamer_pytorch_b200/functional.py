@@ -288,8 +288,8 @@ def mlp_forward_raw(x0, x1, weights, training, precision=None):
     return y, save
 
 
-def mlp_backward_raw(x0, x1, weights, save, dy, dy_scale=None, dx0=None, dx1=None, accumulate_dx=False, precision="fp32",
-                     want_wgrad=False):
+def mlp_backward_raw(x0, x1, weights, save, dy, dy_scale=None, dx0=None, dx1=None, accumulate_dx=False,
+                     want_wgrad=False, precision="fp32"):
     """Runs drm_mlp_bwd; returns the list of weight grads [dW0, db0, dW1, ...] (or None)."""
     lib = _lib.load()
     M = x0.shape[0]
@@ -326,7 +326,8 @@ class MlpFn(torch.autograd.Function):
         x1 = _f32c(x1)
         weights = [_f32c(w) for w in weights]
         training = any(ctx.needs_input_grad)
-        y, save = mlp_forward_raw(x0, x1, weights, training)
+        ctx.precision = get_precision()
+        y, save = mlp_forward_raw(x0, x1, weights, training, ctx.precision)
         ctx.save_for_backward(x0, x1, save, *weights)
         return y
 
@@ -339,7 +340,7 @@ class MlpFn(torch.autograd.Function):
         dx0 = torch.empty_like(x0) if need[0] else None
         dx1 = torch.empty_like(x1) if (x1 is not None and need[1]) else None
         want_w = any(need[2:])
-        grads = mlp_backward_raw(x0, x1, weights, save, dy, None, dx0, dx1, False, want_w)
+        grads = mlp_backward_raw(x0, x1, weights, save, dy, None, dx0, dx1, False, want_w, ctx.precision)
         res = [dx0, dx1] + (grads if grads is not None else [None] * len(weights))
         for i in range(len(res)):
             if not need[i]:

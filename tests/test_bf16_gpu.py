@@ -54,3 +54,46 @@ def test_mlp_fwd_bf16(cuda, M, k0, k1, hidden, out, layers):
     err = rel_err(y, ry)
     assert err < BF16_TOL, err
     assert err > 0  # bf16 operands: an exact match would mean the tensor-core path did not run
+
+
+@pytest.mark.parametrize("M,k0,k1,hidden,out,layers", MLP_SHAPES)
+def test_mlp_fwd_bwd_bf16(cuda, M, k0, k1, hidden, out, layers):
+    """Forward, data gradients and weight gradients (tcgen05 wgrad kernel) through MlpFn."""
+    from dreamer_pytorch_b200.functional import MlpFn
+    from dreamer_pytorch_b200.precision import precision
+
+    ws, x0, x1, gy = _mlp_case(M, k0, k1, hidden, out, layers)
+    r_in = [t.double().requires_grad_(True) for t in ([x0] + ([x1] if k1 else []) + ws)]
+    ry = _mlp_ref(r_in[0], r_in[1] if k1 else None, r_in[(2 if k1 else 1):], layers)
+    rg = torch.autograd.grad(ry, r_in, gy.double())
+    c_in = [t.to(cuda).requires_grad_(True) for t in ([x0] + ([x1] if k1 else []) + ws)]
+    with precision("bf16"):
+        cy = MlpFn.apply(c_in[0], c_in[1] if k1 else None, *c_in[(2 if k1 else 1):])
+        cg = torch.autograd.grad(cy, c_in, gy.to(cuda))
+    torch.cuda.synchronize()
+    assert rel_err(cy, ry) < BF16_TOL
+    names = ["dx0"] + (["dx1"] if k1 else []) + [f"{'dW' if i % 2 == 0 else 'db'}{i // 2}" for i in range(len(ws))]
+    # a gradient summed over fewer rows than one 128-row tile has no averaging of the bf16 rounding of
+    # dY (2^-9 relative per element): allow 2x there; the contract (1e-2) is held at the real sizes
+    tol = BF16_TOL if M >= 128 else 2 * BF16_TOL
+    errs = {nm: rel_err(a, b) for nm, a, b in zip(names, cg, rg)}
+    assert max(errs.values()) < tol, errs
+
+
+def test_mlp_bf16_accumulate_and_frozen(cuda):
+    """dx accumulation (+=) and the frozen-weights variant (no wgrad) used by the actor path."""
+    from dreamer_pytorch_b200.functional import mlp_backward_raw, mlp_forward_raw
+
+    ws, x0, x1, gy = _mlp_case(300, 30, 200, 200, 1, 3)
+    cw = [w.to(cuda) for w in ws]
+    cx0, cx1 = x0.to(cuda), x1.to(cuda)
+    y, save = mlp_forward_raw(cx0, cx1, cw, True, "bf16")
+    dx0 = torch.ones_like(cx0)
+    dx1 = torch.ones_like(cx1)
+    scale = torch.tensor(0.5, device=cuda)
+    mlp_backward_raw(cx0, cx1, cw, save, gy.to(cuda), scale, dx0, dx1, True, False, "bf16")
+    r_in = [x0.double().requires_grad_(True), x1.double().requires_grad_(True)]
+    ry = _mlp_ref(r_in[0], r_in[1], [w.double() for w in ws], 3)
+    rg = torch.autograd.grad(ry, r_in, 0.5 * gy.double())
+    assert rel_err(dx0 - 1, rg[0]) < BF16_TOL
+    assert rel_err(dx1 - 1, rg[1]) < BF16_TOL
