@@ -20,12 +20,15 @@ __global__ void pack_tc_kernel(PackTcJobs jobs) {
         const int chunk = (i >> 3) / j.n_pad;
         const int k = chunk * 8 + kk;
         float v = 0.f;
-        if (n < j.n_valid) {
+        int ns = -1;
+        if (n < j.n_valid) ns = j.n0 + n;
+        else if (n >= j.n2_start && n < j.n2_start + j.n2_valid) ns = j.n2_src0 + (n - j.n2_start);
+        if (ns >= 0) {
             for (int s = 0; s < j.nseg; ++s) {
                 const int d = k - j.seg_kstart[s];
                 if (d >= 0 && d < j.seg_len[s]) {
                     const int ks = j.seg_src0[s] + d;
-                    v = j.transposed ? j.src[(size_t)ks * j.ld + j.n0 + n] : j.src[(size_t)(j.n0 + n) * j.ld + ks];
+                    v = j.transposed ? j.src[(size_t)ks * j.ld + ns] : j.src[(size_t)ns * j.ld + ks];
                 }
             }
         }
@@ -65,7 +68,6 @@ struct MlpTcDev {
     TcProgram pg;
 };
 
-__device__ __forceinline__ float elu_fast(float x) { return x > 0.f ? x : __expf(x) - 1.f; }
 
 // ------------------------------------------------------------------------------------------------
 // forward
@@ -316,6 +318,7 @@ static int add_phase(MlpTcPlan& pl, uint8_t* wbase, int kchunks, int npad, const
         j.ld = ld; j.transposed = transposed;
         int nv = n_valid_total - n0; if (nv < 0) nv = 0; if (nv > part[q]) nv = part[q];
         j.n0 = n0; j.n_valid = nv; j.n_pad = part[q];
+        j.n2_start = 0; j.n2_valid = 0; j.n2_src0 = 0;
         j.k_chunks = kchunks; j.nseg = nseg;
         for (int s = 0; s < nseg; ++s) { j.seg_kstart[s] = seg_kstart[s]; j.seg_len[s] = seg_len[s]; j.seg_src0[s] = seg_src0[s]; }
         pl.wbytes += (size_t)kchunks * part[q] * 16;

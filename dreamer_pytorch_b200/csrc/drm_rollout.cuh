@@ -66,6 +66,16 @@ __host__ __device__ inline int bwd_smem_floats_per_row(const RollDev& p) {
     return p.S4 + p.D + p.MS4 + p.Hd + p.D + p.U + p.AS4 + p.Aout4;
 }
 
+// bf16 tensor-core path (drm_rollout_tc.cu): POLICY mode only
+namespace tc {
+int rollout_tc_supported(const drm_rollout* r);
+size_t rollout_tc_save_bytes(const drm_rollout* r);
+size_t rollout_tc_fwd_workspace_bytes(const drm_rollout* r);
+size_t rollout_tc_bwd_workspace_bytes(const drm_rollout* r);
+int rollout_tc_fwd(const drm_rollout* r, cudaStream_t stream);
+int rollout_tc_bwd(const drm_rollout* r, const drm_rollout_grad* g, cudaStream_t stream);
+}  // namespace tc
+
 int launch_rollout_fwd(const RollDev& p, cudaStream_t stream);
 int launch_rollout_bwd(const RollDev& p, cudaStream_t stream);
 

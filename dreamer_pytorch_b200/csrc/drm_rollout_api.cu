@@ -12,7 +12,7 @@ static int validate(const drm_rollout* r) {
     DRM_REQUIRE(r->steps >= 1 && r->n >= 1, DRM_E_SHAPE, "steps and n must be positive");
     DRM_REQUIRE(w.A >= 1 && w.S >= 1 && w.D >= 4 && w.Hd >= 4, DRM_E_SHAPE, "bad RSSM sizes");
     DRM_REQUIRE(w.D % 4 == 0 && w.Hd % 4 == 0, DRM_E_SHAPE, "deter and hidden sizes must be multiples of 4");
-    DRM_REQUIRE(r->precision == DRM_FP32, DRM_E_SHAPE, "only DRM_FP32 is implemented for the rollouts");
+    DRM_REQUIRE(r->precision == DRM_FP32 || r->precision == DRM_BF16, DRM_E_SHAPE, "unknown precision");
     DRM_REQUIRE(w.W_in && w.b_in && w.W_ih && w.W_hh && w.b_ih && w.b_hh && w.W_p1 && w.b_p1 && w.W_p2 && w.b_p2,
                 DRM_E_ARG, "null transition weight");
     DRM_REQUIRE(r->start_stoch && r->start_deter && r->eps_prior, DRM_E_ARG, "null input");
@@ -180,6 +180,10 @@ static size_t bwd_ws_floats(const drm_rollout* r, const RollDev& d) {
     return f;
 }
 
+// The bf16 request is honoured where the tensor-core path exists (imagination rollouts of supported
+// shapes); every other rollout runs the fp32 kernels, which satisfy the bf16 tolerance a fortiori.
+static bool use_tc(const drm_rollout* r) { return r->precision == DRM_BF16 && tc::rollout_tc_supported(r); }
+
 }  // namespace drm
 
 using namespace drm;
@@ -188,12 +192,17 @@ extern "C" {
 
 size_t drm_rollout_save_bytes(const drm_rollout* r) {
     if (!r) return 0;
+    if (use_tc(r)) return tc::rollout_tc_save_bytes(r);
     RollDev d{}; dims(r, d);
     return carve_save(r, d, nullptr, nullptr) * sizeof(float) + 64;
 }
 
 size_t drm_rollout_workspace_bytes(const drm_rollout* r) {
     if (!r) return 0;
+    if (use_tc(r)) {
+        const size_t f = tc::rollout_tc_fwd_workspace_bytes(r), b = tc::rollout_tc_bwd_workspace_bytes(r);
+        return (f > b ? f : b) + 256;
+    }
     RollDev d{}; dims(r, d);
     const size_t f = fwd_ws_floats(r, d), b = bwd_ws_floats(r, d);
     return (f > b ? f : b) * sizeof(float) + 256;
@@ -203,6 +212,7 @@ int drm_rollout_fwd(const drm_rollout* r, void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     int rc = validate(r); if (rc) return rc;
     rc = check_device(); if (rc) return rc;
+    if (use_tc(r)) return tc::rollout_tc_fwd(r, stream);
     RollDev p{}; dims(r, p);
     DRM_REQUIRE(r->workspace && r->workspace_bytes >= fwd_ws_floats(r, p) * sizeof(float), DRM_E_WORKSPACE,
                 "workspace too small");
@@ -232,6 +242,7 @@ int drm_rollout_bwd(const drm_rollout* r, const drm_rollout_grad* g, void* strea
     int rc = validate(r); if (rc) return rc;
     DRM_REQUIRE(g != nullptr, DRM_E_ARG, "null grad block");
     rc = check_device(); if (rc) return rc;
+    if (use_tc(r)) return tc::rollout_tc_bwd(r, g, stream);
     RollDev p{}; dims(r, p);
     const drm_rssm& w = r->rssm;
     const int A = w.A, S = w.S, D = w.D, Hd = w.Hd, T = r->steps, n = r->n;

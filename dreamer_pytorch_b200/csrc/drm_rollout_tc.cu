@@ -1,0 +1,966 @@
+// bf16 tensor-core (tcgen05) imagination rollout: RSSMRollout.rollout_policy (rnns.py:224-244) with
+// AgentModel.policy (agent.py:101-117), ActionDecoder.forward (action.py:51-66) and RSSMTransition.forward
+// (rnns.py:98-107) fused into ONE persistent kernel per direction.  A CTA owns a tile of 128 start states for
+// all H steps; the recurrent state lives in shared memory as the bf16 A operand of the next GEMM (the fp32
+// master copy of `deter` is the kernel's own output, re-read by the thread that wrote it); weights stream
+// from L2 through the bulk-copy ring of drm_tc_chain.cuh; accumulators live in TMEM.
+//
+// Shared-memory operands (chunk-major, 128 rows):
+//   ST  = [stoch: cs chunks][deter: cdp chunks (incl. zero pad)][action: ca chunks]
+//   HB  = one hidden-activation buffer (actor hidden / rnn input x / prior hidden), rewritten in place
+// Phases per step (an = Linear layers of the actor):
+//   0..an-2  actor hidden layers          A = ST[stoch|deter] or HB      -> HB
+//   an-1     actor output + action sample A = HB                        -> ST[action], action_out
+//   an       x = ELU(W_in [a|stoch] + b)  A = ST[stoch], ST[action]      -> HB
+//   an+1     r (cols 0..), h_n (cols Dp..) A = HB|ST[deter], ST[deter]   -> TMEM cols 0.. := r * h_n
+//   an+2     i_n accumulated onto r*h_n, z A = HB, HB|ST[deter]          -> deter' -> ST[deter], deter out
+//   an+3     prior hidden                 A = ST[deter]                  -> HB
+//   an+4     prior mean | std, sample     A = HB                         -> ST[stoch], prior_* out
+#include <string.h>
+#include "drm_rollout.cuh"
+#include "drm_tc_chain.cuh"
+
+namespace drm {
+namespace tc {
+
+struct RollTcDev {
+    int T, n, ntiles, act_dist, training;
+    int A, S, D, Hd, ah, an, Aout;
+    int cs, cd, cdp, ca, chh, cha;  // chunk counts: stoch, deter (exact / even), action, Hd (even), actor hidden (even)
+    int Sp;                         // column of the first std accumulator in the prior's last Linear (S rounded up to 8)
+    float mean_scale, raw_init_std, act_min_std, temperature, min_std;
+    const float *b_in, *b_ih, *b_hh, *b_p1, *b_p2;
+    const float* ba[DRM_MAX_LINEAR];
+    const float *start_stoch, *start_deter, *eps_prior, *noise_act;
+    float *prior_mean, *prior_std, *prior_stoch, *deter, *action_out;
+    // saves (TCM images indexed by tile-step ts = t * ntiles + tile, except raw)
+    __nv_bfloat16* sv_feat;                 // [stoch|deter] fed into step t            (cs + cdp chunks)
+    __nv_bfloat16* sv_ah[DRM_MAX_LINEAR];   // actor hidden activations                  (cha)
+    __nv_bfloat16* sv_x;                    // ELU(rnn input)                            (chh)
+    __nv_bfloat16 *sv_r, *sv_z, *sv_n, *sv_hn;  // GRU gates and W_hn h + b_hn           (cdp)
+    __nv_bfloat16* sv_hid;                  // prior hidden                              (chh)
+    float* sv_raw;                          // actor output before the distribution, fp32 [T*n][Aout]
+    const uint8_t* wstream;
+    uint32_t st_off, hb_off;
+    // backward
+    const float *g_prior_mean, *g_prior_std, *g_prior_stoch, *g_deter, *g_action_out;
+    __nv_bfloat16* dys_a[DRM_MAX_LINEAR];   // dY of every actor Linear, TCM by tile-step (cha chunks; 2 for the last)
+    __nv_bfloat16* stash;                   // per-CTA scratch: [grid][2][cdp chunks] (d i_n, d h_n between two phases)
+    float* db_a_last;                       // fp32 bias gradient of the actor's last Linear
+    int want_actor;                         // 0: the actor phases are not part of the program
+    uint32_t ga_off, gb_off, g2_off;        // backward operand buffers (GA doubles as the hidden buffer)
+    TcProgram pg;
+};
+
+// ------------------------------------------------------------------------------------------------
+// forward kernel
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const __grid_constant__ RollTcDev p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    ChainBars* bars = reinterpret_cast<ChainBars*>(smem);
+    const uint32_t tmem_base = chain_setup(bars, p.pg);
+    const int warp = threadIdx.x >> 5;
+    const int my_tiles = (int)blockIdx.x < p.ntiles ? (p.ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const int reps = my_tiles * p.T;
+    if (warp == kEpiWarps) {
+        chain_producer(p.pg, bars, smem, p.wstream, reps);
+    } else if (warp == kEpiWarps + 1) {
+        chain_mma(p.pg, bars, smem, tmem_base, reps);
+    } else {
+        EpiSync es(bars);
+        uint8_t* st = smem + p.st_off;
+        uint8_t* hb = smem + p.hb_off;
+        const int row = epi_row(), grp = epi_group();
+        const int S = p.S, D = p.D, A = p.A;
+        const int Dp = p.cdp * 8;
+        const int cfeat = p.cs + p.cdp;
+        const bool save = p.training != 0;
+        for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
+            const int row0 = tile * kTileRows;
+            const int grow = row0 + row;
+            const bool live = grow < p.n;
+            // ---- start state -> ST (and the feat image of step 0); action chunks zero
+            for (int idx = threadIdx.x; idx < (cfeat + p.ca) * kTileRows; idx += kEpiThreads) {
+                const int chunk = idx / kTileRows, r = idx - chunk * kTileRows;
+                const int gr = row0 + r;
+                float v[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) v[i] = 0.f;
+                if (gr < p.n) {
+                    if (chunk < p.cs) {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) if (chunk * 8 + i < S) v[i] = __ldg(p.start_stoch + (size_t)gr * S + chunk * 8 + i);
+                    } else if (chunk < p.cs + p.cd) {
+                        const int cc = chunk - p.cs;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) if (cc * 8 + i < D) v[i] = __ldg(p.start_deter + (size_t)gr * D + cc * 8 + i);
+                    }
+                }
+                st_chunk_bf16(st + (size_t)idx * 16, v);
+                if (save && chunk < cfeat) st_chunk_bf16(p.sv_feat + ((size_t)tile * cfeat * kTileRows + idx) * 8, v);
+            }
+            es.release();
+            for (int t = 0; t < p.T; ++t) {
+                const int ts = t * p.ntiles + tile;
+                const size_t trow = (size_t)t * p.n + grow;
+                // ------------------------------------------------------------ actor hidden layers
+                for (int l = 0; l < p.an - 1; ++l) {
+                    es.wait_acc();
+                    const float* bias = p.ba[l];
+                    const int per = (p.cha + kEpiGroups - 1) / kEpiGroups;
+                    const int cbeg = grp * per, cend = min(p.cha, cbeg + per);
+                    for (int c = cbeg; c < cend; ++c) {
+                        float v[8];
+                        tmem_ld8(epi_taddr(tmem_base, c * 8), v);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int col = c * 8 + i;
+                            v[i] = (live && col < p.ah) ? elu_fast(v[i] + __ldg(bias + col)) : 0.f;
+                        }
+                        st_chunk_bf16(hb + ((size_t)c * kTileRows + row) * 16, v);
+                        if (save) st_chunk_bf16(tcm_at(p.sv_ah[l], p.cha, ts, c, row), v);
+                    }
+                    es.release();
+                }
+                // ------------------------------------------------------------ actor output + action (agent.py:101-117)
+                es.wait_acc();
+                if (grp == 0) {
+                    float raw[16];
+                    {
+                        float v0[8], v1[8];
+                        tmem_ld8(epi_taddr(tmem_base, 0), v0);
+                        tmem_ld8(epi_taddr(tmem_base, 8), v1);
+                        tmem_ld_wait();
+                        const float* bias = p.ba[p.an - 1];
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            raw[i] = i < p.Aout ? v0[i] + __ldg(bias + i) : 0.f;
+                            raw[8 + i] = 8 + i < p.Aout ? v1[i] + __ldg(bias + 8 + i) : 0.f;
+                        }
+                    }
+                    float act[16];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) act[j] = 0.f;
+                    if (live) {
+                        const float* nz = p.noise_act + trow * A;
+                        if (p.act_dist == DRM_DIST_TANH_NORMAL) {
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) {
+                                if (j < A) {
+                                    const float rm = raw[j], rs = raw[A + j];
+                                    const float mean = p.mean_scale * tanh_fast(rm / p.mean_scale);
+                                    const float std = softplus_fast(rs + p.raw_init_std) + p.act_min_std;
+                                    act[j] = tanh_fast(fmaf(std, __ldg(nz + j), mean));
+                                }
+                            }
+                        } else {
+                            float mx = -INFINITY;
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) if (j < A) mx = fmaxf(mx, raw[j]);
+                            if (p.act_dist == DRM_DIST_ONE_HOT) {
+                                float den = 0.f, bv = -INFINITY;
+                                int best = 0;
+#pragma unroll
+                                for (int j = 0; j < 16; ++j) {
+                                    if (j < A) {
+                                        den += __expf(raw[j] - mx);
+                                        const float s = raw[j] + __ldg(nz + j);
+                                        if (s > bv) { bv = s; best = j; }
+                                    }
+                                }
+#pragma unroll
+                                for (int j = 0; j < 16; ++j) {
+                                    if (j < A) {
+                                        const float pj = __expf(raw[j] - mx) / den;
+                                        act[j] = ((j == best ? 1.f : 0.f) + pj) - pj;  // straight-through value
+                                    }
+                                }
+                            } else {  // relaxed one-hot: softmax((logits + g) / temperature)
+                                float smx = -INFINITY, den = 0.f;
+#pragma unroll
+                                for (int j = 0; j < 16; ++j) if (j < A) smx = fmaxf(smx, (raw[j] + __ldg(nz + j)) / p.temperature);
+#pragma unroll
+                                for (int j = 0; j < 16; ++j) {
+                                    if (j < A) { act[j] = __expf((raw[j] + __ldg(nz + j)) / p.temperature - smx); den += act[j]; }
+                                }
+#pragma unroll
+                                for (int j = 0; j < 16; ++j) if (j < A) act[j] /= den;
+                            }
+                        }
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) {
+                            if (j < A) p.action_out[trow * A + j] = act[j];
+                            if (save && j < p.Aout) p.sv_raw[trow * p.Aout + j] = raw[j];
+                        }
+                    }
+                    uint8_t* sa = st + (size_t)cfeat * kChunkBytes;
+                    for (int c = 0; c < p.ca; ++c) {
+                        float v[8];
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) v[i] = c == 0 ? act[i] : act[8 + i];
+                        st_chunk_bf16(sa + ((size_t)c * kTileRows + row) * 16, v);
+                    }
+                }
+                es.release();
+                // ------------------------------------------------------------ x = ELU(W_in [a|stoch] + b)   (rnns.py:99-101)
+                es.wait_acc();
+                {
+                    const int per = (p.chh + kEpiGroups - 1) / kEpiGroups;
+                    const int cbeg = grp * per, cend = min(p.chh, cbeg + per);
+                    for (int c = cbeg; c < cend; ++c) {
+                        float v[8];
+                        tmem_ld8(epi_taddr(tmem_base, c * 8), v);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int col = c * 8 + i;
+                            v[i] = (live && col < p.Hd) ? elu_fast(v[i] + __ldg(p.b_in + col)) : 0.f;
+                        }
+                        st_chunk_bf16(hb + ((size_t)c * kTileRows + row) * 16, v);
+                        if (save) st_chunk_bf16(tcm_at(p.sv_x, p.chh, ts, c, row), v);
+                    }
+                }
+                es.release();
+                // ------------------------------------------------------------ GRU, part 1: r and h_n  (torch GRUCell, rnns.py:102)
+                es.wait_acc();
+                {
+                    const int per = (p.cdp + kEpiGroups - 1) / kEpiGroups;
+                    const int cbeg = grp * per, cend = min(p.cdp, cbeg + per);
+                    for (int c = cbeg; c < cend; ++c) {
+                        float ar[8], ah_[8], rr[8], hn[8];
+                        tmem_ld8(epi_taddr(tmem_base, c * 8), ar);
+                        tmem_ld8(epi_taddr(tmem_base, Dp + c * 8), ah_);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int col = c * 8 + i;
+                            const bool ok = live && col < D;
+                            rr[i] = ok ? sigmoid_fast(ar[i] + __ldg(p.b_ih + col) + __ldg(p.b_hh + col)) : 0.f;
+                            hn[i] = ok ? ah_[i] + __ldg(p.b_hh + 2 * D + col) : 0.f;
+                            ar[i] = rr[i] * hn[i];
+                        }
+                        tmem_st8(epi_taddr(tmem_base, c * 8), ar);  // i_n is accumulated on top of r * h_n by the next phase
+                        if (save) {
+                            st_chunk_bf16(tcm_at(p.sv_r, p.cdp, ts, c, row), rr);
+                            st_chunk_bf16(tcm_at(p.sv_hn, p.cdp, ts, c, row), hn);
+                        }
+                    }
+                    tmem_st_wait();
+                }
+                es.release();
+                // ------------------------------------------------------------ GRU, part 2: n, z, h'
+                es.wait_acc();
+                {
+                    const int per = (p.cdp + kEpiGroups - 1) / kEpiGroups;
+                    const int cbeg = grp * per, cend = min(p.cdp, cbeg + per);
+                    const float* hprev = t == 0 ? p.start_deter + (size_t)grow * D : p.deter + (trow - p.n) * D;
+                    const bool feat_next = save && t + 1 < p.T;
+                    for (int c = cbeg; c < cend; ++c) {
+                        float an_[8], az[8], zz[8], nn[8], hv[8];
+                        tmem_ld8(epi_taddr(tmem_base, c * 8), an_);
+                        tmem_ld8(epi_taddr(tmem_base, Dp + c * 8), az);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int col = c * 8 + i;
+                            const bool ok = live && col < D;
+                            nn[i] = ok ? tanh_fast(an_[i] + __ldg(p.b_ih + 2 * D + col)) : 0.f;
+                            zz[i] = ok ? sigmoid_fast(az[i] + __ldg(p.b_ih + D + col) + __ldg(p.b_hh + D + col)) : 0.f;
+                            const float hp = ok ? hprev[col] : 0.f;
+                            hv[i] = ok ? (1.f - zz[i]) * nn[i] + zz[i] * hp : 0.f;
+                            if (ok) p.deter[trow * D + col] = hv[i];
+                        }
+                        st_chunk_bf16(st + ((size_t)(p.cs + c) * kTileRows + row) * 16, hv);
+                        if (save) {
+                            st_chunk_bf16(tcm_at(p.sv_z, p.cdp, ts, c, row), zz);
+                            st_chunk_bf16(tcm_at(p.sv_n, p.cdp, ts, c, row), nn);
+                        }
+                        if (feat_next) st_chunk_bf16(tcm_at(p.sv_feat, cfeat, ts + p.ntiles, p.cs + c, row), hv);
+                    }
+                }
+                es.release();
+                // ------------------------------------------------------------ prior hidden  (rnns.py:103)
+                es.wait_acc();
+                {
+                    const int per = (p.chh + kEpiGroups - 1) / kEpiGroups;
+                    const int cbeg = grp * per, cend = min(p.chh, cbeg + per);
+                    for (int c = cbeg; c < cend; ++c) {
+                        float v[8];
+                        tmem_ld8(epi_taddr(tmem_base, c * 8), v);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int col = c * 8 + i;
+                            v[i] = (live && col < p.Hd) ? elu_fast(v[i] + __ldg(p.b_p1 + col)) : 0.f;
+                        }
+                        st_chunk_bf16(hb + ((size_t)c * kTileRows + row) * 16, v);
+                        if (save) st_chunk_bf16(tcm_at(p.sv_hid, p.chh, ts, c, row), v);
+                    }
+                }
+                es.release();
+                // ------------------------------------------------------------ prior mean | std, sample  (rnns.py:103-106)
+                es.wait_acc();
+                {
+                    const int per = (p.cs + kEpiGroups - 1) / kEpiGroups;
+                    const int cbeg = grp * per, cend = min(p.cs, cbeg + per);
+                    const bool feat_next = save && t + 1 < p.T;
+                    for (int c = cbeg; c < cend; ++c) {
+                        float am[8], as_[8], sv[8];
+                        tmem_ld8(epi_taddr(tmem_base, c * 8), am);
+                        tmem_ld8(epi_taddr(tmem_base, p.Sp + c * 8), as_);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int j = c * 8 + i;
+                            const bool ok = live && j < S;
+                            float st_ = 0.f;
+                            if (ok) {
+                                const float mean = am[i] + __ldg(p.b_p2 + j);
+                                const float std = softplus_fast(as_[i] + __ldg(p.b_p2 + S + j)) + p.min_std;
+                                const size_t o = trow * S + j;
+                                st_ = fmaf(std, __ldg(p.eps_prior + o), mean);
+                                p.prior_mean[o] = mean; p.prior_std[o] = std; p.prior_stoch[o] = st_;
+                            }
+                            sv[i] = st_;
+                        }
+                        st_chunk_bf16(st + ((size_t)c * kTileRows + row) * 16, sv);
+                        if (feat_next) st_chunk_bf16(tcm_at(p.sv_feat, cfeat, ts + p.ntiles, c, row), sv);
+                    }
+                }
+                if (t + 1 < p.T) es.release();
+            }
+        }
+    }
+    chain_teardown(tmem_base);
+}
+
+// ------------------------------------------------------------------------------------------------
+// backward kernel (reverse time).  Gradients flow state -> state through the transition and into the
+// actions; the actor's input is detached (rnns.py:236-238), the world model is frozen
+// (dreamer_algo.py:293), so only data gradients of the transition and data + weight gradients of the
+// actor are produced.  The carried gradients live in TMEM between steps:
+//   R_H  cols [0, colC)            scratch accumulator of the hidden-sized GEMMs
+//   R_C  cols [colC, colC + Dp)    d deter: prior-path and GRU contributions are ACCUMULATED here by the MMAs
+//   R_AS cols [colAS, ...)         d [stoch | action] of the rnn input Linear; the stoch part is next step's carry
+// Phases per step:
+//   1  d prior hidden   = d[mean|std] . W_p2          A = G2              -> R_H
+//   2  d deter         += dhid . W_p1                 A = GA (as HB)      -> R_C (accumulate)
+//   3  dx  = dpr.W_ir + dpz.W_iz ; d deter_prev += dpr.W_hr + dpz.W_hz    A = GA, GB
+//   4  dx += din.W_in ; d deter_prev += dhn.W_hn                          A = GA, GB (reloaded from the stash)
+//   5  d[stoch|action]  = dx_pre . W_in               A = GA (as HB)      -> R_AS
+//   6  d actor hidden   = d raw . Wa[last]            A = G2              -> R_H
+//   7.. d actor hidden  = dh . Wa[l]                  A = GA (as HB)      -> R_H
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const __grid_constant__ RollTcDev p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    ChainBars* bars = reinterpret_cast<ChainBars*>(smem);
+    const uint32_t tmem_base = chain_setup(bars, p.pg);
+    const int warp = threadIdx.x >> 5;
+    const int my_tiles = (int)blockIdx.x < p.ntiles ? (p.ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const int reps = my_tiles * p.T;
+    if (warp == kEpiWarps) {
+        chain_producer(p.pg, bars, smem, p.wstream, reps);
+    } else if (warp == kEpiWarps + 1) {
+        chain_mma(p.pg, bars, smem, tmem_base, reps);
+    } else {
+        EpiSync es(bars);
+        uint8_t* ga = smem + p.ga_off;
+        uint8_t* gb = smem + p.gb_off;
+        uint8_t* g2 = smem + p.g2_off;
+        const int row = epi_row(), grp = epi_group(), lane = threadIdx.x & 31;
+        const int S = p.S, D = p.D, A = p.A;
+        const int Dp = p.cdp * 8;
+        const int colC = max(p.chh, p.cha) * 8, colAS = colC + Dp;
+        __nv_bfloat16* stash_in = p.stash + (size_t)blockIdx.x * 2 * p.cdp * kTileRows * 8;
+        __nv_bfloat16* stash_hn = stash_in + (size_t)p.cdp * kTileRows * 8;
+        const int last = p.an - 1;
+        for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
+            const int row0 = tile * kTileRows;
+            const int grow = row0 + row;
+            const bool live = grow < p.n;
+            // ---- zero the carried gradients
+            {
+                float z[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) z[i] = 0.f;
+                for (int c = grp; c < p.cdp; c += kEpiGroups) tmem_st8(epi_taddr(tmem_base, colC + c * 8), z);
+                for (int c = grp; c < p.cs; c += kEpiGroups) tmem_st8(epi_taddr(tmem_base, colAS + c * 8), z);
+                tmem_st_wait();
+            }
+            for (int t = p.T - 1; t >= 0; --t) {
+                const int ts = t * p.ntiles + tile;
+                const size_t trow = (size_t)t * p.n + grow;
+                // ------------------------------------------------------------ prior head (pointwise) -> G2
+                {
+                    const int per = (p.cs + kEpiGroups - 1) / kEpiGroups;
+                    const int cbeg = grp * per, cend = min(p.cs, cbeg + per);
+                    for (int c = cbeg; c < cend; ++c) {
+                        float cs_[8], dm[8], ds[8];
+                        tmem_ld8(epi_taddr(tmem_base, colAS + c * 8), cs_);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int j = c * 8 + i;
+                            dm[i] = 0.f; ds[i] = 0.f;
+                            if (live && j < S) {
+                                const size_t o = trow * S + j;
+                                const float dst = (p.g_prior_stoch ? p.g_prior_stoch[o] : 0.f) + cs_[i];
+                                dm[i] = (p.g_prior_mean ? p.g_prior_mean[o] : 0.f) + dst;
+                                const float dsd = (p.g_prior_std ? p.g_prior_std[o] : 0.f) + dst * __ldg(p.eps_prior + o);
+                                ds[i] = dsd * (1.f - __expf(-(p.prior_std[o] - p.min_std)));  // sigmoid(raw) from softplus(raw)
+                            }
+                        }
+                        st_chunk_bf16(g2 + ((size_t)c * kTileRows + row) * 16, dm);
+                        st_chunk_bf16(g2 + ((size_t)(p.cs + c) * kTileRows + row) * 16, ds);
+                    }
+                }
+                es.release();
+                // ------------------------------------------------------------ d prior hidden
+                es.wait_acc();
+                {
+                    const int per = (p.chh + kEpiGroups - 1) / kEpiGroups;
+                    const int cbeg = grp * per, cend = min(p.chh, cbeg + per);
+                    for (int c = cbeg; c < cend; ++c) {
+                        float v[8], h[8];
+                        tmem_ld8(epi_taddr(tmem_base, c * 8), v);
+                        ld_chunk_bf16(tcm_at(p.sv_hid, p.chh, ts, c, row), h);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) v[i] = live ? v[i] * (h[i] > 0.f ? 1.f : h[i] + 1.f) : 0.f;
+                        st_chunk_bf16(ga + ((size_t)c * kTileRows + row) * 16, v);
+                    }
+                }
+                es.release();
+                // ------------------------------------------------------------ GRU cell (pointwise)
+                es.wait_acc();
+                {
+                    const int per = (p.cdp + kEpiGroups - 1) / kEpiGroups;
+                    const int cbeg = grp * per, cend = min(p.cdp, cbeg + per);
+                    const float* hprev = t == 0 ? p.start_deter + (size_t)grow * D : p.deter + (trow - p.n) * D;
+                    for (int c = cbeg; c < cend; ++c) {
+                        float dh[8], rr[8], zz[8], nn[8], hn[8], dpr[8], dpz[8], din[8], dhn[8];
+                        tmem_ld8(epi_taddr(tmem_base, colC + c * 8), dh);
+                        ld_chunk_bf16(tcm_at(p.sv_r, p.cdp, ts, c, row), rr);
+                        ld_chunk_bf16(tcm_at(p.sv_z, p.cdp, ts, c, row), zz);
+                        ld_chunk_bf16(tcm_at(p.sv_n, p.cdp, ts, c, row), nn);
+                        ld_chunk_bf16(tcm_at(p.sv_hn, p.cdp, ts, c, row), hn);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int col = c * 8 + i;
+                            const bool ok = live && col < D;
+                            float d = ok ? dh[i] + (p.g_deter ? p.g_deter[trow * D + col] : 0.f) : 0.f;
+                            const float hp = ok ? hprev[col] : 0.f;
+                            const float dn = d * (1.f - zz[i]);
+                            const float dz = d * (hp - nn[i]);
+                            const float dpn = dn * (1.f - nn[i] * nn[i]);
+                            din[i] = dpn;
+                            dhn[i] = dpn * rr[i];
+                            dpr[i] = dpn * hn[i] * rr[i] * (1.f - rr[i]);
+                            dpz[i] = dz * zz[i] * (1.f - zz[i]);
+                            dh[i] = d * zz[i];  // carry through h' = (1-z) n + z h
+                        }
+                        tmem_st8(epi_taddr(tmem_base, colC + c * 8), dh);
+                        st_chunk_bf16(ga + ((size_t)c * kTileRows + row) * 16, dpr);
+                        st_chunk_bf16(gb + ((size_t)c * kTileRows + row) * 16, dpz);
+                        st_chunk_bf16(stash_in + ((size_t)c * kTileRows + row) * 8, din);
+                        st_chunk_bf16(stash_hn + ((size_t)c * kTileRows + row) * 8, dhn);
+                    }
+                    tmem_st_wait();
+                }
+                es.release();
+                // ------------------------------------------------------------ reload d i_n, d h_n (own writes) -> GA, GB
+                es.wait_acc();
+                {
+                    const int per = (p.cdp + kEpiGroups - 1) / kEpiGroups;
+                    const int cbeg = grp * per, cend = min(p.cdp, cbeg + per);
+                    for (int c = cbeg; c < cend; ++c) {
+                        const uint4 a = *reinterpret_cast<const uint4*>(stash_in + ((size_t)c * kTileRows + row) * 8);
+                        const uint4 b = *reinterpret_cast<const uint4*>(stash_hn + ((size_t)c * kTileRows + row) * 8);
+                        *reinterpret_cast<uint4*>(ga + ((size_t)c * kTileRows + row) * 16) = a;
+                        *reinterpret_cast<uint4*>(gb + ((size_t)c * kTileRows + row) * 16) = b;
+                    }
+                }
+                es.release();
+                // ------------------------------------------------------------ d rnn-input pre-activation
+                es.wait_acc();
+                {
+                    const int per = (p.chh + kEpiGroups - 1) / kEpiGroups;
+                    const int cbeg = grp * per, cend = min(p.chh, cbeg + per);
+                    for (int c = cbeg; c < cend; ++c) {
+                        float v[8], h[8];
+                        tmem_ld8(epi_taddr(tmem_base, c * 8), v);
+                        ld_chunk_bf16(tcm_at(p.sv_x, p.chh, ts, c, row), h);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) v[i] = live ? v[i] * (h[i] > 0.f ? 1.f : h[i] + 1.f) : 0.f;
+                        st_chunk_bf16(ga + ((size_t)c * kTileRows + row) * 16, v);
+                    }
+                }
+                es.release();
+                // ------------------------------------------------------------ d [stoch | action] is in R_AS now
+                es.wait_acc();
+                if (p.want_actor) {
+                    // actor head (pointwise): d action -> d raw -> G2 (K = 16) [+ TCM copy, fp32 bias gradient]
+                    if (grp == 0) {
+                        float da[16], draw[16];
+                        {
+                            float v0[8], v1[8];
+                            tmem_ld8(epi_taddr(tmem_base, colAS + p.Sp), v0);
+                            tmem_ld8(epi_taddr(tmem_base, colAS + p.Sp + 8), v1);
+                            tmem_ld_wait();
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) { da[i] = v0[i]; da[8 + i] = v1[i]; }
+                        }
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) draw[j] = 0.f;
+                        if (live) {
+                            const float* go = p.g_action_out ? p.g_action_out + trow * A : nullptr;
+                            const float* raw = p.sv_raw + trow * p.Aout;
+                            const float* av = p.action_out + trow * A;
+                            if (p.act_dist == DRM_DIST_TANH_NORMAL) {
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) {
+                                    if (j < A) {
+                                        const float d = da[j] + (go ? go[j] : 0.f);
+                                        const float a = av[j];
+                                        const float dpre = d * (1.f - a * a);
+                                        const float th = tanh_fast(raw[j] / p.mean_scale);
+                                        draw[j] = dpre * (1.f - th * th);
+                                        draw[A + j] = dpre * __ldg(p.noise_act + trow * A + j) * sigmoid_fast(raw[A + j] + p.raw_init_std);
+                                    }
+                                }
+                            } else if (p.act_dist == DRM_DIST_ONE_HOT) {
+                                float mx = -INFINITY, den = 0.f, dot = 0.f;
+#pragma unroll
+                                for (int j = 0; j < 16; ++j) if (j < A) mx = fmaxf(mx, raw[j]);
+#pragma unroll
+                                for (int j = 0; j < 16; ++j) if (j < A) den += __expf(raw[j] - mx);
+#pragma unroll
+                                for (int j = 0; j < 16; ++j) if (j < A) dot += (da[j] + (go ? go[j] : 0.f)) * (__expf(raw[j] - mx) / den);
+#pragma unroll
+                                for (int j = 0; j < 16; ++j)
+                                    if (j < A) draw[j] = (__expf(raw[j] - mx) / den) * ((da[j] + (go ? go[j] : 0.f)) - dot);
+                            } else {
+                                float dot = 0.f;
+#pragma unroll
+                                for (int j = 0; j < 16; ++j) if (j < A) dot += (da[j] + (go ? go[j] : 0.f)) * av[j];
+#pragma unroll
+                                for (int j = 0; j < 16; ++j)
+                                    if (j < A) draw[j] = av[j] * ((da[j] + (go ? go[j] : 0.f)) - dot) / p.temperature;
+                            }
+                        }
+                        for (int c = 0; c < 2; ++c) {
+                            float v[8];
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) v[i] = c == 0 ? draw[i] : draw[8 + i];
+                            st_chunk_bf16(g2 + ((size_t)c * kTileRows + row) * 16, v);
+                            st_chunk_bf16(tcm_at(p.dys_a[last], 2, ts, c, row), v);
+                        }
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) {
+                            const float sum = warp_sum(draw[j]);
+                            if (lane == 0 && j < p.Aout) atomicAdd(p.db_a_last + j, sum);
+                        }
+                    }
+                    es.release();
+                    // actor hidden layers, last Linear first; layer 0's input (feat) is detached (rnns.py:238)
+                    for (int l = last; l >= 1; --l) {
+                        es.wait_acc();
+                        const int per = (p.cha + kEpiGroups - 1) / kEpiGroups;
+                        const int cbeg = grp * per, cend = min(p.cha, cbeg + per);
+                        for (int c = cbeg; c < cend; ++c) {
+                            float v[8], h[8];
+                            tmem_ld8(epi_taddr(tmem_base, c * 8), v);
+                            ld_chunk_bf16(tcm_at(p.sv_ah[l - 1], p.cha, ts, c, row), h);
+                            tmem_ld_wait();
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) v[i] = live ? v[i] * (h[i] > 0.f ? 1.f : h[i] + 1.f) : 0.f;
+                            st_chunk_bf16(ga + ((size_t)c * kTileRows + row) * 16, v);
+                            st_chunk_bf16(tcm_at(p.dys_a[l - 1], p.cha, ts, c, row), v);
+                        }
+                        if (l > 1) es.release();
+                    }
+                }
+            }
+            // the next tile's zero-fill of R_C / R_AS and its first release() come after these loads
+        }
+    }
+    chain_teardown(tmem_base);
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side: program, weight images, shared memory and save layout
+// ------------------------------------------------------------------------------------------------
+struct RollTcPlan {
+    RollTcDev dev;
+    PackTcJobs jobs;
+    size_t wbytes;
+    size_t smem_bytes;
+    size_t save_bytes;
+};
+
+int rollout_tc_supported(const drm_rollout* r) {
+    const drm_rssm& w = r->rssm;
+    if (r->mode != DRM_MODE_POLICY) return 0;
+    // Categorical policies sample through an argmax / a temperature-0.1 softmax of the logits: both amplify the
+    // bf16 operand rounding beyond the 1e-2 parity budget (a flipped argmax is an O(1) difference), so those
+    // rollouts stay on the fp32 kernels.
+    if (r->act_dist != DRM_DIST_TANH_NORMAL) return 0;
+    const int Aout = r->actor.out_dim;
+    if (Aout > 16 || w.A > 16) return 0;
+    if (rup(w.D, 16) > 256 || rup(w.Hd, 16) > 256 || rup(r->actor.hidden, 16) > 256 || w.S > 64) return 0;
+    if (r->actor.n_linear < 2) return 0;
+    // tensor memory of the backward: R_H | R_C | R_AS
+    const int chh = rup((w.Hd + 7) / 8, 2), cha = rup((r->actor.hidden + 7) / 8, 2), cdp = rup((w.D + 7) / 8, 2);
+    const int cs = rup((w.S + 7) / 8, 2);
+    if ((chh > cha ? chh : cha) * 8 + cdp * 8 + rup(cs * 8 + 16, 16) > kTmemCols) return 0;
+    return 1;
+}
+
+static void set_dims(const drm_rollout* r, RollTcDev& d) {
+    const drm_rssm& w = r->rssm;
+    memset(&d, 0, sizeof(d));
+    d.T = r->steps; d.n = r->n; d.ntiles = (r->n + kTileRows - 1) / kTileRows;
+    d.act_dist = r->act_dist; d.training = r->training;
+    d.A = w.A; d.S = w.S; d.D = w.D; d.Hd = w.Hd; d.ah = r->actor.hidden; d.an = r->actor.n_linear; d.Aout = r->actor.out_dim;
+    d.cs = rup((w.S + 7) / 8, 2); d.cd = (w.D + 7) / 8; d.cdp = rup(d.cd, 2); d.ca = rup((w.A + 7) / 8, 2);
+    d.chh = rup((w.Hd + 7) / 8, 2); d.cha = rup((d.ah + 7) / 8, 2);
+    d.Sp = d.cs * 8;
+    d.mean_scale = r->act_mean_scale; d.raw_init_std = r->act_raw_init_std; d.act_min_std = r->act_min_std;
+    d.temperature = r->act_temperature; d.min_std = r->min_std;
+}
+
+struct ProgBuilder {
+    TcProgram* pg;
+    PackTcJobs* jobs;
+    uint8_t* wbase;
+    size_t woff;
+    bool ok;
+    TcOp* add_op(uint32_t a0, int c0, uint32_t a1, int c1, int n, int d_col, int accumulate, int phase_end) {
+        if (pg->n_ops >= kMaxOps) { ok = false; return nullptr; }
+        TcOp& op = pg->op[pg->n_ops++];
+        op.a_off[0] = a0; op.a_off[1] = a1; op.a_chunks[0] = (uint16_t)c0; op.a_chunks[1] = (uint16_t)c1;
+        op.n = (uint16_t)n; op.d_col = (uint16_t)d_col; op.accumulate = (uint16_t)accumulate; op.phase_end = (uint16_t)phase_end;
+        if (phase_end) pg->n_phases++;
+        return &op;
+    }
+    // image of `k_chunks` K chunks for an op with MMA N = n_pad; appended to the weight stream
+    PackTcJob* add_job(const float* src, int ld, int transposed, int n0, int n_valid, int n_pad, int k_chunks) {
+        if (jobs->n >= kMaxPackTcJobs) { ok = false; return nullptr; }
+        PackTcJob& j = jobs->j[jobs->n++];
+        memset(&j, 0, sizeof(j));
+        j.src = src; j.dst = wbase ? reinterpret_cast<__nv_bfloat16*>(wbase + woff) : nullptr;
+        j.ld = ld; j.transposed = transposed; j.n0 = n0; j.n_valid = n_valid; j.n_pad = n_pad; j.k_chunks = k_chunks;
+        woff += (size_t)k_chunks * n_pad * 16;
+        return &j;
+    }
+    static void seg(PackTcJob* j, int kstart, int len, int src0) {
+        if (!j) return;
+        j->seg_kstart[j->nseg] = kstart; j->seg_len[j->nseg] = len; j->seg_src0[j->nseg] = src0; j->nseg++;
+    }
+};
+
+static int finish_smem(RollTcDev& d, size_t& smem_bytes) {
+    TcProgram& pg = d.pg;
+    d.st_off = 1024;
+    d.hb_off = d.st_off + (uint32_t)(d.cs + d.cdp + d.ca) * kChunkBytes;
+    const int hb_chunks = d.chh > d.cha ? d.chh : d.cha;
+    pg.stage_off = (uint32_t)rup_sz(d.hb_off + (size_t)hb_chunks * kChunkBytes, 1024);
+    pg.stage_bytes = 32 * 1024;
+    int stages = (int)(((size_t)kMaxSmem - pg.stage_off) / pg.stage_bytes);
+    if (stages > 4) stages = 4;
+    DRM_REQUIRE(stages >= 2, DRM_E_SHAPE, "model too wide for the bf16 rollout's shared memory");
+    pg.n_stages = stages;
+    smem_bytes = pg.stage_off + (size_t)stages * pg.stage_bytes;
+    return DRM_OK;
+}
+
+static int plan_fwd(const drm_rollout* r, uint8_t* wbase, RollTcPlan& pl) {
+    const drm_rssm& w = r->rssm;
+    const drm_mlp& a = r->actor;
+    RollTcDev& d = pl.dev;
+    set_dims(r, d);
+    int rc = finish_smem(d, pl.smem_bytes); if (rc) return rc;
+    const int S = w.S, D = w.D, Hd = w.Hd, A = w.A;
+    const int Dp = d.cdp * 8, Hp = d.chh * 8, Ap = d.cha * 8;
+    const uint32_t st_stoch = d.st_off, st_deter = d.st_off + (uint32_t)d.cs * kChunkBytes;
+    const uint32_t st_act = d.st_off + (uint32_t)(d.cs + d.cdp) * kChunkBytes, hb = d.hb_off;
+    pl.jobs.n = 0; d.pg.n_ops = 0; d.pg.n_phases = 0;
+    ProgBuilder b{&d.pg, &pl.jobs, wbase, 0, true};
+    PackTcJob* j;
+    // actor layer 0 on [stoch | deter]
+    b.add_op(st_stoch, d.cs + d.cdp, 0, 0, Ap, 0, 0, 1);
+    j = b.add_job(a.W[0], S + D, 0, 0, a.hidden, Ap, d.cs + d.cdp);
+    ProgBuilder::seg(j, 0, S, 0); ProgBuilder::seg(j, d.cs * 8, D, S);
+    for (int l = 1; l < a.n_linear; ++l) {
+        const bool lastl = l == a.n_linear - 1;
+        const int npad = lastl ? 16 : Ap;
+        b.add_op(hb, d.cha, 0, 0, npad, 0, 0, 1);
+        j = b.add_job(a.W[l], a.hidden, 0, 0, lastl ? a.out_dim : a.hidden, npad, d.cha);
+        ProgBuilder::seg(j, 0, a.hidden, 0);
+    }
+    // x = W_in [action | stoch]: A operand order is [stoch | action]
+    b.add_op(st_stoch, d.cs, st_act, d.ca, Hp, 0, 0, 1);
+    j = b.add_job(w.W_in, A + S, 0, 0, Hd, Hp, d.cs + d.ca);
+    ProgBuilder::seg(j, 0, S, A); ProgBuilder::seg(j, d.cs * 8, A, 0);
+    // GRU part 1: r = [W_ir x + W_hr h], h_n = W_hn h
+    b.add_op(hb, d.chh, st_deter, d.cdp, Dp, 0, 0, 0);
+    j = b.add_job(w.W_ih, Hd, 0, 0, D, Dp, d.chh); ProgBuilder::seg(j, 0, Hd, 0);
+    j = b.add_job(w.W_hh, D, 0, 0, D, Dp, d.cdp); ProgBuilder::seg(j, 0, D, 0);
+    b.add_op(st_deter, d.cdp, 0, 0, Dp, Dp, 0, 1);
+    j = b.add_job(w.W_hh, D, 0, 2 * D, D, Dp, d.cdp); ProgBuilder::seg(j, 0, D, 0);
+    // GRU part 2: i_n accumulated onto r * h_n, z
+    b.add_op(hb, d.chh, 0, 0, Dp, 0, 1, 0);
+    j = b.add_job(w.W_ih, Hd, 0, 2 * D, D, Dp, d.chh); ProgBuilder::seg(j, 0, Hd, 0);
+    b.add_op(hb, d.chh, st_deter, d.cdp, Dp, Dp, 0, 1);
+    j = b.add_job(w.W_ih, Hd, 0, D, D, Dp, d.chh); ProgBuilder::seg(j, 0, Hd, 0);
+    j = b.add_job(w.W_hh, D, 0, D, D, Dp, d.cdp); ProgBuilder::seg(j, 0, D, 0);
+    // prior
+    b.add_op(st_deter, d.cdp, 0, 0, Hp, 0, 0, 1);
+    j = b.add_job(w.W_p1, D, 0, 0, Hd, Hp, d.cdp); ProgBuilder::seg(j, 0, D, 0);
+    const int n2 = rup(d.Sp + d.cs * 8, 16);
+    b.add_op(hb, d.chh, 0, 0, n2, 0, 0, 1);
+    j = b.add_job(w.W_p2, Hd, 0, 0, S, n2, d.chh); ProgBuilder::seg(j, 0, Hd, 0);
+    if (j) { j->n2_start = d.Sp; j->n2_valid = S; j->n2_src0 = S; }
+    DRM_REQUIRE(b.ok, DRM_E_SHAPE, "actor too deep for the bf16 rollout");
+    pl.wbytes = b.woff;
+    return DRM_OK;
+}
+
+// carve the save buffer; returns bytes
+static size_t carve_save_tc(const RollTcDev& dd, uint8_t* base, RollTcDev* out) {
+    const size_t TS = (size_t)dd.T * dd.ntiles;
+    size_t off = 0;
+    auto take = [&](size_t bytes) -> uint8_t* {
+        uint8_t* ptr = base ? base + off : nullptr;
+        off += rup_sz(bytes, 256);
+        return ptr;
+    };
+    RollTcDev tmp = dd;
+    tmp.sv_feat = (__nv_bfloat16*)take(tcm_bytes(TS, dd.cs + dd.cdp));
+    for (int l = 0; l < dd.an - 1; ++l) tmp.sv_ah[l] = (__nv_bfloat16*)take(tcm_bytes(TS, dd.cha));
+    tmp.sv_x = (__nv_bfloat16*)take(tcm_bytes(TS, dd.chh));
+    tmp.sv_r = (__nv_bfloat16*)take(tcm_bytes(TS, dd.cdp));
+    tmp.sv_z = (__nv_bfloat16*)take(tcm_bytes(TS, dd.cdp));
+    tmp.sv_n = (__nv_bfloat16*)take(tcm_bytes(TS, dd.cdp));
+    tmp.sv_hn = (__nv_bfloat16*)take(tcm_bytes(TS, dd.cdp));
+    tmp.sv_hid = (__nv_bfloat16*)take(tcm_bytes(TS, dd.chh));
+    tmp.sv_raw = (float*)take((size_t)dd.T * dd.n * dd.Aout * sizeof(float));
+    if (out) *out = tmp;
+    return off;
+}
+
+size_t rollout_tc_save_bytes(const drm_rollout* r) {
+    RollTcDev d;
+    set_dims(r, d);
+    return carve_save_tc(d, nullptr, nullptr) + 512;
+}
+
+static void fill_io_tc(const drm_rollout* r, RollTcDev& d) {
+    const drm_rssm& w = r->rssm;
+    d.b_in = w.b_in; d.b_ih = w.b_ih; d.b_hh = w.b_hh; d.b_p1 = w.b_p1; d.b_p2 = w.b_p2;
+    for (int l = 0; l < r->actor.n_linear; ++l) d.ba[l] = r->actor.b[l];
+    d.start_stoch = r->start_stoch; d.start_deter = r->start_deter; d.eps_prior = r->eps_prior; d.noise_act = r->noise_act;
+    d.prior_mean = r->prior_mean; d.prior_std = r->prior_std; d.prior_stoch = r->prior_stoch; d.deter = r->deter;
+    d.action_out = r->action_out;
+}
+
+int rollout_tc_fwd(const drm_rollout* r, cudaStream_t stream) {
+    DRM_REQUIRE(rollout_tc_supported(r), DRM_E_SHAPE, "shape not supported by the bf16 rollout");
+    RollTcPlan pl;
+    uint8_t* ws = reinterpret_cast<uint8_t*>(rup_sz((size_t)r->workspace, 256));
+    int rc = plan_fwd(r, ws, pl); if (rc) return rc;
+    DRM_REQUIRE(r->workspace && r->workspace_bytes >= pl.wbytes + 512, DRM_E_WORKSPACE, "workspace too small (bf16 rollout)");
+    RollTcDev& d = pl.dev;
+    fill_io_tc(r, d);
+    d.wstream = ws;
+    if (r->training) {
+        DRM_REQUIRE(r->save && r->save_bytes >= rollout_tc_save_bytes(r), DRM_E_WORKSPACE, "save buffer too small (bf16 rollout)");
+        RollTcDev carved;
+        carve_save_tc(d, reinterpret_cast<uint8_t*>(rup_sz((size_t)r->save, 256)), &carved);
+        d = carved;
+    }
+    rc = launch_pack_tc(pl.jobs, stream); if (rc) return rc;
+    const int grid = d.ntiles < kNumSM ? d.ntiles : kNumSM;
+    DRM_CUDA_OK(cudaFuncSetAttribute(rollout_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
+    ProfScope prof(PROF_ROLLOUT_FWD, stream);
+    rollout_fwd_tc_kernel<<<grid, kChainThreads, pl.smem_bytes, stream>>>(d);
+    DRM_CUDA_OK(cudaGetLastError());
+    return DRM_OK;
+}
+
+static int finish_smem_bwd(RollTcDev& d, size_t& smem_bytes) {
+    TcProgram& pg = d.pg;
+    const int hb_chunks = max(max(d.chh, d.cha), d.cdp);
+    d.ga_off = 1024;
+    d.gb_off = d.ga_off + (uint32_t)hb_chunks * kChunkBytes;
+    d.g2_off = d.gb_off + (uint32_t)d.cdp * kChunkBytes;
+    const int g2_chunks = 2 * d.cs > 2 ? 2 * d.cs : 2;
+    pg.stage_off = (uint32_t)rup_sz(d.g2_off + (size_t)g2_chunks * kChunkBytes, 1024);
+    pg.stage_bytes = 32 * 1024;
+    int stages = (int)(((size_t)kMaxSmem - pg.stage_off) / pg.stage_bytes);
+    if (stages > 4) stages = 4;
+    DRM_REQUIRE(stages >= 2, DRM_E_SHAPE, "model too wide for the bf16 rollout's shared memory");
+    pg.n_stages = stages;
+    smem_bytes = pg.stage_off + (size_t)stages * pg.stage_bytes;
+    return DRM_OK;
+}
+
+static int plan_bwd(const drm_rollout* r, bool want_actor, uint8_t* wbase, RollTcPlan& pl) {
+    const drm_rssm& w = r->rssm;
+    const drm_mlp& a = r->actor;
+    RollTcDev& d = pl.dev;
+    set_dims(r, d);
+    d.want_actor = want_actor ? 1 : 0;
+    int rc = finish_smem_bwd(d, pl.smem_bytes); if (rc) return rc;
+    const int S = w.S, D = w.D, Hd = w.Hd, A = w.A;
+    const int Dp = d.cdp * 8, Hp = d.chh * 8, Ap = d.cha * 8;
+    const int colC = (d.chh > d.cha ? d.chh : d.cha) * 8, colAS = colC + Dp;
+    const int nAS = rup(d.Sp + 16, 16);
+    DRM_REQUIRE(colAS + nAS <= kTmemCols, DRM_E_SHAPE, "model too wide for the bf16 rollout's tensor memory");
+    const uint32_t ga = d.ga_off, gb = d.gb_off, g2 = d.g2_off;
+    pl.jobs.n = 0; d.pg.n_ops = 0; d.pg.n_phases = 0;
+    ProgBuilder b{&d.pg, &pl.jobs, wbase, 0, true};
+    PackTcJob* j;
+    // 1: d prior hidden = d[mean|std] . W_p2
+    b.add_op(g2, 2 * d.cs, 0, 0, Hp, 0, 0, 1);
+    j = b.add_job(w.W_p2, Hd, 1, 0, Hd, Hp, 2 * d.cs);
+    ProgBuilder::seg(j, 0, S, 0); ProgBuilder::seg(j, d.Sp, S, S);
+    // 2: d deter += dhid . W_p1
+    b.add_op(ga, d.chh, 0, 0, Dp, colC, 1, 1);
+    j = b.add_job(w.W_p1, D, 1, 0, D, Dp, d.chh); ProgBuilder::seg(j, 0, Hd, 0);
+    // 3: dx = dpr.W_ir + dpz.W_iz ; d deter_prev += dpr.W_hr + dpz.W_hz
+    b.add_op(ga, d.cdp, gb, d.cdp, Hp, 0, 0, 0);
+    j = b.add_job(w.W_ih, Hd, 1, 0, Hd, Hp, d.cdp); ProgBuilder::seg(j, 0, D, 0);
+    j = b.add_job(w.W_ih, Hd, 1, 0, Hd, Hp, d.cdp); ProgBuilder::seg(j, 0, D, D);
+    b.add_op(ga, d.cdp, gb, d.cdp, Dp, colC, 1, 1);
+    j = b.add_job(w.W_hh, D, 1, 0, D, Dp, d.cdp); ProgBuilder::seg(j, 0, D, 0);
+    j = b.add_job(w.W_hh, D, 1, 0, D, Dp, d.cdp); ProgBuilder::seg(j, 0, D, D);
+    // 4: dx += din.W_in ; d deter_prev += dhn.W_hn
+    b.add_op(ga, d.cdp, 0, 0, Hp, 0, 1, 0);
+    j = b.add_job(w.W_ih, Hd, 1, 0, Hd, Hp, d.cdp); ProgBuilder::seg(j, 0, D, 2 * D);
+    b.add_op(gb, d.cdp, 0, 0, Dp, colC, 1, 1);
+    j = b.add_job(w.W_hh, D, 1, 0, D, Dp, d.cdp); ProgBuilder::seg(j, 0, D, 2 * D);
+    // 5: d[stoch | action] = dx_pre . W_in   (columns: stoch at 0.., action at Sp..)
+    b.add_op(ga, d.chh, 0, 0, nAS, colAS, 0, 1);
+    j = b.add_job(w.W_in, A + S, 1, A, S, nAS, d.chh); ProgBuilder::seg(j, 0, Hd, 0);
+    if (j) { j->n2_start = d.Sp; j->n2_valid = A; j->n2_src0 = 0; }
+    if (want_actor) {
+        const int last = a.n_linear - 1;
+        b.add_op(g2, 2, 0, 0, Ap, 0, 0, 1);
+        j = b.add_job(a.W[last], a.hidden, 1, 0, a.hidden, Ap, 2); ProgBuilder::seg(j, 0, a.out_dim, 0);
+        for (int l = last - 1; l >= 1; --l) {
+            b.add_op(ga, d.cha, 0, 0, Ap, 0, 0, 1);
+            j = b.add_job(a.W[l], a.hidden, 1, 0, a.hidden, Ap, d.cha); ProgBuilder::seg(j, 0, a.hidden, 0);
+        }
+    }
+    DRM_REQUIRE(b.ok, DRM_E_SHAPE, "actor too deep for the bf16 rollout");
+    pl.wbytes = b.woff;
+    return DRM_OK;
+}
+
+// workspace of the backward: [weight images][dY images of the actor][per-CTA stash]
+static size_t carve_bwd_ws(const RollTcDev& dd, size_t wbytes, uint8_t* base, RollTcDev* out) {
+    const size_t TS = (size_t)dd.T * dd.ntiles;
+    size_t off = rup_sz(wbytes, 256);
+    auto take = [&](size_t bytes) -> uint8_t* {
+        uint8_t* ptr = base ? base + off : nullptr;
+        off += rup_sz(bytes, 256);
+        return ptr;
+    };
+    RollTcDev tmp = dd;
+    for (int l = 0; l < dd.an; ++l) tmp.dys_a[l] = (__nv_bfloat16*)take(tcm_bytes(TS, l == dd.an - 1 ? 2 : dd.cha));
+    const int grid = dd.ntiles < kNumSM ? dd.ntiles : kNumSM;
+    tmp.stash = (__nv_bfloat16*)take((size_t)grid * 2 * dd.cdp * kChunkBytes);
+    if (out) *out = tmp;
+    return off;
+}
+
+size_t rollout_tc_bwd_workspace_bytes(const drm_rollout* r) {
+    RollTcPlan pl;
+    if (!rollout_tc_supported(r) || plan_bwd(r, true, nullptr, pl) != DRM_OK) return 0;
+    return carve_bwd_ws(pl.dev, pl.wbytes, nullptr, nullptr) + 1024;
+}
+
+int rollout_tc_bwd(const drm_rollout* r, const drm_rollout_grad* g, cudaStream_t stream) {
+    DRM_REQUIRE(rollout_tc_supported(r), DRM_E_SHAPE, "shape not supported by the bf16 rollout");
+    DRM_REQUIRE(!g->want_rssm_grad, DRM_E_SHAPE,
+                "the bf16 imagination rollout computes actor gradients only (world model frozen, dreamer_algo.py:293); "
+                "run the rollout in fp32 for transition weight gradients");
+    const drm_mlp& a = r->actor;
+    const bool want_actor = g->want_actor_grad != 0;
+    RollTcPlan pl;
+    uint8_t* ws = reinterpret_cast<uint8_t*>(rup_sz((size_t)r->workspace, 256));
+    int rc = plan_bwd(r, want_actor, ws, pl); if (rc) return rc;
+    DRM_REQUIRE(r->workspace && r->workspace_bytes >= rollout_tc_bwd_workspace_bytes(r), DRM_E_WORKSPACE,
+                "workspace too small (bf16 rollout backward)");
+    DRM_REQUIRE(r->save && r->save_bytes >= rollout_tc_save_bytes(r), DRM_E_WORKSPACE,
+                "save buffer missing: run drm_rollout_fwd with training=1 first");
+    RollTcDev d = pl.dev;
+    {
+        RollTcDev carved;
+        carve_save_tc(d, reinterpret_cast<uint8_t*>(rup_sz((size_t)r->save, 256)), &carved);
+        d = carved;
+        carve_bwd_ws(d, pl.wbytes, ws, &carved);
+        d = carved;
+    }
+    fill_io_tc(r, d);
+    d.wstream = ws;
+    d.g_prior_mean = g->g_prior_mean; d.g_prior_std = g->g_prior_std; d.g_prior_stoch = g->g_prior_stoch;
+    d.g_deter = g->g_deter; d.g_action_out = g->g_action_out;
+    if (want_actor) {
+        for (int l = 0; l < a.n_linear; ++l) {
+            const int nout = l == a.n_linear - 1 ? a.out_dim : a.hidden;
+            const int nin = l == 0 ? a.in_dim : a.hidden;
+            DRM_REQUIRE(g->actor.dW[l] && g->actor.db[l], DRM_E_ARG, "null actor gradient sink");
+            DRM_CUDA_OK(cudaMemsetAsync(g->actor.dW[l], 0, sizeof(float) * nout * nin, stream));
+            DRM_CUDA_OK(cudaMemsetAsync(g->actor.db[l], 0, sizeof(float) * nout, stream));
+        }
+        d.db_a_last = g->actor.db[a.n_linear - 1];
+    }
+    rc = launch_pack_tc(pl.jobs, stream); if (rc) return rc;
+    {
+        const int grid = d.ntiles < kNumSM ? d.ntiles : kNumSM;
+        DRM_CUDA_OK(cudaFuncSetAttribute(rollout_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
+        ProfScope prof(PROF_ROLLOUT_BWD, stream);
+        rollout_bwd_tc_kernel<<<grid, kChainThreads, pl.smem_bytes, stream>>>(d);
+        DRM_CUDA_OK(cudaGetLastError());
+    }
+    if (want_actor) {
+        WgParams wg;
+        memset(&wg, 0, sizeof(wg));
+        wg.n_layers = a.n_linear; wg.row_tiles = d.T * d.ntiles;
+        const int last = a.n_linear - 1;
+        for (int l = 0; l <= last; ++l) {
+            WgLayer& L = wg.L[l];
+            L.dy = d.dys_a[l]; L.dy_cpt = l == last ? 2 : d.cha;
+            L.nout = l == last ? a.out_dim : a.hidden;
+            if (l == 0) {
+                L.nseg = 2;
+                L.seg[0] = WgSeg{d.sv_feat, d.cs + d.cdp, 0, (d.S + 7) / 8, 0, d.S};
+                L.seg[1] = WgSeg{d.sv_feat, d.cs + d.cdp, d.cs, d.cd, d.S, d.D};
+                L.ld_dw = a.in_dim;
+            } else {
+                L.nseg = 1;
+                L.seg[0] = WgSeg{d.sv_ah[l - 1], d.cha, 0, (a.hidden + 7) / 8, 0, a.hidden};
+                L.ld_dw = a.hidden;
+            }
+            L.dW = g->actor.dW[l];
+            L.db = l == last ? nullptr : g->actor.db[l];
+        }
+        wgrad_tc_plan(wg);
+        rc = launch_wgrad_tc(wg, stream); if (rc) return rc;
+    }
+    return DRM_OK;
+}
+
+size_t rollout_tc_fwd_workspace_bytes(const drm_rollout* r) {
+    RollTcPlan pl;
+    if (!rollout_tc_supported(r) || plan_fwd(r, nullptr, pl) != DRM_OK) return 0;
+    return pl.wbytes + 1024;
+}
+
+}  // namespace tc
+}  // namespace drm

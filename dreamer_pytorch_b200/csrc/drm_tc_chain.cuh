@@ -195,6 +195,17 @@ __device__ __forceinline__ uint32_t epi_taddr(uint32_t tmem_base, int col) {
     return tmem_base + ((uint32_t)(32 * ((threadIdx.x >> 5) & 3)) << 16) + (uint32_t)col;
 }
 
+// ---------------------------------------------------------------------------------------------- fast pointwise math
+// (bf16 path only: the operands of the next GEMM are rounded to 8 bits of mantissa anyway)
+__device__ __forceinline__ float elu_fast(float x) { return x > 0.f ? x : __expf(x) - 1.f; }
+__device__ __forceinline__ float tanh_fast(float x) {
+    float y;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float sigmoid_fast(float x) { return fmaf(0.5f, tanh_fast(0.5f * x), 0.5f); }
+__device__ __forceinline__ float softplus_fast(float x) { return x > 20.f ? x : __logf(1.f + __expf(x)); }
+
 // ---------------------------------------------------------------------------------------------- TCM images
 // "Tiled chunk-major" global image of a [rows x F] bf16 matrix: [tile of 128 rows][chunk of 8 features][128][8].
 // It is byte-for-byte the shared-memory A-operand image of each row tile, so the epilogue threads store
@@ -259,6 +270,7 @@ struct PackTcJob {
     __nv_bfloat16* dst;
     int ld, transposed;
     int n0, n_valid, n_pad;
+    int n2_start, n2_valid, n2_src0;  // optional second N segment: image rows [n2_start, +n2_valid) <- src index n2_src0 + i
     int k_chunks;
     int nseg;
     int seg_kstart[3], seg_len[3], seg_src0[3];

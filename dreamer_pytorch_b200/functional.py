@@ -41,6 +41,10 @@ def _f32c(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
     return t.contiguous()
 
 
+def _prec(mode):
+    return _lib.BF16 if (mode or get_precision()) == "bf16" else _lib.FP32
+
+
 def _count(n=1):
     _lib.launch_count += n
 
@@ -81,13 +85,14 @@ class RolloutCfg:
         self.act_dist, self.n_actor = act_dist, n_actor
         self.mean_scale, self.raw_init_std, self.act_min_std = mean_scale, raw_init_std, act_min_std
         self.temperature, self.min_std = temperature, min_std
+        self.precision = None  # resolved (and frozen) by the forward call
 
 
 def _build_rollout(cfg: RolloutCfg, t: dict, rssm, actor, training: bool) -> _lib.drm_rollout:
     r = _lib.drm_rollout()
     r.mode, r.steps, r.n = cfg.mode, cfg.steps, cfg.n
     r.act_dist = _lib.DIST[cfg.act_dist]
-    r.precision = _lib.FP32
+    r.precision = _prec(cfg.precision)
     r.training = 1 if training else 0
     r.act_mean_scale, r.act_raw_init_std, r.act_min_std = cfg.mean_scale, cfg.raw_init_std, cfg.act_min_std
     r.act_temperature, r.min_std = cfg.temperature, cfg.min_std
@@ -119,6 +124,8 @@ def rollout_forward_raw(cfg: RolloutCfg, t: dict, rssm, actor, training: bool):
     """Validates shapes, allocates the outputs into ``t`` and runs drm_rollout_fwd.
     Returns the save buffer (None unless training)."""
     lib = _lib.load()
+    if cfg.precision is None:
+        cfg.precision = get_precision()
     A, S, D, Hd, E = cfg.dims
     T, n = cfg.steps, cfg.n
     dev = t["start_stoch"].device
@@ -217,6 +224,11 @@ class RolloutFn(torch.autograd.Function):
                  obs_embed=_f32c(obs_embed), eps_prior=_f32c(eps_prior), eps_post=_f32c(eps_post),
                  noise_act=_f32c(noise_act))
         training = any(ctx.needs_input_grad)
+        n_rssm = 14 if cfg.mode == _lib.MODE_REPRESENTATION else 10
+        if get_precision() == "bf16" and any(ctx.needs_input_grad[8 + i] for i in range(n_rssm)):
+            # the tensor-core rollout produces actor gradients only (the hot path freezes the world model,
+            # dreamer_algo.py:293); transition / posterior weight gradients come from the fp32 kernels
+            cfg.precision = "fp32"
         save = rollout_forward_raw(cfg, t, rssm, actor, training)
         ctx.cfg = cfg
         ctx.n_w = len(weights)
@@ -252,10 +264,6 @@ class RolloutFn(torch.autograd.Function):
 # ------------------------------------------------------------------------------------------------
 # batched MLP
 # ------------------------------------------------------------------------------------------------
-def _prec(mode):
-    return _lib.BF16 if (mode or get_precision()) == "bf16" else _lib.FP32
-
-
 def _build_mlp_call(x0, x1, weights, M, training, precision=None) -> _lib.drm_mlp_call:
     c = _lib.drm_mlp_call()
     k0 = x0.shape[1]

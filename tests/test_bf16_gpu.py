@@ -97,3 +97,95 @@ def test_mlp_bf16_accumulate_and_frozen(cuda):
     rg = torch.autograd.grad(ry, r_in, 0.5 * gy.double())
     assert rel_err(dx0 - 1, rg[0]) < BF16_TOL
     assert rel_err(dx1 - 1, rg[1]) < BF16_TOL
+
+
+# ------------------------------------------------------------------------------------------------
+# imagination rollout (policy mode) on the tensor cores
+# ------------------------------------------------------------------------------------------------
+ROLL_SIZES = [
+    dict(A=6, S=30, D=200, Hd=200, n=53, T=7),     # reference widths, one ragged tile
+    dict(A=1, S=30, D=200, Hd=200, n=150, T=3),    # cartpole action size, two tiles
+    dict(A=6, S=30, D=200, Hd=200, n=700, T=15),   # six tiles, full horizon
+]
+
+
+@pytest.mark.parametrize("sz", ROLL_SIZES)
+def test_rollout_policy_bf16(cuda, sz):
+    from oracle import dreamer_oracle as O
+    from dreamer_pytorch_b200 import _lib
+    from dreamer_pytorch_b200.functional import RolloutCfg, RolloutFn
+    from dreamer_pytorch_b200.precision import precision
+
+    A, S, D, Hd, n, H = sz["A"], sz["S"], sz["D"], sz["Hd"], sz["n"], sz["T"]
+    shapes = O.weight_shapes(A, S, D, Hd, 1024, "tanh_normal")
+    w = O.make_weights(shapes, 31)
+    nz = O.make_noise(1, 1, n, H, S, A, 32, "tanh_normal")
+    g = torch.Generator().manual_seed(33)
+    start_s, start_h = torch.randn(n, S, generator=g), torch.tanh(torch.randn(n, D, generator=g))
+    TR = O.TR
+    rk = [TR + "_rnn_input_model.0.weight", TR + "_rnn_input_model.0.bias", TR + "_cell.weight_ih",
+          TR + "_cell.weight_hh", TR + "_cell.bias_ih", TR + "_cell.bias_hh",
+          TR + "_stochastic_prior_model.0.weight", TR + "_stochastic_prior_model.0.bias",
+          TR + "_stochastic_prior_model.2.weight", TR + "_stochastic_prior_model.2.bias"]
+    ak = [f"{O.ACT}{2 * i}.{p}" for i in range(4) for p in ("weight", "bias")]
+
+    wd = {k: v.double().requires_grad_(True) for k, v in w.items()}
+    imag, actions = O.rollout_policy(wd, H, start_s.double(), start_h.double(), nz["noise_act"].double(),
+                                     nz["eps_prior_img"].double(), "tanh_normal")
+    ro = list(imag) + [actions]
+
+    wr = [w[k].to(cuda) for k in rk]                         # frozen world model (dreamer_algo.py:293)
+    wa = [w[k].to(cuda).requires_grad_(True) for k in ak]
+    cfg = RolloutCfg(_lib.MODE_POLICY, H, n, (A, S, D, Hd, 0), act_dist="tanh_normal")
+    with precision("bf16"):
+        co = list(RolloutFn.apply(cfg, start_s.to(cuda), start_h.to(cuda), None, None, nz["eps_prior_img"].to(cuda),
+                                  None, nz["noise_act"].to(cuda), *wr, None, None, None, None, *wa))
+        assert cfg.precision == "bf16"
+        # gradient of a smooth functional of the imagined features (what the heads feed back)
+        cots = [torch.randn(o.shape, generator=g) for o in ro]
+        cots[0].zero_(); cots[1].zero_(); cots[4].zero_()      # heads see only stoch and deter
+        cg = torch.autograd.grad(co, wa, [c.to(cuda) for c in cots])
+    torch.cuda.synchronize()
+    names = ["mean", "std", "stoch", "deter", "action"]
+    errs = {nm: rel_err(a, b) for nm, a, b in zip(names, co, ro)}
+    assert max(errs.values()) < BF16_TOL, errs
+    assert max(errs.values()) > 0
+    rg = torch.autograd.grad(ro, [wd[k] for k in ak], [c.double() for c in cots])
+    gerrs = {k: rel_err(a, b) for k, a, b in zip(ak, cg, rg)}
+    tol = BF16_TOL if n * H >= 2048 else 2 * BF16_TOL
+    assert max(gerrs.values()) < tol, gerrs
+
+
+def test_rollout_policy_bf16_all_cotangents(cuda):
+    """Upstream gradients on every output (mean, std, stoch, deter, action), as RolloutFn allows."""
+    from oracle import dreamer_oracle as O
+    from dreamer_pytorch_b200 import _lib
+    from dreamer_pytorch_b200.functional import RolloutCfg, RolloutFn
+    from dreamer_pytorch_b200.precision import precision
+
+    A, S, D, Hd, n, H = 6, 30, 200, 200, 384, 6
+    w = O.make_weights(O.weight_shapes(A, S, D, Hd, 1024, "tanh_normal"), 51)
+    nz = O.make_noise(1, 1, n, H, S, A, 52, "tanh_normal")
+    g = torch.Generator().manual_seed(53)
+    start_s, start_h = torch.randn(n, S, generator=g), torch.tanh(torch.randn(n, D, generator=g))
+    TR = O.TR
+    rk = [TR + "_rnn_input_model.0.weight", TR + "_rnn_input_model.0.bias", TR + "_cell.weight_ih",
+          TR + "_cell.weight_hh", TR + "_cell.bias_ih", TR + "_cell.bias_hh",
+          TR + "_stochastic_prior_model.0.weight", TR + "_stochastic_prior_model.0.bias",
+          TR + "_stochastic_prior_model.2.weight", TR + "_stochastic_prior_model.2.bias"]
+    ak = [f"{O.ACT}{2 * i}.{p}" for i in range(4) for p in ("weight", "bias")]
+    wd = {k: v.double().requires_grad_(True) for k, v in w.items()}
+    imag, actions = O.rollout_policy(wd, H, start_s.double(), start_h.double(), nz["noise_act"].double(),
+                                     nz["eps_prior_img"].double(), "tanh_normal")
+    ro = list(imag) + [actions]
+    wr = [w[k].to(cuda) for k in rk]
+    wa = [w[k].to(cuda).requires_grad_(True) for k in ak]
+    cfg = RolloutCfg(_lib.MODE_POLICY, H, n, (A, S, D, Hd, 0), act_dist="tanh_normal")
+    cots = [torch.randn(o.shape, generator=g) for o in ro]
+    with precision("bf16"):
+        co = list(RolloutFn.apply(cfg, start_s.to(cuda), start_h.to(cuda), None, None, nz["eps_prior_img"].to(cuda),
+                                  None, nz["noise_act"].to(cuda), *wr, None, None, None, None, *wa))
+        cg = torch.autograd.grad(co, wa, [c.to(cuda) for c in cots])
+    rg = torch.autograd.grad(ro, [wd[k] for k in ak], [c.double() for c in cots])
+    gerrs = {k: rel_err(a, b) for k, a, b in zip(ak, cg, rg)}
+    assert max(gerrs.values()) < BF16_TOL, gerrs
