@@ -60,6 +60,7 @@ struct MlpTcDev {
     __nv_bfloat16* sx;                    // TCM image of the input, cin chunks per tile (or nullptr)
     __nv_bfloat16* sh[DRM_MAX_LINEAR];    // TCM images of the hidden activations, ch chunks per tile
     uint32_t act_off;                     // shared-memory offset of the activation buffer
+    uint32_t bias_off; int bstride;       // zero-padded fp32 bias blocks in shared memory: [n_linear][bstride]
     // backward only
     const float* dy; const float* dy_scale;
     float* dx0; float* dx1; int accumulate_dx;
@@ -75,6 +76,9 @@ struct MlpTcDev {
 __global__ void __launch_bounds__(kChainThreads, 1) mlp_fwd_tc_kernel(const __grid_constant__ MlpTcDev p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     ChainBars* bars = reinterpret_cast<ChainBars*>(smem);
+    float* sbias = reinterpret_cast<float*>(smem + p.bias_off);
+    for (int l = 0; l < p.n_linear; ++l)
+        fill_bias(sbias + l * p.bstride, p.b[l], nullptr, l == p.n_linear - 1 ? p.out_dim : p.hidden, p.bstride);
     const uint32_t tmem_base = chain_setup(bars, p.pg);
     const int warp = threadIdx.x >> 5;
     const int tiles = (p.M + kTileRows - 1) / kTileRows;
@@ -98,16 +102,8 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_fwd_tc_kernel(const __gr
 #pragma unroll
                 for (int i = 0; i < 8; ++i) v[i] = 0.f;
                 if (grow < p.M) {
-                    if (chunk < p.c0) {
-                        const float* src = p.x0 + (size_t)grow * p.ld0 + chunk * 8;
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) if (chunk * 8 + i < p.k0) v[i] = __ldg(src + i);
-                    } else if (chunk < p.c0 + p.c1) {
-                        const int cc = chunk - p.c0;
-                        const float* src = p.x1 + (size_t)grow * p.ld1 + cc * 8;
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) if (cc * 8 + i < p.k1) v[i] = __ldg(src + i);
-                    }
+                    if (chunk < p.c0) ldg_row8(p.x0 + (size_t)grow * p.ld0, chunk * 8, p.k0, v);
+                    else if (chunk < p.c0 + p.c1) ldg_row8(p.x1 + (size_t)grow * p.ld1, (chunk - p.c0) * 8, p.k1, v);
                 }
                 st_chunk_bf16(act + (size_t)idx * 16, v);
                 if (p.sx) st_chunk_bf16(p.sx + ((size_t)tile * p.cin * kTileRows + idx) * 8, v);
@@ -117,35 +113,20 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_fwd_tc_kernel(const __gr
             const bool live = grow < p.M;
             for (int l = 0; l <= last; ++l) {
                 es.wait_acc();
-                const float* bias = p.b[l];
+                const float* bias = sbias + l * p.bstride;
                 if (l < last) {
                     // hidden layer: h = ELU(acc + b) -> bf16 A operand of the next layer (in place) [+ TCM save]
                     const int per = (p.ch + kEpiGroups - 1) / kEpiGroups;
                     const int cbeg = grp * per, cend = min(p.ch, cbeg + per);
                     __nv_bfloat16* sv = p.sh[l];
-                    for (int c = cbeg; c < cend; c += 2) {
-                        float v0[8], v1[8];
-                        tmem_ld8(epi_taddr(tmem_base, c * 8), v0);
-                        const bool two = c + 1 < cend;
-                        if (two) tmem_ld8(epi_taddr(tmem_base, c * 8 + 8), v1);
-                        tmem_ld_wait();
+                    epi_for_chunks(tmem_base, 0, cbeg, cend, [&](int c, float (&v)[8]) {
+                        float b[8];
+                        lds8(bias + c * 8, b);
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            const int col = c * 8 + i;
-                            v0[i] = (live && col < p.hidden) ? elu_fast(v0[i] + __ldg(bias + col)) : 0.f;
-                        }
-                        st_chunk_bf16(act + ((size_t)c * kTileRows + row) * 16, v0);
-                        if (sv) st_chunk_bf16(tcm_at(sv, p.ch, tile, c, row), v0);
-                        if (two) {
-#pragma unroll
-                            for (int i = 0; i < 8; ++i) {
-                                const int col = c * 8 + 8 + i;
-                                v1[i] = (live && col < p.hidden) ? elu_fast(v1[i] + __ldg(bias + col)) : 0.f;
-                            }
-                            st_chunk_bf16(act + ((size_t)(c + 1) * kTileRows + row) * 16, v1);
-                            if (sv) st_chunk_bf16(tcm_at(sv, p.ch, tile, c + 1, row), v1);
-                        }
-                    }
+                        for (int i = 0; i < 8; ++i) v[i] = elu_fast(v[i] + b[i]);
+                        st_chunk_bf16(act + ((size_t)c * kTileRows + row) * 16, v);
+                        if (sv) st_chunk_bf16(tcm_at(sv, p.ch, tile, c, row), v);
+                    });
                     es.release();
                 } else {
                     // output layer: y = acc + b (fp32, row-major)
@@ -158,7 +139,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_fwd_tc_kernel(const __gr
 #pragma unroll
                             for (int i = 0; i < 8; ++i) {
                                 const int col = c * 8 + i;
-                                if (col < p.out_dim) p.y[(size_t)grow * p.out_dim + col] = v[i] + (bias ? __ldg(bias + col) : 0.f);
+                                if (col < p.out_dim) p.y[(size_t)grow * p.out_dim + col] = v[i] + bias[col];
                             }
                         }
                     }
@@ -224,40 +205,26 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_bwd_tc_kernel(const __gr
                 const int cbeg = grp * per, cend = min(p.ch, cbeg + per);
                 const __nv_bfloat16* hs = p.sh[l - 1];
                 __nv_bfloat16* dsv = p.dys[l - 1];
-                for (int c = cbeg; c < cend; ++c) {
-                    float v[8], h[8];
-                    tmem_ld8(epi_taddr(tmem_base, c * 8), v);
+                epi_for_chunks(tmem_base, 0, cbeg, cend, [&](int c, float (&v)[8]) {
+                    float h[8];
                     ld_chunk_bf16(tcm_at(hs, p.ch, tile, c, row), h);
-                    tmem_ld_wait();
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const int col = c * 8 + i;
-                        v[i] = (live && col < p.hidden) ? v[i] * (h[i] > 0.f ? 1.f : h[i] + 1.f) : 0.f;
-                    }
+                    for (int i = 0; i < 8; ++i) v[i] = live ? v[i] * (h[i] > 0.f ? 1.f : h[i] + 1.f) : 0.f;
                     st_chunk_bf16(act + ((size_t)c * kTileRows + row) * 16, v);
                     if (dsv) st_chunk_bf16(tcm_at(dsv, p.ch, tile, c, row), v);
-                }
+                });
                 if (l > 1 || want_dx) es.release();
             }
             if (want_dx) {
                 es.wait_acc();
-                const int nin = p.k0 + p.k1;
-                const int cin = (nin + 7) / 8;
-                for (int c = grp; c < cin; c += kEpiGroups) {
+                // accumulator columns: [x0: c0 chunks][x1: c1 chunks] (the dX weight image is laid out per segment)
+                for (int c = grp; c < p.c0 + p.c1; c += kEpiGroups) {
                     float v[8];
                     tmem_ld8(epi_taddr(tmem_base, c * 8), v);
                     tmem_ld_wait();
-                    if (live) {
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            const int col = c * 8 + i;
-                            if (col >= nin) continue;
-                            float* dst;
-                            if (col < p.k0) { if (!p.dx0) continue; dst = p.dx0 + (size_t)grow * p.ld0 + col; }
-                            else { if (!p.dx1) continue; dst = p.dx1 + (size_t)grow * p.ld1 + (col - p.k0); }
-                            *dst = p.accumulate_dx ? *dst + v[i] : v[i];
-                        }
-                    }
+                    if (!live) continue;
+                    if (c < p.c0) { if (p.dx0) stg_row8(p.dx0 + (size_t)grow * p.ld0, c * 8, p.k0, v, p.accumulate_dx != 0); }
+                    else if (p.dx1) stg_row8(p.dx1 + (size_t)grow * p.ld1, (c - p.c0) * 8, p.k1, v, p.accumulate_dx != 0);
                 }
             }
         }
@@ -291,7 +258,7 @@ static int plan_dims(const drm_mlp_call* c, MlpTcPlan& pl) {
     d.n_linear = m.n_linear; d.hidden = m.n_linear > 1 ? m.hidden : 0; d.ch = rup((d.hidden + 7) / 8, 2);
     d.out_dim = m.out_dim; d.cout = rup((m.out_dim + 7) / 8, 2);
     pl.tiles = (c->M + kTileRows - 1) / kTileRows;
-    DRM_REQUIRE(d.ch * 8 <= 512 && rup(m.out_dim, 16) <= 512 && rup(m.in_dim, 16) <= 512, DRM_E_SHAPE,
+    DRM_REQUIRE(d.ch * 8 <= 512 && rup(m.out_dim, 16) <= 512 && d.cin * 8 <= 512, DRM_E_SHAPE,
                 "layer wider than 512 is not supported by the bf16 path");
     pl.dev.pg.n_ops = 0;
     pl.jobs.n = 0;
@@ -331,7 +298,11 @@ static int add_phase(MlpTcPlan& pl, uint8_t* wbase, int kchunks, int npad, const
 static int finish_plan(MlpTcPlan& pl, int act_chunks) {
     MlpTcDev& d = pl.dev;
     TcProgram& pg = d.pg;
-    d.act_off = 1024;
+    d.bias_off = 256;
+    int widest = d.ch * 8;
+    if (rup(d.out_dim, 16) > widest) widest = rup(d.out_dim, 16);
+    d.bstride = widest;
+    d.act_off = (uint32_t)rup_sz(d.bias_off + (size_t)d.n_linear * d.bstride * sizeof(float), 1024);
     pg.stage_off = (uint32_t)rup_sz(d.act_off + (size_t)act_chunks * kChunkBytes, 1024);
     pg.stage_bytes = 32 * 1024;
     int stages = (int)(((size_t)kMaxSmem - pg.stage_off) / pg.stage_bytes);
@@ -379,8 +350,25 @@ static int plan_bwd(const drm_mlp_call* c, bool want_dx, uint8_t* wbase, MlpTcPl
     if (want_dx) {
         const int rows0 = m.n_linear == 1 ? m.out_dim : m.hidden;
         const int ks[1] = {0}, len[1] = {rows0}, s0[1] = {0};
-        rc = add_phase(pl, wbase, m.n_linear == 1 ? d.cout : d.ch, rup(m.in_dim, 16), m.W[0], m.in_dim, 1, m.in_dim, 1, ks, len, s0);
+        rc = add_phase(pl, wbase, m.n_linear == 1 ? d.cout : d.ch, d.cin * 8, m.W[0], m.in_dim, 1, c->k0, 1, ks, len, s0);
         if (rc) return rc;
+        // second N segment: x1's columns start at accumulator column c0 * 8
+        {
+            int q0 = pl.jobs.n - (d.cin * 8 > 256 ? 2 : 1);
+            int n0 = 0;
+            for (int q = q0; q < pl.jobs.n; ++q) {
+                PackTcJob& j = pl.jobs.j[q];
+                // image row n (global accumulator column n0 + n) <- source column: x0 part [0,k0) at cols [0,k0),
+                // x1 part [k0,k0+k1) at cols [c0*8, c0*8+k1)
+                const int lo = n0, hi = n0 + j.n_pad;
+                int v0 = c->k0 - lo; if (v0 < 0) v0 = 0; if (v0 > j.n_pad) v0 = j.n_pad;
+                j.n0 = lo; j.n_valid = v0;                       // columns of x0 inside this part
+                int s1 = d.c0 * 8 > lo ? d.c0 * 8 : lo;            // first x1 accumulator column inside this part
+                int e1 = d.c0 * 8 + c->k1 < hi ? d.c0 * 8 + c->k1 : hi;
+                if (e1 > s1) { j.n2_start = s1 - lo; j.n2_valid = e1 - s1; j.n2_src0 = c->k0 + (s1 - d.c0 * 8); }
+                n0 += j.n_pad;
+            }
+        }
     }
     return finish_plan(pl, d.cout > d.ch ? d.cout : d.ch);
 }

@@ -41,7 +41,7 @@ struct RollTcDev {
     __nv_bfloat16* sv_hid;                  // prior hidden                              (chh)
     float* sv_raw;                          // actor output before the distribution, fp32 [T*n][Aout]
     const uint8_t* wstream;
-    uint32_t st_off, hb_off;
+    uint32_t st_off, hb_off, bias_off;
     // backward
     const float *g_prior_mean, *g_prior_std, *g_prior_stoch, *g_deter, *g_action_out;
     __nv_bfloat16* dys_a[DRM_MAX_LINEAR];   // dY of every actor Linear, TCM by tile-step (cha chunks; 2 for the last)
@@ -55,9 +55,34 @@ struct RollTcDev {
 // ------------------------------------------------------------------------------------------------
 // forward kernel
 // ------------------------------------------------------------------------------------------------
+// zero-padded fp32 bias blocks in shared memory (floats from bias_off)
+struct BiasLayout {
+    int ba0, ba_last, in, r, hn, n, z, p1, p2m, p2s, total;
+};
+__host__ __device__ inline BiasLayout bias_layout(int an, int Ap, int Hp, int Dp, int Sp) {
+    BiasLayout b;
+    b.ba0 = 0; b.ba_last = (an - 1) * Ap; b.in = b.ba_last + 16; b.r = b.in + Hp; b.hn = b.r + Dp; b.n = b.hn + Dp;
+    b.z = b.n + Dp; b.p1 = b.z + Dp; b.p2m = b.p1 + Hp; b.p2s = b.p2m + Sp; b.total = b.p2s + Sp;
+    return b;
+}
+
 __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const __grid_constant__ RollTcDev p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     ChainBars* bars = reinterpret_cast<ChainBars*>(smem);
+    const int S = p.S, D = p.D, A = p.A;
+    const int Dp = p.cdp * 8, Hp = p.chh * 8, Ap = p.cha * 8;
+    float* sbias = reinterpret_cast<float*>(smem + p.bias_off);
+    const BiasLayout bl = bias_layout(p.an, Ap, Hp, Dp, p.Sp);
+    for (int l = 0; l < p.an - 1; ++l) fill_bias(sbias + bl.ba0 + l * Ap, p.ba[l], nullptr, p.ah, Ap);
+    fill_bias(sbias + bl.ba_last, p.ba[p.an - 1], nullptr, p.Aout, 16);
+    fill_bias(sbias + bl.in, p.b_in, nullptr, p.Hd, Hp);
+    fill_bias(sbias + bl.r, p.b_ih, p.b_hh, D, Dp);
+    fill_bias(sbias + bl.hn, p.b_hh + 2 * D, nullptr, D, Dp);
+    fill_bias(sbias + bl.n, p.b_ih + 2 * D, nullptr, D, Dp);
+    fill_bias(sbias + bl.z, p.b_ih + D, p.b_hh + D, D, Dp);
+    fill_bias(sbias + bl.p1, p.b_p1, nullptr, p.Hd, Hp);
+    fill_bias(sbias + bl.p2m, p.b_p2, nullptr, S, p.Sp);
+    fill_bias(sbias + bl.p2s, p.b_p2 + S, nullptr, S, p.Sp);
     const uint32_t tmem_base = chain_setup(bars, p.pg);
     const int warp = threadIdx.x >> 5;
     const int my_tiles = (int)blockIdx.x < p.ntiles ? (p.ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
@@ -71,10 +96,13 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
         uint8_t* st = smem + p.st_off;
         uint8_t* hb = smem + p.hb_off;
         const int row = epi_row(), grp = epi_group();
-        const int S = p.S, D = p.D, A = p.A;
-        const int Dp = p.cdp * 8;
         const int cfeat = p.cs + p.cdp;
         const bool save = p.training != 0;
+        // this thread's chunk ranges for the three operand widths
+        const int per_a = (p.cha + kEpiGroups - 1) / kEpiGroups, a_beg = grp * per_a, a_end = min(p.cha, a_beg + per_a);
+        const int per_h = (p.chh + kEpiGroups - 1) / kEpiGroups, h_beg = grp * per_h, h_end = min(p.chh, h_beg + per_h);
+        const int per_d = (p.cdp + kEpiGroups - 1) / kEpiGroups, d_beg = grp * per_d, d_end = min(p.cdp, d_beg + per_d);
+        const int per_s = (p.cs + kEpiGroups - 1) / kEpiGroups, s_beg = grp * per_s, s_end = min(p.cs, s_beg + per_s);
         for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
             const int row0 = tile * kTileRows;
             const int grow = row0 + row;
@@ -87,14 +115,8 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
 #pragma unroll
                 for (int i = 0; i < 8; ++i) v[i] = 0.f;
                 if (gr < p.n) {
-                    if (chunk < p.cs) {
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) if (chunk * 8 + i < S) v[i] = __ldg(p.start_stoch + (size_t)gr * S + chunk * 8 + i);
-                    } else if (chunk < p.cs + p.cd) {
-                        const int cc = chunk - p.cs;
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) if (cc * 8 + i < D) v[i] = __ldg(p.start_deter + (size_t)gr * D + cc * 8 + i);
-                    }
+                    if (chunk < p.cs) ldg_row8(p.start_stoch + (size_t)gr * S, chunk * 8, S, v);
+                    else if (chunk < p.cs + p.cd) ldg_row8(p.start_deter + (size_t)gr * D, (chunk - p.cs) * 8, D, v);
                 }
                 st_chunk_bf16(st + (size_t)idx * 16, v);
                 if (save && chunk < cfeat) st_chunk_bf16(p.sv_feat + ((size_t)tile * cfeat * kTileRows + idx) * 8, v);
@@ -106,21 +128,16 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                 // ------------------------------------------------------------ actor hidden layers
                 for (int l = 0; l < p.an - 1; ++l) {
                     es.wait_acc();
-                    const float* bias = p.ba[l];
-                    const int per = (p.cha + kEpiGroups - 1) / kEpiGroups;
-                    const int cbeg = grp * per, cend = min(p.cha, cbeg + per);
-                    for (int c = cbeg; c < cend; ++c) {
-                        float v[8];
-                        tmem_ld8(epi_taddr(tmem_base, c * 8), v);
-                        tmem_ld_wait();
+                    const float* bias = sbias + bl.ba0 + l * Ap;
+                    __nv_bfloat16* sv = save ? p.sv_ah[l] : nullptr;
+                    epi_for_chunks(tmem_base, 0, a_beg, a_end, [&](int c, float (&v)[8]) {
+                        float b[8];
+                        lds8(bias + c * 8, b);
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            const int col = c * 8 + i;
-                            v[i] = (live && col < p.ah) ? elu_fast(v[i] + __ldg(bias + col)) : 0.f;
-                        }
+                        for (int i = 0; i < 8; ++i) v[i] = elu_fast(v[i] + b[i]);
                         st_chunk_bf16(hb + ((size_t)c * kTileRows + row) * 16, v);
-                        if (save) st_chunk_bf16(tcm_at(p.sv_ah[l], p.cha, ts, c, row), v);
-                    }
+                        if (sv) st_chunk_bf16(tcm_at(sv, p.cha, ts, c, row), v);
+                    });
                     es.release();
                 }
                 // ------------------------------------------------------------ actor output + action (agent.py:101-117)
@@ -128,16 +145,14 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                 if (grp == 0) {
                     float raw[16];
                     {
-                        float v0[8], v1[8];
+                        float v0[8], v1[8], b0[8], b1[8];
                         tmem_ld8(epi_taddr(tmem_base, 0), v0);
                         tmem_ld8(epi_taddr(tmem_base, 8), v1);
+                        lds8(sbias + bl.ba_last, b0);
+                        lds8(sbias + bl.ba_last + 8, b1);
                         tmem_ld_wait();
-                        const float* bias = p.ba[p.an - 1];
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            raw[i] = i < p.Aout ? v0[i] + __ldg(bias + i) : 0.f;
-                            raw[8 + i] = 8 + i < p.Aout ? v1[i] + __ldg(bias + 8 + i) : 0.f;
-                        }
+                        for (int i = 0; i < 8; ++i) { raw[i] = v0[i] + b0[i]; raw[8 + i] = v1[i] + b1[i]; }
                     }
                     float act[16];
 #pragma unroll
@@ -206,70 +221,76 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                 // ------------------------------------------------------------ x = ELU(W_in [a|stoch] + b)   (rnns.py:99-101)
                 es.wait_acc();
                 {
-                    const int per = (p.chh + kEpiGroups - 1) / kEpiGroups;
-                    const int cbeg = grp * per, cend = min(p.chh, cbeg + per);
-                    for (int c = cbeg; c < cend; ++c) {
-                        float v[8];
-                        tmem_ld8(epi_taddr(tmem_base, c * 8), v);
-                        tmem_ld_wait();
+                    const float* bias = sbias + bl.in;
+                    __nv_bfloat16* sv = save ? p.sv_x : nullptr;
+                    epi_for_chunks(tmem_base, 0, h_beg, h_end, [&](int c, float (&v)[8]) {
+                        float b[8];
+                        lds8(bias + c * 8, b);
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            const int col = c * 8 + i;
-                            v[i] = (live && col < p.Hd) ? elu_fast(v[i] + __ldg(p.b_in + col)) : 0.f;
-                        }
+                        for (int i = 0; i < 8; ++i) v[i] = elu_fast(v[i] + b[i]);
                         st_chunk_bf16(hb + ((size_t)c * kTileRows + row) * 16, v);
-                        if (save) st_chunk_bf16(tcm_at(p.sv_x, p.chh, ts, c, row), v);
-                    }
+                        if (sv) st_chunk_bf16(tcm_at(sv, p.chh, ts, c, row), v);
+                    });
                 }
                 es.release();
                 // ------------------------------------------------------------ GRU, part 1: r and h_n  (torch GRUCell, rnns.py:102)
                 es.wait_acc();
-                {
-                    const int per = (p.cdp + kEpiGroups - 1) / kEpiGroups;
-                    const int cbeg = grp * per, cend = min(p.cdp, cbeg + per);
-                    for (int c = cbeg; c < cend; ++c) {
-                        float ar[8], ah_[8], rr[8], hn[8];
-                        tmem_ld8(epi_taddr(tmem_base, c * 8), ar);
-                        tmem_ld8(epi_taddr(tmem_base, Dp + c * 8), ah_);
-                        tmem_ld_wait();
+                epi_for_chunks2(tmem_base, 0, Dp, d_beg, d_end, [&](int c, float (&ar)[8], float (&ahn)[8]) {
+                    float br[8], bh[8], rr[8], hn[8];
+                    lds8(sbias + bl.r + c * 8, br);
+                    lds8(sbias + bl.hn + c * 8, bh);
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            const int col = c * 8 + i;
-                            const bool ok = live && col < D;
-                            rr[i] = ok ? sigmoid_fast(ar[i] + __ldg(p.b_ih + col) + __ldg(p.b_hh + col)) : 0.f;
-                            hn[i] = ok ? ah_[i] + __ldg(p.b_hh + 2 * D + col) : 0.f;
-                            ar[i] = rr[i] * hn[i];
-                        }
-                        tmem_st8(epi_taddr(tmem_base, c * 8), ar);  // i_n is accumulated on top of r * h_n by the next phase
-                        if (save) {
-                            st_chunk_bf16(tcm_at(p.sv_r, p.cdp, ts, c, row), rr);
-                            st_chunk_bf16(tcm_at(p.sv_hn, p.cdp, ts, c, row), hn);
-                        }
+                    for (int i = 0; i < 8; ++i) {
+                        rr[i] = sigmoid_fast(ar[i] + br[i]);  // pad columns: r = 0.5, h_n = 0
+                        hn[i] = ahn[i] + bh[i];
+                        ar[i] = rr[i] * hn[i];
                     }
-                    tmem_st_wait();
-                }
+                    tmem_st8(epi_taddr(tmem_base, c * 8), ar);  // i_n is accumulated on top of r * h_n by the next phase
+                    if (save) {
+                        st_chunk_bf16(tcm_at(p.sv_r, p.cdp, ts, c, row), rr);
+                        st_chunk_bf16(tcm_at(p.sv_hn, p.cdp, ts, c, row), hn);
+                    }
+                });
+                tmem_st_wait();
                 es.release();
                 // ------------------------------------------------------------ GRU, part 2: n, z, h'
                 es.wait_acc();
                 {
-                    const int per = (p.cdp + kEpiGroups - 1) / kEpiGroups;
-                    const int cbeg = grp * per, cend = min(p.cdp, cbeg + per);
                     const float* hprev = t == 0 ? p.start_deter + (size_t)grow * D : p.deter + (trow - p.n) * D;
                     const bool feat_next = save && t + 1 < p.T;
-                    for (int c = cbeg; c < cend; ++c) {
-                        float an_[8], az[8], zz[8], nn[8], hv[8];
-                        tmem_ld8(epi_taddr(tmem_base, c * 8), an_);
-                        tmem_ld8(epi_taddr(tmem_base, Dp + c * 8), az);
-                        tmem_ld_wait();
+                    const bool vec = (D & 3) == 0;
+                    epi_for_chunks2(tmem_base, 0, Dp, d_beg, d_end, [&](int c, float (&an_)[8], float (&az)[8]) {
+                        float bn[8], bz[8], zz[8], nn[8], hv[8], hp[8];
+                        lds8(sbias + bl.n + c * 8, bn);
+                        lds8(sbias + bl.z + c * 8, bz);
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) hp[i] = 0.f;
+                        if (live) {
+                            // plain (coherent) loads: deter[t-1] was written by this very thread one step ago
+                            if (vec && c * 8 + 8 <= D) {
+                                const float4 lo = *reinterpret_cast<const float4*>(hprev + c * 8);
+                                const float4 hi = *reinterpret_cast<const float4*>(hprev + c * 8 + 4);
+                                hp[0] = lo.x; hp[1] = lo.y; hp[2] = lo.z; hp[3] = lo.w; hp[4] = hi.x; hp[5] = hi.y; hp[6] = hi.z; hp[7] = hi.w;
+                            } else {
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) if (c * 8 + i < D) hp[i] = hprev[c * 8 + i];
+                            }
+                        }
 #pragma unroll
                         for (int i = 0; i < 8; ++i) {
-                            const int col = c * 8 + i;
-                            const bool ok = live && col < D;
-                            nn[i] = ok ? tanh_fast(an_[i] + __ldg(p.b_ih + 2 * D + col)) : 0.f;
-                            zz[i] = ok ? sigmoid_fast(az[i] + __ldg(p.b_ih + D + col) + __ldg(p.b_hh + D + col)) : 0.f;
-                            const float hp = ok ? hprev[col] : 0.f;
-                            hv[i] = ok ? (1.f - zz[i]) * nn[i] + zz[i] * hp : 0.f;
-                            if (ok) p.deter[trow * D + col] = hv[i];
+                            nn[i] = tanh_fast(an_[i] + bn[i]);     // pad columns: n = 0, z = 0.5, h' = 0.5 * 0
+                            zz[i] = sigmoid_fast(az[i] + bz[i]);
+                            hv[i] = fmaf(zz[i], hp[i] - nn[i], nn[i]);  // (1-z) n + z h
+                        }
+                        if (live) {
+                            float* dst = p.deter + trow * D + c * 8;
+                            if (vec && c * 8 + 8 <= D) {
+                                *reinterpret_cast<float4*>(dst) = make_float4(hv[0], hv[1], hv[2], hv[3]);
+                                *reinterpret_cast<float4*>(dst + 4) = make_float4(hv[4], hv[5], hv[6], hv[7]);
+                            } else {
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) if (c * 8 + i < D) dst[i] = hv[i];
+                            }
                         }
                         st_chunk_bf16(st + ((size_t)(p.cs + c) * kTileRows + row) * 16, hv);
                         if (save) {
@@ -277,47 +298,39 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                             st_chunk_bf16(tcm_at(p.sv_n, p.cdp, ts, c, row), nn);
                         }
                         if (feat_next) st_chunk_bf16(tcm_at(p.sv_feat, cfeat, ts + p.ntiles, p.cs + c, row), hv);
-                    }
+                    });
                 }
                 es.release();
                 // ------------------------------------------------------------ prior hidden  (rnns.py:103)
                 es.wait_acc();
                 {
-                    const int per = (p.chh + kEpiGroups - 1) / kEpiGroups;
-                    const int cbeg = grp * per, cend = min(p.chh, cbeg + per);
-                    for (int c = cbeg; c < cend; ++c) {
-                        float v[8];
-                        tmem_ld8(epi_taddr(tmem_base, c * 8), v);
-                        tmem_ld_wait();
+                    const float* bias = sbias + bl.p1;
+                    __nv_bfloat16* sv = save ? p.sv_hid : nullptr;
+                    epi_for_chunks(tmem_base, 0, h_beg, h_end, [&](int c, float (&v)[8]) {
+                        float b[8];
+                        lds8(bias + c * 8, b);
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            const int col = c * 8 + i;
-                            v[i] = (live && col < p.Hd) ? elu_fast(v[i] + __ldg(p.b_p1 + col)) : 0.f;
-                        }
+                        for (int i = 0; i < 8; ++i) v[i] = elu_fast(v[i] + b[i]);
                         st_chunk_bf16(hb + ((size_t)c * kTileRows + row) * 16, v);
-                        if (save) st_chunk_bf16(tcm_at(p.sv_hid, p.chh, ts, c, row), v);
-                    }
+                        if (sv) st_chunk_bf16(tcm_at(sv, p.chh, ts, c, row), v);
+                    });
                 }
                 es.release();
                 // ------------------------------------------------------------ prior mean | std, sample  (rnns.py:103-106)
                 es.wait_acc();
                 {
-                    const int per = (p.cs + kEpiGroups - 1) / kEpiGroups;
-                    const int cbeg = grp * per, cend = min(p.cs, cbeg + per);
                     const bool feat_next = save && t + 1 < p.T;
-                    for (int c = cbeg; c < cend; ++c) {
-                        float am[8], as_[8], sv[8];
-                        tmem_ld8(epi_taddr(tmem_base, c * 8), am);
-                        tmem_ld8(epi_taddr(tmem_base, p.Sp + c * 8), as_);
-                        tmem_ld_wait();
+                    epi_for_chunks2(tmem_base, 0, p.Sp, s_beg, s_end, [&](int c, float (&am)[8], float (&as_)[8]) {
+                        float bm[8], bs[8], sv[8];
+                        lds8(sbias + bl.p2m + c * 8, bm);
+                        lds8(sbias + bl.p2s + c * 8, bs);
 #pragma unroll
                         for (int i = 0; i < 8; ++i) {
                             const int j = c * 8 + i;
-                            const bool ok = live && j < S;
                             float st_ = 0.f;
-                            if (ok) {
-                                const float mean = am[i] + __ldg(p.b_p2 + j);
-                                const float std = softplus_fast(as_[i] + __ldg(p.b_p2 + S + j)) + p.min_std;
+                            if (live && j < S) {
+                                const float mean = am[i] + bm[i];
+                                const float std = softplus_fast(as_[i] + bs[i]) + p.min_std;
                                 const size_t o = trow * S + j;
                                 st_ = fmaf(std, __ldg(p.eps_prior + o), mean);
                                 p.prior_mean[o] = mean; p.prior_std[o] = std; p.prior_stoch[o] = st_;
@@ -326,7 +339,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                         }
                         st_chunk_bf16(st + ((size_t)c * kTileRows + row) * 16, sv);
                         if (feat_next) st_chunk_bf16(tcm_at(p.sv_feat, cfeat, ts + p.ntiles, c, row), sv);
-                    }
+                    });
                 }
                 if (t + 1 < p.T) es.release();
             }
@@ -421,15 +434,13 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                 {
                     const int per = (p.chh + kEpiGroups - 1) / kEpiGroups;
                     const int cbeg = grp * per, cend = min(p.chh, cbeg + per);
-                    for (int c = cbeg; c < cend; ++c) {
-                        float v[8], h[8];
-                        tmem_ld8(epi_taddr(tmem_base, c * 8), v);
+                    epi_for_chunks(tmem_base, 0, cbeg, cend, [&](int c, float (&v)[8]) {
+                        float h[8];
                         ld_chunk_bf16(tcm_at(p.sv_hid, p.chh, ts, c, row), h);
-                        tmem_ld_wait();
 #pragma unroll
                         for (int i = 0; i < 8; ++i) v[i] = live ? v[i] * (h[i] > 0.f ? 1.f : h[i] + 1.f) : 0.f;
                         st_chunk_bf16(ga + ((size_t)c * kTileRows + row) * 16, v);
-                    }
+                    });
                 }
                 es.release();
                 // ------------------------------------------------------------ GRU cell (pointwise)
@@ -438,20 +449,26 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                     const int per = (p.cdp + kEpiGroups - 1) / kEpiGroups;
                     const int cbeg = grp * per, cend = min(p.cdp, cbeg + per);
                     const float* hprev = t == 0 ? p.start_deter + (size_t)grow * D : p.deter + (trow - p.n) * D;
-                    for (int c = cbeg; c < cend; ++c) {
-                        float dh[8], rr[8], zz[8], nn[8], hn[8], dpr[8], dpz[8], din[8], dhn[8];
-                        tmem_ld8(epi_taddr(tmem_base, colC + c * 8), dh);
+                    const bool vec = (D & 3) == 0;
+                    epi_for_chunks(tmem_base, colC, cbeg, cend, [&](int c, float (&dh)[8]) {
+                        float rr[8], zz[8], nn[8], hn[8], dpr[8], dpz[8], din[8], dhn[8], gd[8], hpv[8];
                         ld_chunk_bf16(tcm_at(p.sv_r, p.cdp, ts, c, row), rr);
                         ld_chunk_bf16(tcm_at(p.sv_z, p.cdp, ts, c, row), zz);
                         ld_chunk_bf16(tcm_at(p.sv_n, p.cdp, ts, c, row), nn);
                         ld_chunk_bf16(tcm_at(p.sv_hn, p.cdp, ts, c, row), hn);
-                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) { gd[i] = 0.f; hpv[i] = 0.f; }
+                        if (live) {
+                            ldg_row8(hprev, c * 8, D, hpv);
+                            if (p.g_deter) ldg_row8(p.g_deter + trow * D, c * 8, D, gd);
+                        }
+                        (void)vec;
 #pragma unroll
                         for (int i = 0; i < 8; ++i) {
                             const int col = c * 8 + i;
                             const bool ok = live && col < D;
-                            float d = ok ? dh[i] + (p.g_deter ? p.g_deter[trow * D + col] : 0.f) : 0.f;
-                            const float hp = ok ? hprev[col] : 0.f;
+                            float d = ok ? dh[i] + gd[i] : 0.f;
+                            const float hp = hpv[i];
                             const float dn = d * (1.f - zz[i]);
                             const float dz = d * (hp - nn[i]);
                             const float dpn = dn * (1.f - nn[i] * nn[i]);
@@ -466,7 +483,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                         st_chunk_bf16(gb + ((size_t)c * kTileRows + row) * 16, dpz);
                         st_chunk_bf16(stash_in + ((size_t)c * kTileRows + row) * 8, din);
                         st_chunk_bf16(stash_hn + ((size_t)c * kTileRows + row) * 8, dhn);
-                    }
+                    });
                     tmem_st_wait();
                 }
                 es.release();
@@ -488,15 +505,13 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                 {
                     const int per = (p.chh + kEpiGroups - 1) / kEpiGroups;
                     const int cbeg = grp * per, cend = min(p.chh, cbeg + per);
-                    for (int c = cbeg; c < cend; ++c) {
-                        float v[8], h[8];
-                        tmem_ld8(epi_taddr(tmem_base, c * 8), v);
+                    epi_for_chunks(tmem_base, 0, cbeg, cend, [&](int c, float (&v)[8]) {
+                        float h[8];
                         ld_chunk_bf16(tcm_at(p.sv_x, p.chh, ts, c, row), h);
-                        tmem_ld_wait();
 #pragma unroll
                         for (int i = 0; i < 8; ++i) v[i] = live ? v[i] * (h[i] > 0.f ? 1.f : h[i] + 1.f) : 0.f;
                         st_chunk_bf16(ga + ((size_t)c * kTileRows + row) * 16, v);
-                    }
+                    });
                 }
                 es.release();
                 // ------------------------------------------------------------ d [stoch | action] is in R_AS now
@@ -570,16 +585,14 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                         es.wait_acc();
                         const int per = (p.cha + kEpiGroups - 1) / kEpiGroups;
                         const int cbeg = grp * per, cend = min(p.cha, cbeg + per);
-                        for (int c = cbeg; c < cend; ++c) {
-                            float v[8], h[8];
-                            tmem_ld8(epi_taddr(tmem_base, c * 8), v);
+                        epi_for_chunks(tmem_base, 0, cbeg, cend, [&](int c, float (&v)[8]) {
+                            float h[8];
                             ld_chunk_bf16(tcm_at(p.sv_ah[l - 1], p.cha, ts, c, row), h);
-                            tmem_ld_wait();
 #pragma unroll
                             for (int i = 0; i < 8; ++i) v[i] = live ? v[i] * (h[i] > 0.f ? 1.f : h[i] + 1.f) : 0.f;
                             st_chunk_bf16(ga + ((size_t)c * kTileRows + row) * 16, v);
                             st_chunk_bf16(tcm_at(p.dys_a[l - 1], p.cha, ts, c, row), v);
-                        }
+                        });
                         if (l > 1) es.release();
                     }
                 }
@@ -664,7 +677,9 @@ struct ProgBuilder {
 
 static int finish_smem(RollTcDev& d, size_t& smem_bytes) {
     TcProgram& pg = d.pg;
-    d.st_off = 1024;
+    d.bias_off = 256;
+    const BiasLayout bl = bias_layout(d.an, d.cha * 8, d.chh * 8, d.cdp * 8, d.Sp);
+    d.st_off = (uint32_t)rup_sz(d.bias_off + (size_t)bl.total * sizeof(float), 1024);
     d.hb_off = d.st_off + (uint32_t)(d.cs + d.cdp + d.ca) * kChunkBytes;
     const int hb_chunks = d.chh > d.cha ? d.chh : d.cha;
     pg.stage_off = (uint32_t)rup_sz(d.hb_off + (size_t)hb_chunks * kChunkBytes, 1024);

@@ -22,7 +22,7 @@ namespace drm {
 namespace tc {
 
 constexpr int kTileRows = 128;
-constexpr int kEpiWarps = 8;
+constexpr int kEpiWarps = 16;  // 4 per scheduler: the epilogues are latency bound, not issue bound
 constexpr int kEpiThreads = kEpiWarps * 32;
 constexpr int kChainThreads = kEpiThreads + 64;
 constexpr int kMaxOps = 24;
@@ -79,7 +79,7 @@ __device__ __forceinline__ uint32_t chain_setup(ChainBars* bars, const TcProgram
             mbar_init(&bars->empty[s], 1);
         }
         mbar_init(&bars->acc_full, 1);
-        mbar_init(&bars->a_ready, kEpiThreads);
+        mbar_init(&bars->a_ready, kEpiWarps);
         fence_barrier_init();
     }
     if (warp == kEpiWarps) tmem_alloc(&bars->tmem_slot, kTmemCols);
@@ -183,7 +183,8 @@ struct EpiSync {
     __device__ __forceinline__ void release() {
         fence_proxy_async_smem();
         tc_fence_before_sync();
-        mbar_arrive(&bars->a_ready);
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) mbar_arrive(&bars->a_ready);
     }
 };
 
@@ -195,9 +196,101 @@ __device__ __forceinline__ uint32_t epi_taddr(uint32_t tmem_base, int col) {
     return tmem_base + ((uint32_t)(32 * ((threadIdx.x >> 5) & 3)) << 16) + (uint32_t)col;
 }
 
+// Walks this thread's accumulator chunks [cbeg, cend) of the region starting at TMEM column col0, four chunks
+// (32 columns) per tcgen05.wait::ld so that the TMEM loads and the pointwise math of a batch overlap.
+// f(chunk, v[8]) is called for every chunk.
+template <class F>
+__device__ __forceinline__ void epi_for_chunks(uint32_t tmem_base, int col0, int cbeg, int cend, F&& f) {
+    for (int c = cbeg; c < cend; c += 2) {
+        float v[2][8];
+        const bool two = c + 1 < cend;
+        tmem_ld8(epi_taddr(tmem_base, col0 + c * 8), v[0]);
+        if (two) tmem_ld8(epi_taddr(tmem_base, col0 + c * 8 + 8), v[1]);
+        tmem_ld_wait();
+        f(c, v[0]);
+        if (two) f(c + 1, v[1]);
+    }
+}
+// Same for two accumulator regions read together (two chunks of each per wait).
+template <class F>
+__device__ __forceinline__ void epi_for_chunks2(uint32_t tmem_base, int colA, int colB, int cbeg, int cend, F&& f) {
+    for (int c = cbeg; c < cend; ++c) {
+        float a[8], b[8];
+        tmem_ld8(epi_taddr(tmem_base, colA + c * 8), a);
+        tmem_ld8(epi_taddr(tmem_base, colB + c * 8), b);
+        tmem_ld_wait();
+        f(c, a, b);
+    }
+}
+// 8 consecutive fp32 values from a 32-byte aligned shared-memory vector (bias blocks are zero padded)
+__device__ __forceinline__ void lds8(const float* src, float (&b)[8]) {
+    const float4 lo = *reinterpret_cast<const float4*>(src);
+    const float4 hi = *reinterpret_cast<const float4*>(src + 4);
+    b[0] = lo.x; b[1] = lo.y; b[2] = lo.z; b[3] = lo.w; b[4] = hi.x; b[5] = hi.y; b[6] = hi.z; b[7] = hi.w;
+}
+// v[0..8) = row[k .. k+8) of an fp32 row with `kvalid` real columns (zero beyond), widest aligned loads possible.
+__device__ __forceinline__ void ldg_row8(const float* __restrict__ row, int k, int kvalid, float (&v)[8]) {
+    const float* src = row + k;
+    if (k + 8 <= kvalid) {
+        const uintptr_t a = reinterpret_cast<uintptr_t>(src);
+        if ((a & 15) == 0) {
+            const float4 lo = __ldg(reinterpret_cast<const float4*>(src));
+            const float4 hi = __ldg(reinterpret_cast<const float4*>(src) + 1);
+            v[0] = lo.x; v[1] = lo.y; v[2] = lo.z; v[3] = lo.w; v[4] = hi.x; v[5] = hi.y; v[6] = hi.z; v[7] = hi.w;
+            return;
+        }
+        if ((a & 7) == 0) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float2 q = __ldg(reinterpret_cast<const float2*>(src) + i);
+                v[2 * i] = q.x; v[2 * i + 1] = q.y;
+            }
+            return;
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] = (k + i < kvalid) ? __ldg(src + i) : 0.f;
+}
+
+// row[k .. k+8) (=|+=) v[0..8) for the columns below kvalid, widest aligned accesses possible.
+__device__ __forceinline__ void stg_row8(float* row, int k, int kvalid, const float (&v)[8], bool accumulate) {
+    float* dst = row + k;
+    const uintptr_t a = reinterpret_cast<uintptr_t>(dst);
+    if (k + 8 <= kvalid && (a & 15) == 0) {
+        float4 lo = make_float4(v[0], v[1], v[2], v[3]), hi = make_float4(v[4], v[5], v[6], v[7]);
+        if (accumulate) {
+            const float4 o0 = *reinterpret_cast<const float4*>(dst), o1 = *reinterpret_cast<const float4*>(dst + 4);
+            lo.x += o0.x; lo.y += o0.y; lo.z += o0.z; lo.w += o0.w; hi.x += o1.x; hi.y += o1.y; hi.z += o1.z; hi.w += o1.w;
+        }
+        *reinterpret_cast<float4*>(dst) = lo;
+        *reinterpret_cast<float4*>(dst + 4) = hi;
+        return;
+    }
+    if ((a & 7) == 0) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (k + 2 * i + 1 < kvalid) {
+                float2 q = make_float2(v[2 * i], v[2 * i + 1]);
+                if (accumulate) { const float2 o = *reinterpret_cast<const float2*>(dst + 2 * i); q.x += o.x; q.y += o.y; }
+                *reinterpret_cast<float2*>(dst + 2 * i) = q;
+            } else if (k + 2 * i < kvalid) {
+                dst[2 * i] = accumulate ? dst[2 * i] + v[2 * i] : v[2 * i];
+            }
+        }
+        return;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) if (k + i < kvalid) dst[i] = accumulate ? dst[i] + v[i] : v[i];
+}
+
+// Cooperative fill of a zero-padded bias block in shared memory: dst[i] = i < n ? a[i] (+ b[i]) : 0 for i < npad.
+__device__ __forceinline__ void fill_bias(float* dst, const float* a, const float* b, int n, int npad) {
+    for (int i = threadIdx.x; i < npad; i += blockDim.x) dst[i] = i < n ? (a ? a[i] : 0.f) + (b ? b[i] : 0.f) : 0.f;
+}
+
 // ---------------------------------------------------------------------------------------------- fast pointwise math
 // (bf16 path only: the operands of the next GEMM are rounded to 8 bits of mantissa anyway)
-__device__ __forceinline__ float elu_fast(float x) { return x > 0.f ? x : __expf(x) - 1.f; }
+__device__ __forceinline__ float elu_fast(float x) { return fmaxf(x, 0.f) + (__expf(fminf(x, 0.f)) - 1.f); }
 __device__ __forceinline__ float tanh_fast(float x) {
     float y;
     asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
