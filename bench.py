@@ -59,7 +59,8 @@ def flops_per_state(w, ah=200, al=3, vh=200, vl=3, rh=300, rl=3, ph=200, pl=3):
     bwd = f_tr + 2 * f_pol + f_rew + f_val + 2 * f_val + f_pc
     # the reverse-time rollout kernel alone: transition data-grad + actor data-grad (weight grads are
     # separate GEMM launches), per state
-    bwd_rollout_kernel = f_tr + f_pol
+    # (the actor's first Linear gets no data gradient: its input is detached, rnns.py:238)
+    bwd_rollout_kernel = f_tr + f_pol - 2 * F * ah
     fwd_rollout_kernel = f_tr + f_pol
     return dict(fwd=fwd, bwd=bwd, total=fwd + bwd, fwd_rollout_kernel=fwd_rollout_kernel,
                 bwd_rollout_kernel=bwd_rollout_kernel)
@@ -73,6 +74,17 @@ def measured_peaks():
         return dict(bf16_tflops=float(p["bf16_tflops"]), bf16_tflops_sustained=float(p["bf16_tflops_sustained"]),
                     hbm_gbs=float(p["hbm_gbs"]), source="measured")
     return dict(bf16_tflops=1590.0, bf16_tflops_sustained=1400.0, hbm_gbs=6650.0, source="fallback")
+
+
+def ncu_traffic(workload, n_states, precision, kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
+    `ncu --set full` capture of this workload (profiles/ncu_traffic.json), or None when there is none."""
+    path = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if not os.path.exists(path):
+        return None
+    with open(path) as f:
+        table = json.load(f)
+    return table.get(f"{workload}:{n_states}:{precision}:{kernel}")
 
 
 class ClockSampler:
@@ -188,16 +200,11 @@ def run_b200(args):
     flush = torch.empty(512 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
     h_losses = torch.empty(2, dtype=torch.float32).pin_memory()
 
+    from dreamer_pytorch_b200.parallel import allreduce_grads as _allreduce
+
     def allreduce_grads():
-        # equal shards: mean of shard means = global mean; one flat bucket per group
-        for group in (actor_params, value_params):
-            flat = torch.cat([p.grad.reshape(-1) for p in group])
-            dist.all_reduce(flat, op=dist.ReduceOp.AVG)
-            off = 0
-            for p in group:
-                k = p.numel()
-                p.grad.copy_(flat[off:off + k].view_as(p))
-                off += k
+        # equal shards: mean of shard means = global mean; one flat bucket per optimizer group
+        _allreduce([actor_params, value_params])
 
     def step(stoch, deter):
         for p in grad_params:
@@ -300,7 +307,7 @@ def run_b200(args):
                 "h2d_bytes_per_step": int(h_stoch.numel() * 4 + h_deter.numel() * 4), "d2h_bytes_per_step": 8},
         "gpu_launches": launches,
         "roofline": {"bound": "tensor", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                     "frac": achieved / peak, "traffic": None, "peak_source": peaks["source"] + " bf16 sustained",
+                     "frac": achieved / peak, "traffic": ncu_traffic(args.workload, N, args.precision, dom), "peak_source": peaks["source"] + " bf16 sustained",
                      "kernel_ms": dom_ms, "whole_step_tflops": value * fl["total"] / 1e12},
         "kernels_ms_per_step": {k: round(v["ms_per_step"], 4) for k, v in prof.items()},
         "wall_ms_per_step": t_wall * 1e3 / args.steps,
@@ -414,7 +421,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="walker", choices=sorted(WORKLOADS))
     ap.add_argument("--n-states", type=int, default=0, help="override start states per GPU")
-    ap.add_argument("--precision", default="fp32", choices=["fp32", "bf16"])
+    ap.add_argument("--precision", default="bf16", choices=["fp32", "bf16"],
+                    help="bf16: tcgen05 tensor-core kernels (BASELINE.json configs[1]); fp32: FFMA kernels")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     args = ap.parse_args()
