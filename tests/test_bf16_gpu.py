@@ -189,3 +189,46 @@ def test_rollout_policy_bf16_all_cotangents(cuda):
     rg = torch.autograd.grad(ro, [wd[k] for k in ak], [c.double() for c in cots])
     gerrs = {k: rel_err(a, b) for k, a, b in zip(ak, cg, rg)}
     assert max(gerrs.values()) < BF16_TOL, gerrs
+
+
+def test_full_size_loss_section_bf16(cuda):
+    """BASELINE.json configs[1] shapes on the bf16 path: walker-sized agent (A=6, tanh-normal), B=50 T=50 H=15
+    (2 500 start states), RSSM + heads (synthetic obs_embed).  Losses and every parameter gradient after
+    model/actor/value backward must agree with the fp32 oracle within the bf16 budget (1e-2 normwise)."""
+    from oracle import dreamer_oracle as O
+    from dreamer_pytorch_b200 import noise
+    from dreamer_pytorch_b200.algo import dreamer_loss
+    from dreamer_pytorch_b200.dropin.agent import AtariDreamerModel
+    from dreamer_pytorch_b200.precision import precision
+
+    torch.set_num_threads(max(1, min(16, torch.get_num_threads())))
+    A, T, B, H = 6, 50, 50, 15
+    w = O.make_weights(O.weight_shapes(A, conv=True), 0)
+    g = torch.Generator().manual_seed(1)
+    embed = torch.randn(T, B, 1024, generator=g)
+    action = torch.rand(T, B, A, generator=g) * 2 - 1
+    reward = torch.randn(T, B, 1, generator=g)
+    nz = O.make_noise(T, B, T * B, H, 30, A, 2)
+    wl = {k: v.clone().requires_grad_(True) for k, v in w.items()}
+    out = O.dreamer_loss(wl, None, torch.cat([action[:1], action]), torch.cat([reward[:1, :, 0], reward[:, :, 0]]),
+                         None, nz, horizon=H, obs_embed=embed)
+    names = [k for k in wl if not k.startswith("observation_")]
+    total = out["model_loss"] + out["actor_loss"] + out["value_loss"]
+    rgrads = dict(zip(names, torch.autograd.grad(total, [wl[k] for k in names], allow_unused=True)))
+
+    model = AtariDreamerModel(action_shape=(A,), action_dist="tanh_normal")
+    model.load_state_dict(O.expand_aliases(w))
+    model = model.to(cuda).train()
+    with precision("bf16"), noise.injected(eps_prior=[nz["eps_prior_obs"], nz["eps_prior_img"]],
+                                           eps_post=[nz["eps_post_obs"]], noise_act=[nz["noise_act"]]):
+        ml, al, vl, _ = dreamer_loss(model, None, action.to(cuda), reward.to(cuda), None, horizon=H,
+                                     obs_embed=embed.to(cuda))
+        ml.backward(); al.backward(); vl.backward()
+    errs = {"model_loss": rel_err(ml, out["model_loss"]), "actor_loss": rel_err(al, out["actor_loss"]),
+            "value_loss": rel_err(vl, out["value_loss"])}
+    for k, p in model.named_parameters():
+        if p.grad is not None and not k.startswith("observation_") and rgrads.get(k) is not None:
+            errs[k] = rel_err(p.grad, rgrads[k])
+    bad = {k: v for k, v in errs.items() if not v < BF16_TOL}
+    assert not bad, bad
+    assert len(errs) > 30
