@@ -10,7 +10,8 @@ import os
 
 MAXL = 8  # DRM_MAX_LINEAR
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdreamer_b200.so")
+# DRM_B200_LIB: developer override (e.g. the -DDRM_TIMELINE build of tools/timeline.py); same ABI, same checks.
+LIB_PATH = os.environ.get("DRM_B200_LIB") or os.path.join(_HERE, "libdreamer_b200.so")
 
 MODE_POLICY, MODE_TRANSITION, MODE_REPRESENTATION = 0, 1, 2
 DIST = {"tanh_normal": 0, "one_hot": 1, "relaxed_one_hot": 2}

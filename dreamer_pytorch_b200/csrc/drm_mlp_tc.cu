@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_fwd_tc_kernel(const __gr
     for (int l = 0; l < p.n_linear; ++l)
         fill_bias(sbias + l * p.bstride, p.b[l], nullptr, l == p.n_linear - 1 ? p.out_dim : p.hidden, p.bstride);
     const uint32_t tmem_base = chain_setup(bars, p.pg);
-    const int warp = threadIdx.x >> 5;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // warp-uniform for the compiler
     const int tiles = (p.M + kTileRows - 1) / kTileRows;
     const int reps = blockIdx.x < tiles ? (tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
     if (warp == kEpiWarps) {
@@ -159,7 +159,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_bwd_tc_kernel(const __gr
     extern __shared__ __align__(1024) uint8_t smem[];
     ChainBars* bars = reinterpret_cast<ChainBars*>(smem);
     const uint32_t tmem_base = chain_setup(bars, p.pg);
-    const int warp = threadIdx.x >> 5;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // warp-uniform for the compiler
     const int tiles = (p.M + kTileRows - 1) / kTileRows;
     const int reps = blockIdx.x < tiles ? (tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
     if (warp == kEpiWarps) {

@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
     fill_bias(sbias + bl.p2m, p.b_p2, nullptr, S, p.Sp);
     fill_bias(sbias + bl.p2s, p.b_p2 + S, nullptr, S, p.Sp);
     const uint32_t tmem_base = chain_setup(bars, p.pg);
-    const int warp = threadIdx.x >> 5;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // warp-uniform for the compiler
     const int my_tiles = (int)blockIdx.x < p.ntiles ? (p.ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
     const int reps = my_tiles * p.T;
     if (warp == kEpiWarps) {
@@ -369,7 +369,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
     extern __shared__ __align__(1024) uint8_t smem[];
     ChainBars* bars = reinterpret_cast<ChainBars*>(smem);
     const uint32_t tmem_base = chain_setup(bars, p.pg);
-    const int warp = threadIdx.x >> 5;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // warp-uniform for the compiler
     const int my_tiles = (int)blockIdx.x < p.ntiles ? (p.ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
     const int reps = my_tiles * p.T;
     if (warp == kEpiWarps) {
@@ -979,3 +979,15 @@ size_t rollout_tc_fwd_workspace_bytes(const drm_rollout* r) {
 
 }  // namespace tc
 }  // namespace drm
+
+#ifdef DRM_TIMELINE
+// Debug only: copy out (and reset) the handshake stamps CTA 0 of the rollout kernels recorded.
+extern "C" int drm_debug_timeline(long long* stamps, int* counts) {
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(stamps, drm::tc::g_tl, sizeof(long long) * 4 * 4096);
+    cudaMemcpyFromSymbol(counts, drm::tc::g_tl_n, sizeof(int) * 4);
+    int zero[4] = {0, 0, 0, 0};
+    cudaMemcpyToSymbol(drm::tc::g_tl_n, zero, sizeof(zero));
+    return 0;
+}
+#endif

@@ -61,6 +61,18 @@ inline size_t program_weight_bytes(const TcProgram& pg) {
     return b;
 }
 
+// Debug timeline (-DDRM_TIMELINE): CTA 0 records SM-clock stamps of its handshakes (one copy per translation unit).
+#ifdef DRM_TIMELINE
+static __device__ long long g_tl[4][4096];
+static __device__ int g_tl_n[4];
+__device__ __forceinline__ void tl_mark(int role) {
+    if (blockIdx.x == 0) { int i = g_tl_n[role]; if (i < 4096) { g_tl[role][i] = clock64(); g_tl_n[role] = i + 1; } }
+}
+#define DRM_TL(role) tl_mark(role)
+#else
+#define DRM_TL(role)
+#endif
+
 struct ChainBars {
     uint64_t full[8];
     uint64_t empty[8];
@@ -121,48 +133,67 @@ __device__ __forceinline__ void chain_producer(const TcProgram& pg, ChainBars* b
     }
 }
 
-// MMA warp: issue the ops of `reps` repetitions.
+// MMA warp: issue the ops of `reps` repetitions.  One thread issues ~150 tcgen05.mma per rollout step, so the
+// loop is kept to a handful of instructions per MMA: the 64-bit shared-memory descriptors are built once per op
+// (constant high word; the low word = address | LBO advances by plain 32-bit adds) and a weight slab is issued
+// by a branch-light inner loop.
 __device__ __forceinline__ void chain_mma(const TcProgram& pg, ChainBars* bars, uint8_t* smem, uint32_t tmem_base, int reps) {
-    if ((threadIdx.x & 31) != 0) return;
+    // The whole warp runs the (warp-uniform) control flow so that descriptors and counters live in uniform
+    // registers; only the tcgen05 instructions themselves are issued by one elected lane.
+    tmem_base = __shfl_sync(0xffffffffu, tmem_base, 0);
     const uint32_t smem_base = smem_u32(smem);
+    const uint32_t desc_hi = (128u >> 4) | (1u << 14);  // SBO = 128 B, descriptor version 1 (bits 32..47)
+    const uint32_t a_lo_flags = (uint32_t)(kChunkBytes >> 4) << 16;  // LBO of an A operand
+    const uint32_t stage0 = smem_base + pg.stage_off;
+    const int n_stages = pg.n_stages, stage_bytes = pg.stage_bytes, n_ops = pg.n_ops;
     int stage = 0;
     uint32_t phase = 0, ready_phase = 0;
     bool phase_start = true;
     for (int rep = 0; rep < reps; ++rep) {
-        for (int i = 0; i < pg.n_ops; ++i) {
+        for (int i = 0; i < n_ops; ++i) {
             const TcOp op = pg.op[i];
             if (phase_start) {
                 mbar_wait(&bars->a_ready, ready_phase);
                 ready_phase ^= 1;
                 tc_fence_after_sync();
                 phase_start = false;
+                if ((threadIdx.x & 31) == 0) DRM_TL(1);
             }
-            const int n = op.n;
+            const uint32_t n = op.n;
             const int total = op.a_chunks[0] + op.a_chunks[1];
-            const int kc = slab_chunks(pg.stage_bytes, n);
-            const uint32_t idesc = make_idesc_bf16(kTileRows, n);
-            const uint32_t b_lbo = (uint32_t)n * 16;
-            int in_slab = 0;
-            for (int c = 0; c < total; c += 2) {
-                if (in_slab == 0) {
-                    mbar_wait(&bars->full[stage], phase);
-                    tc_fence_after_sync();
+            const int seg0 = op.a_chunks[0];
+            const int kc = slab_chunks(stage_bytes, (int)n);
+            const uint32_t idesc = make_idesc_bf16(kTileRows, (int)n);
+            const uint32_t b_flags = n << 16;                      // LBO = n * 16 B, in 16-byte units
+            const uint32_t b_step = 2u * n;                        // two K chunks of the weight slab, 16-byte units
+            uint32_t a_lo = (((smem_base + op.a_off[0]) & 0x3FFFFu) >> 4) | a_lo_flags;
+            const uint32_t a_lo1 = (((smem_base + op.a_off[1]) & 0x3FFFFu) >> 4) | a_lo_flags;
+            const uint32_t d_addr = tmem_base + op.d_col;
+            uint32_t acc = op.accumulate;
+            int c = 0;
+            while (c < total) {
+                const int cnt = min(kc, total - c);
+                mbar_wait(&bars->full[stage], phase);
+                tc_fence_after_sync();
+                uint32_t b_lo = (((stage0 + (uint32_t)stage * stage_bytes) & 0x3FFFFu) >> 4) | b_flags;
+#pragma unroll 1
+                for (int k = 0; k < cnt; k += 2) {
+                    if (c == seg0) a_lo = a_lo1;
+                    const uint64_t adesc = ((uint64_t)desc_hi << 32) | a_lo;
+                    const uint64_t bdesc = ((uint64_t)desc_hi << 32) | b_lo;
+                    if (elect_one()) umma_bf16(d_addr, adesc, bdesc, idesc, acc);
+                    acc = 1;
+                    a_lo += (2 * kChunkBytes) >> 4;
+                    b_lo += b_step;
+                    c += 2;
                 }
-                const uint32_t a_addr = c < op.a_chunks[0] ? smem_base + op.a_off[0] + (uint32_t)c * kChunkBytes
-                                                           : smem_base + op.a_off[1] + (uint32_t)(c - op.a_chunks[0]) * kChunkBytes;
-                const uint32_t b_addr = smem_base + pg.stage_off + (uint32_t)stage * pg.stage_bytes + (uint32_t)in_slab * b_lbo;
-                umma_bf16(tmem_base + op.d_col, make_desc(a_addr, kChunkBytes, 128), make_desc(b_addr, b_lbo, 128), idesc,
-                          op.accumulate || c > 0);
-                in_slab += 2;
-                if (in_slab >= kc || c + 2 >= total) {
-                    umma_commit(&bars->empty[stage]);  // slab consumed once these MMAs retire
-                    in_slab = 0;
-                    if (++stage == pg.n_stages) { stage = 0; phase ^= 1; }
-                }
+                if (elect_one()) umma_commit(&bars->empty[stage]);  // slab consumed once these MMAs retire
+                if (++stage == n_stages) { stage = 0; phase ^= 1; }
             }
             if (op.phase_end) {
-                umma_commit(&bars->acc_full);
+                if (elect_one()) umma_commit(&bars->acc_full);
                 phase_start = true;
+                if ((threadIdx.x & 31) == 0) DRM_TL(1);
             }
         }
     }
@@ -178,12 +209,16 @@ struct EpiSync {
         mbar_wait(&bars->acc_full, acc_phase);
         acc_phase ^= 1;
         tc_fence_after_sync();
+        if (threadIdx.x == 0) DRM_TL(0);
+        if (threadIdx.x == kEpiThreads - 32) DRM_TL(2);
     }
     // A operands written (generic proxy) + accumulators consumed -> let the MMA warp go on
     __device__ __forceinline__ void release() {
         fence_proxy_async_smem();
         tc_fence_before_sync();
         __syncwarp();
+        if (threadIdx.x == 0) DRM_TL(0);
+        if (threadIdx.x == kEpiThreads - 32) DRM_TL(2);
         if ((threadIdx.x & 31) == 0) mbar_arrive(&bars->a_ready);
     }
 };
