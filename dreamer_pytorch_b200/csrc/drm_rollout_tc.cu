@@ -23,6 +23,8 @@
 namespace drm {
 namespace tc {
 
+constexpr int kMaxPerD = 8;  // deter chunks per epilogue thread (cdp <= 32)
+
 struct RollTcDev {
     int T, n, ntiles, act_dist, training;
     int A, S, D, Hd, ah, an, Aout;
@@ -39,6 +41,9 @@ struct RollTcDev {
     __nv_bfloat16* sv_x;                    // ELU(rnn input)                            (chh)
     __nv_bfloat16 *sv_r, *sv_z, *sv_n, *sv_hn;  // GRU gates and W_hn h + b_hn           (cdp)
     __nv_bfloat16* sv_hid;                  // prior hidden                              (chh)
+    __nv_bfloat16* sv_lo;                   // bf16(deter - bf16(deter)) of the deter fed into step t  (cdp);
+                                            // not training: one slot per CTA (lo_per_cta = 1)
+    int lo_per_cta;
     float* sv_raw;                          // actor output before the distribution, fp32 [T*n][Aout]
     const uint8_t* wstream;
     uint32_t st_off, hb_off, bias_off;
@@ -98,6 +103,9 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
         const int row = epi_row(), grp = epi_group();
         const int cfeat = p.cs + p.cdp;
         const bool save = p.training != 0;
+        const size_t lo_stride = (size_t)p.cdp * kTileRows * 8;
+        const int tid = threadIdx.x, lane = threadIdx.x & 31;
+        float* hbf = reinterpret_cast<float*>(hb);
         // this thread's chunk ranges for the three operand widths
         const int per_a = (p.cha + kEpiGroups - 1) / kEpiGroups, a_beg = grp * per_a, a_end = min(p.cha, a_beg + per_a);
         const int per_h = (p.chh + kEpiGroups - 1) / kEpiGroups, h_beg = grp * per_h, h_end = min(p.chh, h_beg + per_h);
@@ -108,6 +116,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
             const int grow = row0 + row;
             const bool live = grow < p.n;
             // ---- start state -> ST (and the feat image of step 0); action chunks zero
+            __nv_bfloat16* lo0 = p.sv_lo + (size_t)(p.lo_per_cta ? (int)blockIdx.x : tile) * lo_stride;
             for (int idx = threadIdx.x; idx < (cfeat + p.ca) * kTileRows; idx += kEpiThreads) {
                 const int chunk = idx / kTileRows, r = idx - chunk * kTileRows;
                 const int gr = row0 + r;
@@ -118,9 +127,14 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                     if (chunk < p.cs) ldg_row8(p.start_stoch + (size_t)gr * S, chunk * 8, S, v);
                     else if (chunk < p.cs + p.cd) ldg_row8(p.start_deter + (size_t)gr * D, (chunk - p.cs) * 8, D, v);
                 }
-                st_chunk_bf16(st + (size_t)idx * 16, v);
-                if (save && chunk < cfeat) st_chunk_bf16(p.sv_feat + ((size_t)tile * cfeat * kTileRows + idx) * 8, v);
+                uint4 hi, lo;
+                split_hi_lo(v, hi, lo);
+                *reinterpret_cast<uint4*>(st + (size_t)idx * 16) = hi;
+                if (save && chunk < cfeat) *reinterpret_cast<uint4*>(p.sv_feat + ((size_t)tile * cfeat * kTileRows + idx) * 8) = hi;
+                if (chunk >= p.cs && chunk < cfeat)
+                    *reinterpret_cast<uint4*>(lo0 + ((size_t)(chunk - p.cs) * kTileRows + r) * 8) = lo;
             }
+            named_bar<kEpiThreads, 1>();  // the lo image is re-read by other threads (ownership differs from this loop's)
             es.release();
             for (int t = 0; t < p.T; ++t) {
                 const int ts = t * p.ntiles + tile;
@@ -141,8 +155,27 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                     es.release();
                 }
                 // ------------------------------------------------------------ actor output + action (agent.py:101-117)
+                // Global I/O of this small phase goes through shared memory (the hidden buffer is dead once the
+                // actor's last GEMM has retired): the 128 threads of column group 0 read the tile's noise block with
+                // coalesced loads before the wait, and write action / raw blocks back coalesced after the release.
+                const int arows = min(kTileRows, p.n - row0);
+                float* sN = hbf;                       // [128][A] noise
+                float* sA = hbf + kTileRows * 16;      // [128][A] action
+                float* sR = hbf + 2 * kTileRows * 16;  // [128][Aout] pre-distribution actor output
+                float nzr[16];
+                if (grp == 0) {
+                    const float* nz_t = p.noise_act + ((size_t)t * p.n + row0) * A;
+#pragma unroll
+                    for (int k = 0; k < 16; ++k) {
+                        const int i = tid + k * kTileRows;
+                        nzr[k] = (k < A && i < arows * A) ? __ldg(nz_t + i) : 0.f;
+                    }
+                }
                 es.wait_acc();
                 if (grp == 0) {
+#pragma unroll
+                    for (int k = 0; k < 16; ++k) if (k < A) sN[tid + k * kTileRows] = nzr[k];
+                    named_bar<kTileRows, 2>();
                     float raw[16];
                     {
                         float v0[8], v1[8], b0[8], b1[8];
@@ -158,7 +191,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
 #pragma unroll
                     for (int j = 0; j < 16; ++j) act[j] = 0.f;
                     if (live) {
-                        const float* nz = p.noise_act + trow * A;
+                        const float* nz = sN + row * A;
                         if (p.act_dist == DRM_DIST_TANH_NORMAL) {
 #pragma unroll
                             for (int j = 0; j < 8; ++j) {
@@ -166,7 +199,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                                     const float rm = raw[j], rs = raw[A + j];
                                     const float mean = p.mean_scale * tanh_fast(rm / p.mean_scale);
                                     const float std = softplus_fast(rs + p.raw_init_std) + p.act_min_std;
-                                    act[j] = tanh_fast(fmaf(std, __ldg(nz + j), mean));
+                                    act[j] = tanh_fast(fmaf(std, nz[j], mean));
                                 }
                             }
                         } else {
@@ -180,7 +213,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                                 for (int j = 0; j < 16; ++j) {
                                     if (j < A) {
                                         den += __expf(raw[j] - mx);
-                                        const float s = raw[j] + __ldg(nz + j);
+                                        const float s = raw[j] + nz[j];
                                         if (s > bv) { bv = s; best = j; }
                                     }
                                 }
@@ -194,20 +227,20 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                             } else {  // relaxed one-hot: softmax((logits + g) / temperature)
                                 float smx = -INFINITY, den = 0.f;
 #pragma unroll
-                                for (int j = 0; j < 16; ++j) if (j < A) smx = fmaxf(smx, (raw[j] + __ldg(nz + j)) / p.temperature);
+                                for (int j = 0; j < 16; ++j) if (j < A) smx = fmaxf(smx, (raw[j] + nz[j]) / p.temperature);
 #pragma unroll
                                 for (int j = 0; j < 16; ++j) {
-                                    if (j < A) { act[j] = __expf((raw[j] + __ldg(nz + j)) / p.temperature - smx); den += act[j]; }
+                                    if (j < A) { act[j] = __expf((raw[j] + nz[j]) / p.temperature - smx); den += act[j]; }
                                 }
 #pragma unroll
                                 for (int j = 0; j < 16; ++j) if (j < A) act[j] /= den;
                             }
                         }
+                    }
 #pragma unroll
-                        for (int j = 0; j < 16; ++j) {
-                            if (j < A) p.action_out[trow * A + j] = act[j];
-                            if (save && j < p.Aout) p.sv_raw[trow * p.Aout + j] = raw[j];
-                        }
+                    for (int j = 0; j < 16; ++j) {
+                        if (j < A) sA[row * A + j] = act[j];
+                        if (j < p.Aout) sR[row * p.Aout + j] = raw[j];
                     }
                     uint8_t* sa = st + (size_t)cfeat * kChunkBytes;
                     for (int c = 0; c < p.ca; ++c) {
@@ -218,6 +251,16 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                     }
                 }
                 es.release();
+                if (grp == 0) {
+                    named_bar<kTileRows, 2>();
+                    float* ao = p.action_out + ((size_t)t * p.n + row0) * A;
+                    for (int i = tid; i < arows * A; i += kTileRows) ao[i] = sA[i];
+                    if (save) {
+                        float* ro = p.sv_raw + ((size_t)t * p.n + row0) * p.Aout;
+                        for (int i = tid; i < arows * p.Aout; i += kTileRows) ro[i] = sR[i];
+                    }
+                }
+                named_bar<kEpiThreads, 1>();  // the hidden buffer is written again by the next epilogue
                 // ------------------------------------------------------------ x = ELU(W_in [a|stoch] + b)   (rnns.py:99-101)
                 es.wait_acc();
                 {
@@ -254,54 +297,93 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                 tmem_st_wait();
                 es.release();
                 // ------------------------------------------------------------ GRU, part 2: n, z, h'
+                // h (fed into this step) = hi + lo: hi is the bf16 operand in ST, lo its bf16 remainder in the side
+                // image (written by this very thread one step ago) -- fetched before the wait, coalesced.
+                uint4 lo_in[kMaxPerD];
+                {
+                    const __nv_bfloat16* lo_cur = p.sv_lo + (size_t)(p.lo_per_cta ? (int)blockIdx.x : ts) * lo_stride;
+#pragma unroll
+                    for (int i = 0; i < kMaxPerD; ++i) {
+                        const int c = d_beg + i;
+                        lo_in[i] = make_uint4(0u, 0u, 0u, 0u);
+                        if (c < d_end) lo_in[i] = *reinterpret_cast<const uint4*>(lo_cur + ((size_t)c * kTileRows + row) * 8);
+                    }
+                }
                 es.wait_acc();
                 {
-                    const float* hprev = t == 0 ? p.start_deter + (size_t)grow * D : p.deter + (trow - p.n) * D;
                     const bool feat_next = save && t + 1 < p.T;
-                    const bool vec = (D & 3) == 0;
-                    epi_for_chunks2(tmem_base, 0, Dp, d_beg, d_end, [&](int c, float (&an_)[8], float (&az)[8]) {
-                        float bn[8], bz[8], zz[8], nn[8], hv[8], hp[8];
-                        lds8(sbias + bl.n + c * 8, bn);
-                        lds8(sbias + bl.z + c * 8, bz);
+                    const bool lo_next_on = p.lo_per_cta || t + 1 < p.T;
+                    __nv_bfloat16* lo_nxt = p.sv_lo + (size_t)(p.lo_per_cta ? (int)blockIdx.x : ts + p.ntiles) * lo_stride;
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) hp[i] = 0.f;
-                        if (live) {
-                            // plain (coherent) loads: deter[t-1] was written by this very thread one step ago
-                            if (vec && c * 8 + 8 <= D) {
-                                const float4 lo = *reinterpret_cast<const float4*>(hprev + c * 8);
-                                const float4 hi = *reinterpret_cast<const float4*>(hprev + c * 8 + 4);
-                                hp[0] = lo.x; hp[1] = lo.y; hp[2] = lo.z; hp[3] = lo.w; hp[4] = hi.x; hp[5] = hi.y; hp[6] = hi.z; hp[7] = hi.w;
-                            } else {
+                    for (int i = 0; i < kMaxPerD; ++i) {
+                        const int c = d_beg + i;
+                        if (c < d_end) {
+                            float an_[8], az[8], bn[8], bz[8], zz[8], nn[8], hv[8], hp[8], hl[8];
+                            tmem_ld8(epi_taddr(tmem_base, c * 8), an_);
+                            tmem_ld8(epi_taddr(tmem_base, Dp + c * 8), az);
+                            uint8_t* st_c = st + ((size_t)(p.cs + c) * kTileRows + row) * 16;
+                            unpack_bf16x8(*reinterpret_cast<const uint4*>(st_c), hp);
+                            unpack_bf16x8(lo_in[i], hl);
+                            lds8(sbias + bl.n + c * 8, bn);
+                            lds8(sbias + bl.z + c * 8, bz);
+                            tmem_ld_wait();
 #pragma unroll
-                                for (int i = 0; i < 8; ++i) if (c * 8 + i < D) hp[i] = hprev[c * 8 + i];
+                            for (int k = 0; k < 8; ++k) {
+                                const float h = hp[k] + hl[k];
+                                nn[k] = tanh_fast(an_[k] + bn[k]);     // pad columns: n = 0, z = 0.5, h' = 0.5 * 0
+                                zz[k] = sigmoid_fast(az[k] + bz[k]);
+                                hv[k] = live ? fmaf(zz[k], h - nn[k], nn[k]) : 0.f;  // (1-z) n + z h
                             }
-                        }
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            nn[i] = tanh_fast(an_[i] + bn[i]);     // pad columns: n = 0, z = 0.5, h' = 0.5 * 0
-                            zz[i] = sigmoid_fast(az[i] + bz[i]);
-                            hv[i] = fmaf(zz[i], hp[i] - nn[i], nn[i]);  // (1-z) n + z h
-                        }
-                        if (live) {
-                            float* dst = p.deter + trow * D + c * 8;
-                            if (vec && c * 8 + 8 <= D) {
-                                *reinterpret_cast<float4*>(dst) = make_float4(hv[0], hv[1], hv[2], hv[3]);
-                                *reinterpret_cast<float4*>(dst + 4) = make_float4(hv[4], hv[5], hv[6], hv[7]);
-                            } else {
-#pragma unroll
-                                for (int i = 0; i < 8; ++i) if (c * 8 + i < D) dst[i] = hv[i];
+                            uint4 hi, lo;
+                            split_hi_lo(hv, hi, lo);
+                            *reinterpret_cast<uint4*>(st_c) = hi;
+                            *reinterpret_cast<uint4*>(hb + ((size_t)c * kTileRows + row) * 16) = lo;
+                            if (lo_next_on) *reinterpret_cast<uint4*>(lo_nxt + ((size_t)c * kTileRows + row) * 8) = lo;
+                            if (save) {
+                                st_chunk_bf16(tcm_at(p.sv_z, p.cdp, ts, c, row), zz);
+                                st_chunk_bf16(tcm_at(p.sv_n, p.cdp, ts, c, row), nn);
                             }
+                            if (feat_next) *reinterpret_cast<uint4*>(tcm_at(p.sv_feat, cfeat, ts + p.ntiles, p.cs + c, row)) = hi;
                         }
-                        st_chunk_bf16(st + ((size_t)(p.cs + c) * kTileRows + row) * 16, hv);
-                        if (save) {
-                            st_chunk_bf16(tcm_at(p.sv_z, p.cdp, ts, c, row), zz);
-                            st_chunk_bf16(tcm_at(p.sv_n, p.cdp, ts, c, row), nn);
-                        }
-                        if (feat_next) st_chunk_bf16(tcm_at(p.sv_feat, cfeat, ts + p.ntiles, p.cs + c, row), hv);
-                    });
+                    }
                 }
                 es.release();
+                // fp32 deter rows of this tile-step, rebuilt from hi (ST) + lo (hidden buffer, dead until the next
+                // epilogue) after the release: 8 rows x 64 contiguous bytes per warp instruction
+                named_bar<kEpiThreads, 1>();
+                {
+                    const int q4 = D >> 2, qblocks = (q4 + 3) >> 2, nblocks = (kTileRows / 8) * qblocks;
+                    const uint8_t* st_d = st + (size_t)p.cs * kChunkBytes;
+                    float* out_t = p.deter + ((size_t)t * p.n + row0) * D;
+                    for (int b = tid >> 5; b < nblocks; b += kEpiWarps) {
+                        const int rb = b / qblocks, qb = b - rb * qblocks;
+                        const int r = rb * 8 + (lane >> 2), q = qb * 4 + (lane & 3);
+                        if (q < q4 && row0 + r < p.n) {
+                            const uint32_t off = (uint32_t)(((q >> 1) * kTileRows + r) * 16 + (q & 1) * 8);
+                            const uint2 h2 = *reinterpret_cast<const uint2*>(st_d + off);
+                            const uint2 l2 = *reinterpret_cast<const uint2*>(hb + off);
+                            float4 o;
+                            o.x = __uint_as_float(h2.x << 16) + __uint_as_float(l2.x << 16);
+                            o.y = __uint_as_float(h2.x & 0xFFFF0000u) + __uint_as_float(l2.x & 0xFFFF0000u);
+                            o.z = __uint_as_float(h2.y << 16) + __uint_as_float(l2.y << 16);
+                            o.w = __uint_as_float(h2.y & 0xFFFF0000u) + __uint_as_float(l2.y & 0xFFFF0000u);
+                            *reinterpret_cast<float4*>(out_t + (size_t)r * D + q * 4) = o;
+                        }
+                    }
+                }
+                named_bar<kEpiThreads, 1>();
                 // ------------------------------------------------------------ prior hidden  (rnns.py:103)
+                // the tile's eps block for the prior sample is fetched here (coalesced, 8 registers), two phases early
+                const int pcount = min(kTileRows, p.n - row0) * S;
+                float epsr[8];
+                {
+                    const float* eps_t = p.eps_prior + ((size_t)t * p.n + row0) * S;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const int i = tid + k * kEpiThreads;
+                        epsr[k] = i < pcount ? __ldg(eps_t + i) : 0.f;
+                    }
+                }
                 es.wait_acc();
                 {
                     const float* bias = sbias + bl.p1;
@@ -317,8 +399,19 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                 }
                 es.release();
                 // ------------------------------------------------------------ prior mean | std, sample  (rnns.py:103-106)
+                // Outputs are staged in the (now dead) hidden buffer as [128][S] blocks and leave with coalesced
+                // stores after the release; eps arrives the same way.
                 es.wait_acc();
                 {
+                    float* sE = hbf;                      // eps in, stoch out
+                    float* sM = hbf + kTileRows * S;
+                    float* sD = hbf + 2 * kTileRows * S;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const int i = tid + k * kEpiThreads;
+                        if (i < kTileRows * S) sE[i] = epsr[k];
+                    }
+                    named_bar<kEpiThreads, 1>();
                     const bool feat_next = save && t + 1 < p.T;
                     epi_for_chunks2(tmem_base, 0, p.Sp, s_beg, s_end, [&](int c, float (&am)[8], float (&as_)[8]) {
                         float bm[8], bs[8], sv[8];
@@ -328,12 +421,12 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                         for (int i = 0; i < 8; ++i) {
                             const int j = c * 8 + i;
                             float st_ = 0.f;
-                            if (live && j < S) {
+                            if (j < S) {
                                 const float mean = am[i] + bm[i];
                                 const float std = softplus_fast(as_[i] + bs[i]) + p.min_std;
-                                const size_t o = trow * S + j;
-                                st_ = fmaf(std, __ldg(p.eps_prior + o), mean);
-                                p.prior_mean[o] = mean; p.prior_std[o] = std; p.prior_stoch[o] = st_;
+                                const int o = row * S + j;
+                                st_ = live ? fmaf(std, sE[o], mean) : 0.f;
+                                sM[o] = mean; sD[o] = std; sE[o] = st_;
                             }
                             sv[i] = st_;
                         }
@@ -342,6 +435,19 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                     });
                 }
                 if (t + 1 < p.T) es.release();
+                named_bar<kEpiThreads, 1>();
+                {
+                    const size_t o0 = ((size_t)t * p.n + row0) * S;
+                    const float* sE = hbf;
+                    const float* sM = hbf + kTileRows * S;
+                    const float* sD = hbf + 2 * kTileRows * S;
+                    for (int i = tid; i < pcount; i += kEpiThreads) {
+                        p.prior_mean[o0 + i] = sM[i];
+                        p.prior_std[o0 + i] = sD[i];
+                        p.prior_stoch[o0 + i] = sE[i];
+                    }
+                }
+                named_bar<kEpiThreads, 1>();  // the hidden buffer is written again by the next epilogue
             }
         }
     }
@@ -448,21 +554,19 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                 {
                     const int per = (p.cdp + kEpiGroups - 1) / kEpiGroups;
                     const int cbeg = grp * per, cend = min(p.cdp, cbeg + per);
-                    const float* hprev = t == 0 ? p.start_deter + (size_t)grow * D : p.deter + (trow - p.n) * D;
-                    const bool vec = (D & 3) == 0;
+                    const int cfeat = p.cs + p.cdp;
                     epi_for_chunks(tmem_base, colC, cbeg, cend, [&](int c, float (&dh)[8]) {
-                        float rr[8], zz[8], nn[8], hn[8], dpr[8], dpz[8], din[8], dhn[8], gd[8], hpv[8];
+                        float rr[8], zz[8], nn[8], hn[8], dpr[8], dpz[8], din[8], dhn[8], gd[8], hpv[8], hlo[8];
                         ld_chunk_bf16(tcm_at(p.sv_r, p.cdp, ts, c, row), rr);
                         ld_chunk_bf16(tcm_at(p.sv_z, p.cdp, ts, c, row), zz);
                         ld_chunk_bf16(tcm_at(p.sv_n, p.cdp, ts, c, row), nn);
                         ld_chunk_bf16(tcm_at(p.sv_hn, p.cdp, ts, c, row), hn);
+                        // deter fed into step t = hi (feat image) + lo (side image), both tile-major and coalesced
+                        ld_chunk_bf16(tcm_at(p.sv_feat, cfeat, ts, p.cs + c, row), hpv);
+                        ld_chunk_bf16(tcm_at(p.sv_lo, p.cdp, ts, c, row), hlo);
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) { gd[i] = 0.f; hpv[i] = 0.f; }
-                        if (live) {
-                            ldg_row8(hprev, c * 8, D, hpv);
-                            if (p.g_deter) ldg_row8(p.g_deter + trow * D, c * 8, D, gd);
-                        }
-                        (void)vec;
+                        for (int i = 0; i < 8; ++i) { gd[i] = 0.f; hpv[i] += hlo[i]; }
+                        if (live && p.g_deter) ldg_row8(p.g_deter + trow * D, c * 8, D, gd);
 #pragma unroll
                         for (int i = 0; i < 8; ++i) {
                             const int col = c * 8 + i;
@@ -625,6 +729,14 @@ int rollout_tc_supported(const drm_rollout* r) {
     if (Aout > 16 || w.A > 16) return 0;
     if (rup(w.D, 16) > 256 || rup(w.Hd, 16) > 256 || rup(r->actor.hidden, 16) > 256 || w.S > 64) return 0;
     if (r->actor.n_linear < 2) return 0;
+    // staged global I/O: fp32 [128][S] x 3 and [128][16] x 3 blocks in the hidden buffer, 8 eps registers per thread,
+    // float4 deter rows
+    {
+        const int hbc = (rup((w.Hd + 7) / 8, 2) > rup((r->actor.hidden + 7) / 8, 2)) ? rup((w.Hd + 7) / 8, 2) : rup((r->actor.hidden + 7) / 8, 2);
+        if (w.S > 32 || (w.D & 3) || 3 * kTileRows * w.S * 4 > hbc * kChunkBytes || 3 * kTileRows * 16 * 4 > hbc * kChunkBytes) return 0;
+        if (rup((w.D + 7) / 8, 2) > hbc) return 0;  // lo staging of the deter tile
+        if (rup((w.D + 7) / 8, 2) > 4 * kMaxPerD) return 0;
+    }
     // tensor memory of the backward: R_H | R_C | R_AS
     const int chh = rup((w.Hd + 7) / 8, 2), cha = rup((r->actor.hidden + 7) / 8, 2), cdp = rup((w.D + 7) / 8, 2);
     const int cs = rup((w.S + 7) / 8, 2);
@@ -762,6 +874,7 @@ static size_t carve_save_tc(const RollTcDev& dd, uint8_t* base, RollTcDev* out) 
     tmp.sv_n = (__nv_bfloat16*)take(tcm_bytes(TS, dd.cdp));
     tmp.sv_hn = (__nv_bfloat16*)take(tcm_bytes(TS, dd.cdp));
     tmp.sv_hid = (__nv_bfloat16*)take(tcm_bytes(TS, dd.chh));
+    tmp.sv_lo = (__nv_bfloat16*)take(tcm_bytes(TS, dd.cdp));
     tmp.sv_raw = (float*)take((size_t)dd.T * dd.n * dd.Aout * sizeof(float));
     if (out) *out = tmp;
     return off;
@@ -791,14 +904,20 @@ int rollout_tc_fwd(const drm_rollout* r, cudaStream_t stream) {
     RollTcDev& d = pl.dev;
     fill_io_tc(r, d);
     d.wstream = ws;
+    const int grid = d.ntiles < kNumSM ? d.ntiles : kNumSM;
     if (r->training) {
         DRM_REQUIRE(r->save && r->save_bytes >= rollout_tc_save_bytes(r), DRM_E_WORKSPACE, "save buffer too small (bf16 rollout)");
         RollTcDev carved;
         carve_save_tc(d, reinterpret_cast<uint8_t*>(rup_sz((size_t)r->save, 256)), &carved);
         d = carved;
+        d.lo_per_cta = 0;
+    } else {
+        // no save buffer: the lo image of the carried deter lives in one workspace slot per CTA
+        DRM_REQUIRE(r->workspace_bytes >= rollout_tc_fwd_workspace_bytes(r), DRM_E_WORKSPACE, "workspace too small (bf16 rollout)");
+        d.sv_lo = reinterpret_cast<__nv_bfloat16*>(ws + rup_sz(pl.wbytes, 256));
+        d.lo_per_cta = 1;
     }
     rc = launch_pack_tc(pl.jobs, stream); if (rc) return rc;
-    const int grid = d.ntiles < kNumSM ? d.ntiles : kNumSM;
     DRM_CUDA_OK(cudaFuncSetAttribute(rollout_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
     ProfScope prof(PROF_ROLLOUT_FWD, stream);
     rollout_fwd_tc_kernel<<<grid, kChainThreads, pl.smem_bytes, stream>>>(d);
@@ -974,7 +1093,8 @@ int rollout_tc_bwd(const drm_rollout* r, const drm_rollout_grad* g, cudaStream_t
 size_t rollout_tc_fwd_workspace_bytes(const drm_rollout* r) {
     RollTcPlan pl;
     if (!rollout_tc_supported(r) || plan_fwd(r, nullptr, pl) != DRM_OK) return 0;
-    return pl.wbytes + 1024;
+    const int grid = pl.dev.ntiles < kNumSM ? pl.dev.ntiles : kNumSM;
+    return rup_sz(pl.wbytes, 256) + tcm_bytes((size_t)grid, pl.dev.cdp) + 1024;
 }
 
 }  // namespace tc

@@ -165,5 +165,36 @@ __device__ __forceinline__ void st_chunk_bf16(void* dst, const float (&v)[8]) {
     *reinterpret_cast<uint4*>(dst) = q;
 }
 
+// 8 bf16 (one 16-byte chunk row) -> 8 fp32
+__device__ __forceinline__ void unpack_bf16x8(const uint4 q, float (&v)[8]) {
+    const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        v[2 * i] = __uint_as_float(w[i] << 16);
+        v[2 * i + 1] = __uint_as_float(w[i] & 0xFFFF0000u);
+    }
+}
+__device__ __forceinline__ uint4 pack_bf16x8(const float (&v)[8]) {
+    uint4 q;
+    q.x = pack_bf16x2(v[0], v[1]);
+    q.y = pack_bf16x2(v[2], v[3]);
+    q.z = pack_bf16x2(v[4], v[5]);
+    q.w = pack_bf16x2(v[6], v[7]);
+    return q;
+}
+// hi = bf16(v), lo = bf16(v - hi): v is recovered as hi + lo with 16 bits of mantissa.  The recurrent state of
+// the rollouts is carried this way: hi IS the tensor-core operand, lo rides along in a bf16 side image.
+__device__ __forceinline__ void split_hi_lo(const float (&v)[8], uint4& hi, uint4& lo) {
+    float h[8], r[8];
+    hi = pack_bf16x8(v);
+    unpack_bf16x8(hi, h);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) r[i] = v[i] - h[i];
+    lo = pack_bf16x8(r);
+}
+// named barrier among the epilogue threads only (barrier 0 stays __syncthreads)
+template <int kThreads, int kId>
+__device__ __forceinline__ void named_bar() { asm volatile("bar.sync %0, %1;" ::"n"(kId), "n"(kThreads) : "memory"); }
+
 }  // namespace tc
 }  // namespace drm

@@ -153,6 +153,7 @@ def test_rollout_policy_bf16(cuda, sz):
     rg = torch.autograd.grad(ro, [wd[k] for k in ak], [c.double() for c in cots])
     gerrs = {k: rel_err(a, b) for k, a, b in zip(ak, cg, rg)}
     tol = BF16_TOL if n * H >= 2048 else 2 * BF16_TOL
+    print(f"[margin] rollout bf16 n={n} T={H}: outputs {max(errs.values()):.2e}, actor grads {max(gerrs.values()):.2e}")
     assert max(gerrs.values()) < tol, gerrs
 
 
@@ -188,6 +189,7 @@ def test_rollout_policy_bf16_all_cotangents(cuda):
         cg = torch.autograd.grad(co, wa, [c.to(cuda) for c in cots])
     rg = torch.autograd.grad(ro, [wd[k] for k in ak], [c.double() for c in cots])
     gerrs = {k: rel_err(a, b) for k, a, b in zip(ak, cg, rg)}
+    print(f"[margin] rollout bf16 all cotangents: actor grads {max(gerrs.values()):.2e}")
     assert max(gerrs.values()) < BF16_TOL, gerrs
 
 
@@ -230,5 +232,7 @@ def test_full_size_loss_section_bf16(cuda):
         if p.grad is not None and not k.startswith("observation_") and rgrads.get(k) is not None:
             errs[k] = rel_err(p.grad, rgrads[k])
     bad = {k: v for k, v in errs.items() if not v < BF16_TOL}
+    worst = max(errs, key=errs.get)
+    print(f"[margin] full-size bf16 loss section: worst {worst} {errs[worst]:.2e}")
     assert not bad, bad
     assert len(errs) > 30
