@@ -487,17 +487,52 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
         uint8_t* ga = smem + p.ga_off;
         uint8_t* gb = smem + p.gb_off;
         uint8_t* g2 = smem + p.g2_off;
-        const int row = epi_row(), grp = epi_group(), lane = threadIdx.x & 31;
+        const int row = epi_row(), grp = epi_group(), lane = threadIdx.x & 31, tid = threadIdx.x;
         const int S = p.S, D = p.D, A = p.A;
         const int Dp = p.cdp * 8;
+        const int cfeat = p.cs + p.cdp;
         const int colC = max(p.chh, p.cha) * 8, colAS = colC + Dp;
         __nv_bfloat16* stash_in = p.stash + (size_t)blockIdx.x * 2 * p.cdp * kTileRows * 8;
         __nv_bfloat16* stash_hn = stash_in + (size_t)p.cdp * kTileRows * 8;
         const int last = p.an - 1;
+        // fp32 staging blocks of the prior head, [128][S] each: GB is dead from the GRU's last GEMM until the next
+        // GRU epilogue, GA from the step's last GEMM until the d-prior-hidden epilogue
+        float* sEps = reinterpret_cast<float*>(gb);
+        float* sStd = sEps + kTileRows * S;
+        float* sGst = sStd + kTileRows * S;
+        float* sGm = reinterpret_cast<float*>(ga);
+        float* sGs = sGm + kTileRows * S;
+        const size_t chunk_img = (size_t)kTileRows * 8;  // elements of one chunk of a TCM image
         for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
             const int row0 = tile * kTileRows;
             const int grow = row0 + row;
             const bool live = grow < p.n;
+            const int rows_live = min(kTileRows, p.n - row0);
+            // asynchronous, coalesced fetch of step t2's prior-head blocks into the staging area
+            auto fetch_prior = [&](int t2) {
+                const size_t o0 = ((size_t)t2 * p.n + row0) * S;
+                for (int i = tid; i < rows_live * S; i += kEpiThreads) {
+                    cp_async4(sEps + i, p.eps_prior + o0 + i);
+                    cp_async4(sStd + i, p.prior_std + o0 + i);
+                    if (p.g_prior_stoch) cp_async4(sGst + i, p.g_prior_stoch + o0 + i);
+                    if (p.g_prior_mean) cp_async4(sGm + i, p.g_prior_mean + o0 + i);
+                    if (p.g_prior_std) cp_async4(sGs + i, p.g_prior_std + o0 + i);
+                }
+            };
+            // L2 prefetch (one thread) of what the epilogues of step t2 read, issued about one phase ahead
+            auto pf_hid = [&](int t2) { if (tid == 0) l2_prefetch(tcm_at(p.sv_hid, p.chh, t2 * p.ntiles + tile, 0, 0), p.chh * chunk_img * 2); };
+            auto pf_gru = [&](int t2) {
+                if (tid == 0) {
+                    const int ts2 = t2 * p.ntiles + tile;
+                    l2_prefetch(tcm_at(p.sv_r, p.cdp, ts2, 0, 0), p.cdp * chunk_img * 2);
+                    l2_prefetch(tcm_at(p.sv_z, p.cdp, ts2, 0, 0), p.cdp * chunk_img * 2);
+                    l2_prefetch(tcm_at(p.sv_n, p.cdp, ts2, 0, 0), p.cdp * chunk_img * 2);
+                    l2_prefetch(tcm_at(p.sv_hn, p.cdp, ts2, 0, 0), p.cdp * chunk_img * 2);
+                    l2_prefetch(tcm_at(p.sv_lo, p.cdp, ts2, 0, 0), p.cdp * chunk_img * 2);
+                    l2_prefetch(tcm_at(p.sv_feat, cfeat, ts2, p.cs, 0), p.cdp * chunk_img * 2);
+                    if (p.g_deter) l2_prefetch(p.g_deter + ((size_t)t2 * p.n + row0) * D, (size_t)rows_live * D * 4);
+                }
+            };
             // ---- zero the carried gradients
             {
                 float z[8];
@@ -507,10 +542,15 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                 for (int c = grp; c < p.cs; c += kEpiGroups) tmem_st8(epi_taddr(tmem_base, colAS + c * 8), z);
                 tmem_st_wait();
             }
+            fetch_prior(p.T - 1);
+            pf_hid(p.T - 1);
             for (int t = p.T - 1; t >= 0; --t) {
                 const int ts = t * p.ntiles + tile;
                 const size_t trow = (size_t)t * p.n + grow;
                 // ------------------------------------------------------------ prior head (pointwise) -> G2
+                cp_async_wait_all();
+                named_bar<kEpiThreads, 1>();
+                pf_gru(t);
                 {
                     const int per = (p.cs + kEpiGroups - 1) / kEpiGroups;
                     const int cbeg = grp * per, cend = min(p.cs, cbeg + per);
@@ -523,11 +563,11 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                             const int j = c * 8 + i;
                             dm[i] = 0.f; ds[i] = 0.f;
                             if (live && j < S) {
-                                const size_t o = trow * S + j;
-                                const float dst = (p.g_prior_stoch ? p.g_prior_stoch[o] : 0.f) + cs_[i];
-                                dm[i] = (p.g_prior_mean ? p.g_prior_mean[o] : 0.f) + dst;
-                                const float dsd = (p.g_prior_std ? p.g_prior_std[o] : 0.f) + dst * __ldg(p.eps_prior + o);
-                                ds[i] = dsd * (1.f - __expf(-(p.prior_std[o] - p.min_std)));  // sigmoid(raw) from softplus(raw)
+                                const int o = row * S + j;
+                                const float dst = (p.g_prior_stoch ? sGst[o] : 0.f) + cs_[i];
+                                dm[i] = (p.g_prior_mean ? sGm[o] : 0.f) + dst;
+                                const float dsd = (p.g_prior_std ? sGs[o] : 0.f) + dst * sEps[o];
+                                ds[i] = dsd * (1.f - __expf(-(sStd[o] - p.min_std)));  // sigmoid(raw) from softplus(raw)
                             }
                         }
                         st_chunk_bf16(g2 + ((size_t)c * kTileRows + row) * 16, dm);
@@ -536,25 +576,40 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                 }
                 es.release();
                 // ------------------------------------------------------------ d prior hidden
-                es.wait_acc();
                 {
                     const int per = (p.chh + kEpiGroups - 1) / kEpiGroups;
                     const int cbeg = grp * per, cend = min(p.chh, cbeg + per);
-                    epi_for_chunks(tmem_base, 0, cbeg, cend, [&](int c, float (&v)[8]) {
-                        float h[8];
-                        ld_chunk_bf16(tcm_at(p.sv_hid, p.chh, ts, c, row), h);
+                    epi_for_chunks_saved(es, tmem_base, 0, cbeg, cend,
+                        [&](int c) { return *reinterpret_cast<const uint4*>(tcm_at(p.sv_hid, p.chh, ts, c, row)); },
+                        [&](int c, float (&v)[8], const uint4 hq) {
+                            float h[8];
+                            unpack_bf16x8(hq, h);
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) v[i] = live ? v[i] * (h[i] > 0.f ? 1.f : h[i] + 1.f) : 0.f;
-                        st_chunk_bf16(ga + ((size_t)c * kTileRows + row) * 16, v);
-                    });
+                            for (int i = 0; i < 8; ++i) v[i] = live ? v[i] * (h[i] > 0.f ? 1.f : h[i] + 1.f) : 0.f;
+                            st_chunk_bf16(ga + ((size_t)c * kTileRows + row) * 16, v);
+                        });
                 }
                 es.release();
                 // ------------------------------------------------------------ GRU cell (pointwise)
                 es.wait_acc();
+                if (tid == 0) l2_prefetch(tcm_at(p.sv_x, p.chh, ts, 0, 0), p.chh * chunk_img * 2);
+                if (p.g_deter) {
+                    // upstream d deter rows of this tile-step, coalesced (8 rows x 64 bytes per warp instruction), as
+                    // fp32 chunk-major halves into GA | GB: exactly the slots this thread overwrites below
+                    const int q4 = D >> 2, qblocks = (q4 + 3) >> 2, nblocks = (kTileRows / 8) * qblocks;
+                    const float* src_t = p.g_deter + ((size_t)t * p.n + row0) * D;
+                    for (int b = tid >> 5; b < nblocks; b += kEpiWarps) {
+                        const int rb = b / qblocks, qb = b - rb * qblocks;
+                        const int r = rb * 8 + (lane >> 2), q = qb * 4 + (lane & 3);
+                        if (q < q4 && r < rows_live)
+                            cp_async16(((q & 1) ? gb : ga) + ((size_t)(q >> 1) * kTileRows + r) * 16, src_t + (size_t)r * D + q * 4);
+                    }
+                    cp_async_wait_all();
+                    named_bar<kEpiThreads, 1>();
+                }
                 {
                     const int per = (p.cdp + kEpiGroups - 1) / kEpiGroups;
                     const int cbeg = grp * per, cend = min(p.cdp, cbeg + per);
-                    const int cfeat = p.cs + p.cdp;
                     epi_for_chunks(tmem_base, colC, cbeg, cend, [&](int c, float (&dh)[8]) {
                         float rr[8], zz[8], nn[8], hn[8], dpr[8], dpz[8], din[8], dhn[8], gd[8], hpv[8], hlo[8];
                         ld_chunk_bf16(tcm_at(p.sv_r, p.cdp, ts, c, row), rr);
@@ -566,7 +621,12 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                         ld_chunk_bf16(tcm_at(p.sv_lo, p.cdp, ts, c, row), hlo);
 #pragma unroll
                         for (int i = 0; i < 8; ++i) { gd[i] = 0.f; hpv[i] += hlo[i]; }
-                        if (live && p.g_deter) ldg_row8(p.g_deter + trow * D, c * 8, D, gd);
+                        if (p.g_deter) {
+                            const float4 lo4 = *reinterpret_cast<const float4*>(ga + ((size_t)c * kTileRows + row) * 16);
+                            const float4 hi4 = *reinterpret_cast<const float4*>(gb + ((size_t)c * kTileRows + row) * 16);
+                            gd[0] = lo4.x; gd[1] = lo4.y; gd[2] = lo4.z; gd[3] = lo4.w;
+                            gd[4] = hi4.x; gd[5] = hi4.y; gd[6] = hi4.z; gd[7] = hi4.w;
+                        }
 #pragma unroll
                         for (int i = 0; i < 8; ++i) {
                             const int col = c * 8 + i;
@@ -592,10 +652,11 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                 }
                 es.release();
                 // ------------------------------------------------------------ reload d i_n, d h_n (own writes) -> GA, GB
-                es.wait_acc();
                 {
                     const int per = (p.cdp + kEpiGroups - 1) / kEpiGroups;
                     const int cbeg = grp * per, cend = min(p.cdp, cbeg + per);
+                    es.wait_acc();
+#pragma unroll 2
                     for (int c = cbeg; c < cend; ++c) {
                         const uint4 a = *reinterpret_cast<const uint4*>(stash_in + ((size_t)c * kTileRows + row) * 8);
                         const uint4 b = *reinterpret_cast<const uint4*>(stash_hn + ((size_t)c * kTileRows + row) * 8);
@@ -605,21 +666,24 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                 }
                 es.release();
                 // ------------------------------------------------------------ d rnn-input pre-activation
-                es.wait_acc();
                 {
                     const int per = (p.chh + kEpiGroups - 1) / kEpiGroups;
                     const int cbeg = grp * per, cend = min(p.chh, cbeg + per);
-                    epi_for_chunks(tmem_base, 0, cbeg, cend, [&](int c, float (&v)[8]) {
-                        float h[8];
-                        ld_chunk_bf16(tcm_at(p.sv_x, p.chh, ts, c, row), h);
+                    epi_for_chunks_saved(es, tmem_base, 0, cbeg, cend,
+                        [&](int c) { return *reinterpret_cast<const uint4*>(tcm_at(p.sv_x, p.chh, ts, c, row)); },
+                        [&](int c, float (&v)[8], const uint4 hq) {
+                            float h[8];
+                            unpack_bf16x8(hq, h);
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) v[i] = live ? v[i] * (h[i] > 0.f ? 1.f : h[i] + 1.f) : 0.f;
-                        st_chunk_bf16(ga + ((size_t)c * kTileRows + row) * 16, v);
-                    });
+                            for (int i = 0; i < 8; ++i) v[i] = live ? v[i] * (h[i] > 0.f ? 1.f : h[i] + 1.f) : 0.f;
+                            st_chunk_bf16(ga + ((size_t)c * kTileRows + row) * 16, v);
+                        });
+                    if (p.want_actor && tid == 0) l2_prefetch(tcm_at(p.sv_ah[last - 1], p.cha, ts, 0, 0), p.cha * chunk_img * 2);
                 }
                 es.release();
                 // ------------------------------------------------------------ d [stoch | action] is in R_AS now
                 es.wait_acc();
+                if (!p.want_actor && t > 0) { fetch_prior(t - 1); pf_hid(t - 1); }
                 if (p.want_actor) {
                     // actor head (pointwise): d action -> d raw -> G2 (K = 16) [+ TCM copy, fp32 bias gradient]
                     if (grp == 0) {
@@ -686,17 +750,27 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                     es.release();
                     // actor hidden layers, last Linear first; layer 0's input (feat) is detached (rnns.py:238)
                     for (int l = last; l >= 1; --l) {
-                        es.wait_acc();
                         const int per = (p.cha + kEpiGroups - 1) / kEpiGroups;
                         const int cbeg = grp * per, cend = min(p.cha, cbeg + per);
-                        epi_for_chunks(tmem_base, 0, cbeg, cend, [&](int c, float (&v)[8]) {
-                            float h[8];
-                            ld_chunk_bf16(tcm_at(p.sv_ah[l - 1], p.cha, ts, c, row), h);
+                        epi_for_chunks_saved(es, tmem_base, 0, cbeg, cend,
+                            [&](int c) { return *reinterpret_cast<const uint4*>(tcm_at(p.sv_ah[l - 1], p.cha, ts, c, row)); },
+                            [&](int c, float (&v)[8], const uint4 hq) {
+                                float h[8];
+                                unpack_bf16x8(hq, h);
 #pragma unroll
-                            for (int i = 0; i < 8; ++i) v[i] = live ? v[i] * (h[i] > 0.f ? 1.f : h[i] + 1.f) : 0.f;
-                            st_chunk_bf16(ga + ((size_t)c * kTileRows + row) * 16, v);
-                            st_chunk_bf16(tcm_at(p.dys_a[l - 1], p.cha, ts, c, row), v);
-                        });
+                                for (int i = 0; i < 8; ++i) v[i] = live ? v[i] * (h[i] > 0.f ? 1.f : h[i] + 1.f) : 0.f;
+                                if (l > 1) st_chunk_bf16(ga + ((size_t)c * kTileRows + row) * 16, v);  // layer 0 gets no data gradient
+                                st_chunk_bf16(tcm_at(p.dys_a[l - 1], p.cha, ts, c, row), v);
+                            },
+                            [&] {
+                                if (l > 1) {
+                                    if (tid == 0) l2_prefetch(tcm_at(p.sv_ah[l - 2], p.cha, ts, 0, 0), p.cha * chunk_img * 2);
+                                } else if (t > 0) {
+                                    // last epilogue of the step: GA and GB are dead, start on the next step's prior head
+                                    fetch_prior(t - 1);
+                                    pf_hid(t - 1);
+                                }
+                            });
                         if (l > 1) es.release();
                     }
                 }

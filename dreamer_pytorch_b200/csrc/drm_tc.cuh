@@ -192,6 +192,22 @@ __device__ __forceinline__ void split_hi_lo(const float (&v)[8], uint4& hi, uint
     for (int i = 0; i < 8; ++i) r[i] = v[i] - h[i];
     lo = pack_bf16x8(r);
 }
+// Ampere-style asynchronous copies global -> shared (generic proxy), used to stage small row-major blocks
+__device__ __forceinline__ void cp_async4(void* dst_smem, const void* src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async16(void* dst_smem, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+// Bulk L2 prefetch of a contiguous global range (any alignment: widened to 16-byte units; a prefetch never faults
+// inside the caller's allocation granule).  One thread, one instruction per range.
+__device__ __forceinline__ void l2_prefetch(const void* ptr, size_t bytes) {
+    const uintptr_t a = reinterpret_cast<uintptr_t>(ptr) & ~(uintptr_t)15;
+    const uintptr_t e = (reinterpret_cast<uintptr_t>(ptr) + bytes + 15) & ~(uintptr_t)15;
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a), "r"((uint32_t)(e - a)) : "memory");
+}
+
 // named barrier among the epilogue threads only (barrier 0 stays __syncthreads)
 template <int kThreads, int kId>
 __device__ __forceinline__ void named_bar() { asm volatile("bar.sync %0, %1;" ::"n"(kId), "n"(kThreads) : "memory"); }

@@ -257,6 +257,36 @@ __device__ __forceinline__ void epi_for_chunks2(uint32_t tmem_base, int colA, in
         f(c, a, b);
     }
 }
+// ELU-backward style epilogue: walks accumulator chunks like epi_for_chunks, but each chunk also needs a saved
+// activation chunk from global memory (16 bytes per thread).  Those loads do not depend on the accumulators, so the
+// first pair is issued BEFORE the accumulator wait and pair k+1 before pair k is processed.
+// ld(c) -> uint4, f(c, v[8], uint4 saved); after_wait() runs once, right after the accumulator wait.
+template <class L, class F, class W>
+__device__ __forceinline__ void epi_for_chunks_saved(EpiSync& es, uint32_t tmem_base, int col0, int cbeg, int cend, L&& ld, F&& f,
+                                                     W&& after_wait) {
+    const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+    uint4 h0 = cbeg < cend ? ld(cbeg) : zero;
+    uint4 h1 = cbeg + 1 < cend ? ld(cbeg + 1) : zero;
+    es.wait_acc();
+    after_wait();
+    for (int c = cbeg; c < cend; c += 2) {
+        float v[2][8];
+        const bool two = c + 1 < cend;
+        tmem_ld8(epi_taddr(tmem_base, col0 + c * 8), v[0]);
+        if (two) tmem_ld8(epi_taddr(tmem_base, col0 + c * 8 + 8), v[1]);
+        const uint4 n0 = c + 2 < cend ? ld(c + 2) : zero;
+        const uint4 n1 = c + 3 < cend ? ld(c + 3) : zero;
+        tmem_ld_wait();
+        f(c, v[0], h0);
+        if (two) f(c + 1, v[1], h1);
+        h0 = n0; h1 = n1;
+    }
+}
+template <class L, class F>
+__device__ __forceinline__ void epi_for_chunks_saved(EpiSync& es, uint32_t tmem_base, int col0, int cbeg, int cend, L&& ld, F&& f) {
+    epi_for_chunks_saved(es, tmem_base, col0, cbeg, cend, ld, f, [] {});
+}
+
 // 8 consecutive fp32 values from a 32-byte aligned shared-memory vector (bias blocks are zero padded)
 __device__ __forceinline__ void lds8(const float* src, float (&b)[8]) {
     const float4 lo = *reinterpret_cast<const float4*>(src);
