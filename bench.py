@@ -206,7 +206,7 @@ def run_b200(args):
         # equal shards: mean of shard means = global mean; one flat bucket per optimizer group
         _allreduce([actor_params, value_params])
 
-    def step(stoch, deter):
+    def eager_step(stoch, deter):
         for p in grad_params:
             p.grad = None
         start = RSSMState(stoch, stoch, stoch, deter)  # mean/std of a start state are never read
@@ -216,6 +216,21 @@ def run_b200(args):
         if world > 1:
             allreduce_grads()
         return actor_loss, value_loss
+
+    graph = None
+    if not args.no_graph:
+        # the whole step (noise, packing, both rollouts, heads, losses, all backward kernels) as ONE CUDA graph
+        from dreamer_pytorch_b200.graph import ImaginationGraph
+
+        graph = ImaginationGraph(model, N, H, use_pcont=w["use_pcont"])
+
+    def step(stoch, deter):
+        if graph is None:
+            return eager_step(stoch, deter)
+        losses = graph.step(stoch, deter)
+        if world > 1:
+            allreduce_grads()
+        return losses
 
     def barrier():
         if world > 1:
@@ -232,7 +247,11 @@ def run_b200(args):
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    lib.drm_prof_enable(1)
+    if graph is not None:
+        graph.stoch.copy_(d_stoch); graph.deter.copy_(d_deter)
+        d_stoch, d_deter = graph.stoch, graph.deter  # inputs resident in HBM: the captured buffers themselves
+    else:
+        lib.drm_prof_enable(1)
     launches0 = lib.drm_launch_count()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     barrier()
@@ -244,16 +263,29 @@ def run_b200(args):
         b.record()
     barrier()
     t_wall = time.perf_counter() - t_wall0
-    launches = int(lib.drm_launch_count() - launches0)
+    launches = int(lib.drm_launch_count() - launches0) if graph is None else graph.launches_per_replay * args.steps
     ms_dev = sum(a.elapsed_time(b) for a, b in ev)
     import ctypes as C
+
+    prof_steps = args.steps
+    if graph is not None:
+        # per-kernel CUDA-event times (roofline.kernel_ms): the same step run eagerly -- events cannot be read inside
+        # a replayed graph -- with the same L2 flush between steps
+        prof_steps = min(args.steps, 5)
+        lib.drm_prof_enable(1)
+        for _ in range(prof_steps):
+            flush.zero_()
+            eager_step(d_stoch, d_deter)
+        torch.cuda.synchronize()
+        for p, g in zip(graph.params, graph.grads):
+            p.grad = g
 
     prof = {}
     names = ["pack", "rollout_fwd", "rollout_bwd", "mlp_fwd", "mlp_bwd", "wgrad", "loss"]
     for i, nm in enumerate(names):
         tot, cnt = C.c_double(0), C.c_int(0)
         lib.drm_prof_read(i, C.byref(tot), C.byref(cnt))
-        prof[nm] = dict(ms_per_step=tot.value / args.steps, launches_per_step=cnt.value / args.steps)
+        prof[nm] = dict(ms_per_step=tot.value / prof_steps, launches_per_step=cnt.value / prof_steps)
     lib.drm_prof_enable(0)
 
     # ---- timed region 2: end to end through the public API with HOST buffers
@@ -302,6 +334,8 @@ def run_b200(args):
                    "states_per_gpu_per_step": N * H, "global_states_per_step": N * H * world,
                    "parallelism": f"dp{world} over start states; NCCL all-reduce of actor+value grads",
                    "l2": "512 MiB buffer written between timed steps (L2 flush); per-step CUDA events",
+                   "launch": "eager" if graph is None else "one CUDA graph replay per step (ImaginationGraph); kernels_ms_per_step "
+                                                           "from an eager pass of the same step",
                    "flops_per_state": fl["total"]},
         "e2e": {"value": states / (ms_e2e * 1e-3), "unit": UNIT,
                 "h2d_bytes_per_step": int(h_stoch.numel() * 4 + h_deter.numel() * 4), "d2h_bytes_per_step": 8},
@@ -424,6 +458,7 @@ def main():
     ap.add_argument("--precision", default="bf16", choices=["fp32", "bf16"],
                     help="bf16: tcgen05 tensor-core kernels (BASELINE.json configs[1]); fp32: FFMA kernels")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="launch the step eagerly instead of replaying one CUDA graph")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     args = ap.parse_args()
     if args.impl == "reference":

@@ -24,6 +24,16 @@ from .dropin.rnns import RSSMState, get_feat
 from .functional import (KLFn, RolloutCfg, _f32c, mlp_backward_raw, mlp_forward_raw, returns_loss_raw,
                          rollout_backward_raw, rollout_forward_raw)
 
+_SIDE = {}
+
+
+def _side_stream(device) -> "torch.cuda.Stream":
+    key = (device.type, device.index)
+    if key not in _SIDE:
+        _SIDE[key] = torch.cuda.Stream(device=device)
+    return _SIDE[key]
+
+
 ImagInfo = namedtuple("ImagInfo", ["imag", "actions", "reward", "value", "returns", "discount"])
 
 
@@ -37,7 +47,7 @@ class _ActorLossFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, pack, *actor_w):
-        (cfg, t, rssm, reward_w, value_w, pcont_w, discount, lambda_) = pack
+        (cfg, t, rssm, reward_w, value_w, pcont_w, discount, lambda_, shared) = pack
         actor = [_f32c(w) for w in actor_w]
         training = any(ctx.needs_input_grad)
         save = rollout_forward_raw(cfg, t, rssm, actor, training)
@@ -53,7 +63,7 @@ class _ActorLossFn(torch.autograd.Function):
         pc, psave = (mlp_forward_raw(x0, x1, pcont_w, training, prec) if pcont_w else (None, None))
         out = returns_loss_raw(reward.view(H, N), value.view(H, N), None if pc is None else pc.view(H, N), discount,
                                lambda_)
-        ctx.pack = (cfg, t, rssm, actor, save, reward_w, value_w, pcont_w, rsave, vsave, psave, out, x0, x1, prec)
+        ctx.pack = (cfg, t, rssm, actor, save, reward_w, value_w, pcont_w, rsave, vsave, psave, out, x0, x1, prec, shared)
         aux = (t["prior_mean"], t["prior_std"], t["prior_stoch"], t["deter"], t["action_out"], reward.view(H, N, 1),
                value.view(H, N, 1), out["returns"].view(H - 1, N, 1), out["disc"].view(H - 1, N, 1),
                out["losses"][1].clone(), out["d_value_pred"], vsave if vsave is not None else torch.empty(0))
@@ -62,7 +72,7 @@ class _ActorLossFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g_loss, *_):
-        (cfg, t, rssm, actor, save, reward_w, value_w, pcont_w, rsave, vsave, psave, out, x0, x1, prec) = ctx.pack
+        (cfg, t, rssm, actor, save, reward_w, value_w, pcont_w, rsave, vsave, psave, out, x0, x1, prec, shared) = ctx.pack
         H, N = cfg.steps, cfg.n
         g_loss = _f32c(g_loss)
         g_stoch = torch.empty_like(t["prior_stoch"])
@@ -72,8 +82,25 @@ class _ActorLossFn(torch.autograd.Function):
         mlp_backward_raw(x0, x1, value_w, vsave, out["d_value"].view(H * N, 1), g_loss, gs, gd, True, False, prec)
         if pcont_w:
             mlp_backward_raw(x0, x1, pcont_w, psave, out["d_pcont"].view(H * N, 1), g_loss, gs, gd, True, False, prec)
+        # The reverse-time rollout kernel occupies one SM per 128 start states; the value loss' weight-gradient pass
+        # (dreamer_algo.py:331-337) depends on nothing computed here, so it runs beside it on a side stream and
+        # _ValueLossFn.backward only has to scale the result (it recomputes if this backward never ran).
+        main = torch.cuda.current_stream()
+        side = None
+        if shared is not None and not shared.get("value_done") and "value_grads" not in shared:
+            side = _side_stream(g_loss.device)
+            side.wait_stream(main)
         _, _, gactor = rollout_backward_raw(cfg, t, rssm, actor, save, dict(g_prior_stoch=g_stoch, g_deter=g_deter),
                                             want_actor=True)
+        if side is not None:
+            with torch.cuda.stream(side):
+                vg = mlp_backward_raw(x0, x1, value_w, vsave, out["d_value_pred"].view(H * N, 1), None, None, None, False,
+                                      True, prec)
+                ev = torch.cuda.Event()
+                ev.record(side)
+            for g in vg:
+                g.record_stream(main)
+            shared["value_grads"] = (vg, ev)
         ctx.pack = None
         return (None, *gactor)
 
@@ -85,16 +112,24 @@ class _ValueLossFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, pack, *value_w):
-        (x0, x1, vsave, d_value_pred, loss, prec) = pack
-        ctx.pack = (x0, x1, vsave, d_value_pred, [_f32c(w) for w in value_w], prec)
+        (x0, x1, vsave, d_value_pred, loss, prec, shared) = pack
+        ctx.pack = (x0, x1, vsave, d_value_pred, [_f32c(w) for w in value_w], prec, shared)
         return loss.clone()
 
     @staticmethod
     def backward(ctx, g_loss):
-        x0, x1, vsave, d_value_pred, value_w, prec = ctx.pack
+        x0, x1, vsave, d_value_pred, value_w, prec, shared = ctx.pack
+        ctx.pack = None
+        cached = shared.pop("value_grads", None) if shared is not None else None
+        if shared is not None:
+            shared["value_done"] = True
+        if cached is not None:
+            grads, ev = cached  # computed beside the rollout backward with unit upstream gradient
+            torch.cuda.current_stream().wait_event(ev)
+            torch._foreach_mul_(grads, _f32c(g_loss))
+            return (None, *grads)
         grads = mlp_backward_raw(x0, x1, value_w, vsave, d_value_pred.view(-1, 1), _f32c(g_loss), None, None, False,
                                  True, prec)
-        ctx.pack = None
         return (None, *grads)
 
 
@@ -128,11 +163,12 @@ def imagination_losses(model, start_state: RSSMState, horizon: int, discount: fl
     reward_w = frozen(mlp_weights(model.reward_model.model))
     value_params = mlp_weights(model.value_model.model)
     pcont_w = frozen(mlp_weights(model.pcont.model)) if use_pcont else []
-    pack = (cfg, t, rssm, reward_w, frozen(value_params), pcont_w, discount, discount_lambda)
+    shared = {}  # lets the two loss nodes overlap independent backward work (see _ActorLossFn.backward)
+    pack = (cfg, t, rssm, reward_w, frozen(value_params), pcont_w, discount, discount_lambda, shared)
     (actor_loss, mean, std, st, dt, actions, reward, value, returns, disc, vloss, d_value_pred,
      vsave) = _ActorLossFn.apply(pack, *dec.weights())
     x0, x1 = st.view(horizon * N, -1), dt.view(horizon * N, -1)
-    value_loss = _ValueLossFn.apply((x0, x1, vsave, d_value_pred, vloss, get_precision()), *value_params)
+    value_loss = _ValueLossFn.apply((x0, x1, vsave, d_value_pred, vloss, get_precision(), shared), *value_params)
     info = ImagInfo(RSSMState(mean, std, st, dt), actions, reward, value, returns, disc)
     return actor_loss, value_loss, info
 

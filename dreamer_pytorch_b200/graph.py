@@ -1,0 +1,79 @@
+"""One CUDA graph for the whole imagination step (actor + value loss, forward and backward).
+
+The fused loss section launches ~35 small kernels around the two persistent rollout kernels (weight packing,
+head MLPs, weight-gradient GEMMs, memsets).  At the reference batch (2 500 start states) the host cannot issue
+them as fast as the GPU retires them, so the step is captured once -- kernels, the side-stream fork/join of
+``algo._ActorLossFn.backward`` and the noise generation included -- and replayed: one launch per update, no
+Python on the critical path, gradients land in static ``.grad`` tensors (the usual whole-step capture pattern).
+
+    g = ImaginationGraph(model, n_states=2500, horizon=15)
+    actor_loss, value_loss = g.step(stoch, deter)      # tensors [n_states, S] / [n_states, D], any device
+    # model.action_decoder / model.value_model parameters now hold .grad; run the optimizers as usual
+
+Replaces the Python-level sequence of dreamer_algo.py:283-337 + :174-180 (actor_loss.backward(),
+value_loss.backward()) for callers that own the training loop; ``imagination_losses`` stays the eager API.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from .algo import imagination_losses
+from .dropin.rnns import RSSMState
+
+
+class ImaginationGraph:
+    def __init__(self, model, n_states: int, horizon: int, discount: float = 0.99, discount_lambda: float = 0.95,
+                 use_pcont: bool = False, warmup: int = 3):
+        p0 = next(model.parameters())
+        if not p0.is_cuda:
+            raise RuntimeError("ImaginationGraph needs a CUDA model (there is no CPU fallback)")
+        self.model, self.n, self.horizon = model, int(n_states), int(horizon)
+        self._kw = dict(discount=discount, discount_lambda=discount_lambda, use_pcont=use_pcont)
+        dev = p0.device
+        self.stoch = torch.zeros(self.n, model.stochastic_size, device=dev)
+        self.deter = torch.zeros(self.n, model.deterministic_size, device=dev)
+        self.actor_params = list(model.action_decoder.parameters())
+        self.value_params = list(model.value_model.parameters())
+        self.params = self.actor_params + self.value_params
+        # eager warm-up on a side stream (lazy initialisation, allocator high-water mark), as capture requires
+        cur = torch.cuda.current_stream(dev)
+        s = torch.cuda.Stream(device=dev)
+        s.wait_stream(cur)
+        with torch.cuda.stream(s):
+            for _ in range(max(1, warmup)):
+                self._eager()
+        cur.wait_stream(s)
+        torch.cuda.synchronize(dev)
+        self.graph = torch.cuda.CUDAGraph()
+        lib = _lib.load()
+        n0 = lib.drm_launch_count()
+        with torch.cuda.graph(self.graph):
+            self.actor_loss, self.value_loss, self.grads = self._eager()
+        self.launches_per_replay = int(lib.drm_launch_count() - n0)  # kernels of this library inside the graph
+        for p, g in zip(self.params, self.grads):
+            p.grad = g  # static tensors from the graph's pool, refreshed by every replay
+
+    def _eager(self):
+        start = RSSMState(self.stoch, self.stoch, self.stoch, self.deter)  # mean / std of a start state are never read
+        actor_loss, value_loss, _ = imagination_losses(self.model, start, self.horizon, **self._kw)
+        # autograd.grad rather than .backward(): no AccumulateGrad nodes (they remember the stream they were created
+        # on, which breaks capture when the model has been used on the default stream before)
+        ga = torch.autograd.grad(actor_loss, self.actor_params)
+        gv = torch.autograd.grad(value_loss, self.value_params)
+        return actor_loss.detach(), value_loss.detach(), list(ga) + list(gv)
+
+    def step(self, stoch: torch.Tensor, deter: torch.Tensor):
+        """Copies the start states into the captured buffers (a host->device copy when they live in pinned host
+        memory), replays the step and returns the (static) loss tensors; parameter gradients are refreshed in place."""
+        if stoch.shape != self.stoch.shape or deter.shape != self.deter.shape:
+            raise ValueError(f"start states must be {tuple(self.stoch.shape)} / {tuple(self.deter.shape)}")
+        if stoch.data_ptr() != self.stoch.data_ptr():
+            self.stoch.copy_(stoch, non_blocking=True)
+        if deter.data_ptr() != self.deter.data_ptr():
+            self.deter.copy_(deter, non_blocking=True)
+        for p, g in zip(self.params, self.grads):
+            if p.grad is not g:
+                p.grad = g  # an optimizer's zero_grad(set_to_none=True) dropped it; the graph writes into g
+        self.graph.replay()
+        return self.actor_loss, self.value_loss
