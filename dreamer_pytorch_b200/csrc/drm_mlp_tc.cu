@@ -92,29 +92,135 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_fwd_tc_kernel(const __gr
         uint8_t* act = smem + p.act_off;
         const int row = epi_row(), grp = epi_group();
         const int last = p.n_linear - 1;
-        for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        // coalesced staging needs vector-aligned rows: x1 as float4 (k1 % 8 == 0 keeps its chunks whole), x0 as float2
+        const bool fast_stage = p.x1 && p.k1 > 0 && (p.k1 & 7) == 0 && (p.ld1 & 3) == 0 &&
+                                (reinterpret_cast<uintptr_t>(p.x1) & 15) == 0 &&
+                                p.c0 <= 4 && (p.c0 == 0 || (p.x0 && (p.k0 & 1) == 0 && (p.ld0 & 1) == 0 && (reinterpret_cast<uintptr_t>(p.x0) & 7) == 0));
+        // ---- staging of one input tile: fp32 global -> bf16 chunk-major shared [+ TCM copy for the wgrad], in parts
+        // so that the NEXT tile can be staged, slice by slice, behind the releases of the current one (the epilogue
+        // warps would otherwise idle while the tensor core runs).  Loads go 8 rows x 64 (x1) / 32 (x0) contiguous
+        // bytes per warp instruction, kU in flight per thread: the staging is latency bound.
+        const int wq = threadIdx.x >> 5, ln = threadIdx.x & 31;
+        constexpr int kU = 7;
+        const int q4 = p.k1 >> 2, qblocks1 = (q4 + 3) >> 2, nblocks1 = (kTileRows / 8) * qblocks1;
+        const int ublocks1 = (nblocks1 + kEpiWarps - 1) / kEpiWarps;  // x1 blocks per warp
+        const int n_parts = fast_stage ? (ublocks1 + kU - 1) / kU + 1 : 1;
+        // stage_issue() puts this thread's loads of one part in flight (registers), stage_commit() converts and stores.
+        float4 sv4[kU];
+        auto blk1 = [&](int part, int u, int& r, int& q) {  // x1 block slot -> (row, float4 column) of this lane
+            const int b = wq + (part * kU + u) * kEpiWarps;
+            const int rb = b / qblocks1, qb = b - rb * qblocks1;
+            r = rb * 8 + (ln >> 2); q = qb * 4 + (ln & 3);
+            return b < nblocks1 && q < q4;
+        };
+        auto blk0 = [&](int u, int& r, int& q) {            // x0 block slot -> (row, float2 column)
+            const int b = wq + u * kEpiWarps;
+            const int rb = b / max(p.c0, 1), qb = b - rb * max(p.c0, 1);
+            r = rb * 8 + (ln >> 2); q = qb * 4 + (ln & 3);
+            return b < (kTileRows / 8) * p.c0;
+        };
+        auto stage_issue = [&](int tile, int part) {
+            if (!fast_stage) return;
             const int row0 = tile * kTileRows;
-            // ---- stage the input tile: fp32 global -> bf16 chunk-major shared [+ TCM copy for the wgrad]
-            for (int idx = threadIdx.x; idx < p.cin * kTileRows; idx += kEpiThreads) {
-                const int chunk = idx / kTileRows, r = idx - chunk * kTileRows;
-                const int grow = row0 + r;
-                float v[8];
+            if (part < n_parts - 1) {
 #pragma unroll
-                for (int i = 0; i < 8; ++i) v[i] = 0.f;
-                if (grow < p.M) {
-                    if (chunk < p.c0) ldg_row8(p.x0 + (size_t)grow * p.ld0, chunk * 8, p.k0, v);
-                    else if (chunk < p.c0 + p.c1) ldg_row8(p.x1 + (size_t)grow * p.ld1, (chunk - p.c0) * 8, p.k1, v);
+                for (int u = 0; u < kU; ++u) {
+                    int r, q;
+                    sv4[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (blk1(part, u, r, q) && row0 + r < p.M)
+                        sv4[u] = __ldg(reinterpret_cast<const float4*>(p.x1 + (size_t)(row0 + r) * p.ld1) + q);
                 }
-                st_chunk_bf16(act + (size_t)idx * 16, v);
-                if (p.sx) st_chunk_bf16(p.sx + ((size_t)tile * p.cin * kTileRows + idx) * 8, v);
+            } else {
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {  // requires c0 <= 4 * kEpiWarps / 16 blocks per warp = 4 (k0 <= 32)
+                    int r, q;
+                    sv4[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (blk0(u, r, q) && 2 * q < p.k0 && row0 + r < p.M) {
+                        const float2 w = __ldg(reinterpret_cast<const float2*>(p.x0 + (size_t)(row0 + r) * p.ld0) + q);
+                        sv4[u].x = w.x; sv4[u].y = w.y;
+                    }
+                }
             }
+        };
+        auto stage_commit = [&](int tile, uint8_t* dst, int part) {
+            const int row0 = tile * kTileRows;
+            if (!fast_stage) {
+                for (int idx = threadIdx.x; idx < p.cin * kTileRows; idx += kEpiThreads) {
+                    const int chunk = idx / kTileRows, r = idx - chunk * kTileRows;
+                    const int grow = row0 + r;
+                    float v[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) v[i] = 0.f;
+                    if (grow < p.M) {
+                        if (chunk < p.c0) ldg_row8(p.x0 + (size_t)grow * p.ld0, chunk * 8, p.k0, v);
+                        else if (chunk < p.c0 + p.c1) ldg_row8(p.x1 + (size_t)grow * p.ld1, (chunk - p.c0) * 8, p.k1, v);
+                    }
+                    st_chunk_bf16(dst + (size_t)idx * 16, v);
+                    if (p.sx) st_chunk_bf16(p.sx + ((size_t)tile * p.cin * kTileRows + idx) * 8, v);
+                }
+                return;
+            }
+            uint8_t* sx_t = p.sx ? reinterpret_cast<uint8_t*>(p.sx + (size_t)tile * p.cin * kTileRows * 8) : nullptr;
+            if (part < n_parts - 1) {
+#pragma unroll
+                for (int u = 0; u < kU; ++u) {
+                    int r, q;
+                    if (blk1(part, u, r, q)) {
+                        const uint2 w = make_uint2(pack_bf16x2(sv4[u].x, sv4[u].y), pack_bf16x2(sv4[u].z, sv4[u].w));
+                        const size_t off = ((size_t)(p.c0 + (q >> 1)) * kTileRows + r) * 16 + (q & 1) * 8;
+                        *reinterpret_cast<uint2*>(dst + off) = w;
+                        if (sx_t) *reinterpret_cast<uint2*>(sx_t + off) = w;
+                    }
+                }
+                return;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                int r, q;
+                if (blk0(u, r, q)) {
+                    const uint32_t w = pack_bf16x2(sv4[u].x, sv4[u].y);
+                    const size_t off = ((size_t)(q >> 2) * kTileRows + r) * 16 + (q & 3) * 4;
+                    *reinterpret_cast<uint32_t*>(dst + off) = w;
+                    if (sx_t) *reinterpret_cast<uint32_t*>(sx_t + off) = w;
+                }
+            }
+            for (int idx = (p.c0 + p.c1) * kTileRows + threadIdx.x; idx < p.cin * kTileRows; idx += kEpiThreads) {
+                *reinterpret_cast<uint4*>(dst + (size_t)idx * 16) = make_uint4(0u, 0u, 0u, 0u);
+                if (sx_t) *reinterpret_cast<uint4*>(sx_t + (size_t)idx * 16) = make_uint4(0u, 0u, 0u, 0u);
+            }
+        };
+        auto stage_part = [&](int tile, uint8_t* dst, int part) { stage_issue(tile, part); stage_commit(tile, dst, part); };
+        auto l2_pull = [&](int tile) {  // one thread: the rows of `tile` into L2
+            if (tile < tiles && threadIdx.x == 0) {
+                const int nrows = min(kTileRows, p.M - tile * kTileRows);
+                if (p.x0) l2_prefetch(p.x0 + (size_t)tile * kTileRows * p.ld0, ((size_t)(nrows - 1) * p.ld0 + p.k0) * 4);
+                if (p.x1) l2_prefetch(p.x1 + (size_t)tile * kTileRows * p.ld1, ((size_t)(nrows - 1) * p.ld1 + p.k1) * 4);
+            }
+        };
+        const bool dbl = p.pg.a_alt != 0;  // second operand buffer available
+        if ((int)blockIdx.x < tiles) {
+            l2_pull(blockIdx.x + gridDim.x);
+            for (int part = 0; part < n_parts; ++part) stage_part(blockIdx.x, act, part);
             es.release();
+        }
+        int it = 0;
+        for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
+            const int row0 = tile * kTileRows;
+            uint8_t* act_cur = act + ((it & 1) ? p.pg.a_alt : 0u);
+            uint8_t* act_nxt = act + ((it & 1) ? 0u : p.pg.a_alt);
+            const int nxt = tile + gridDim.x;
+            const bool has_next = nxt < tiles;
+            int parts_done = 0;
+            l2_pull(nxt + gridDim.x);
             const int grow = row0 + row;
             const bool live = grow < p.M;
             for (int l = 0; l <= last; ++l) {
                 es.wait_acc();
                 const float* bias = sbias + l * p.bstride;
                 if (l < last) {
+                    // a slice of the next tile's input: loads in flight across this epilogue, stored after its release
+                    const bool slice = dbl && has_next && parts_done < n_parts;
+                    if (slice) stage_issue(nxt, parts_done);
                     // hidden layer: h = ELU(acc + b) -> bf16 A operand of the next layer (in place) [+ TCM save]
                     const int per = (p.ch + kEpiGroups - 1) / kEpiGroups;
                     const int cbeg = grp * per, cend = min(p.ch, cbeg + per);
@@ -124,10 +230,12 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_fwd_tc_kernel(const __gr
                         lds8(bias + c * 8, b);
 #pragma unroll
                         for (int i = 0; i < 8; ++i) v[i] = elu_fast(v[i] + b[i]);
-                        st_chunk_bf16(act + ((size_t)c * kTileRows + row) * 16, v);
-                        if (sv) st_chunk_bf16(tcm_at(sv, p.ch, tile, c, row), v);
+                        const uint4 q = pack_bf16x8(v);
+                        *reinterpret_cast<uint4*>(act_cur + ((size_t)c * kTileRows + row) * 16) = q;
+                        if (sv) *reinterpret_cast<uint4*>(tcm_at(sv, p.ch, tile, c, row)) = q;
                     });
                     es.release();
+                    if (slice) stage_commit(nxt, act_nxt, parts_done++);
                 } else {
                     // output layer: y = acc + b (fp32, row-major)
                     const int oc = (p.out_dim + 7) / 8;
@@ -143,8 +251,14 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_fwd_tc_kernel(const __gr
                             }
                         }
                     }
-                    // the next tile's input staging is followed by release(), which also covers these loads
                 }
+            }
+            if (has_next) {
+                // whatever is left of the next tile's input (everything when there is no second buffer: the operand
+                // buffer is free now that the output GEMM has retired); release() also covers the TMEM loads above
+                uint8_t* dst = dbl ? act_nxt : act;
+                while (parts_done < n_parts) stage_part(nxt, dst, parts_done++);
+                es.release();
             }
         }
     }
@@ -199,20 +313,28 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_bwd_tc_kernel(const __gr
             es.release();
             const int grow = row0 + row;
             const bool live = grow < p.M;
+            // the next tile's saved activations are pulled into L2 while this tile is processed
+            {
+                const int nxt = tile + gridDim.x;
+                if (nxt < tiles && threadIdx.x == 0)
+                    for (int l = 0; l < last; ++l) l2_prefetch(tcm_at(p.sh[l], p.ch, nxt, 0, 0), (size_t)p.ch * kChunkBytes);
+            }
             for (int l = last; l >= 1; --l) {
-                es.wait_acc();
                 const int per = (p.ch + kEpiGroups - 1) / kEpiGroups;
                 const int cbeg = grp * per, cend = min(p.ch, cbeg + per);
                 const __nv_bfloat16* hs = p.sh[l - 1];
                 __nv_bfloat16* dsv = p.dys[l - 1];
-                epi_for_chunks(tmem_base, 0, cbeg, cend, [&](int c, float (&v)[8]) {
-                    float h[8];
-                    ld_chunk_bf16(tcm_at(hs, p.ch, tile, c, row), h);
+                epi_for_chunks_saved(es, tmem_base, 0, cbeg, cend,
+                    [&](int c) { return *reinterpret_cast<const uint4*>(tcm_at(hs, p.ch, tile, c, row)); },
+                    [&](int c, float (&v)[8], const uint4 hq) {
+                        float h[8];
+                        unpack_bf16x8(hq, h);
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) v[i] = live ? v[i] * (h[i] > 0.f ? 1.f : h[i] + 1.f) : 0.f;
-                    st_chunk_bf16(act + ((size_t)c * kTileRows + row) * 16, v);
-                    if (dsv) st_chunk_bf16(tcm_at(dsv, p.ch, tile, c, row), v);
-                });
+                        for (int i = 0; i < 8; ++i) v[i] = live ? v[i] * (h[i] > 0.f ? 1.f : h[i] + 1.f) : 0.f;
+                        const uint4 q = pack_bf16x8(v);
+                        *reinterpret_cast<uint4*>(act + ((size_t)c * kTileRows + row) * 16) = q;
+                        if (dsv) *reinterpret_cast<uint4*>(tcm_at(dsv, p.ch, tile, c, row)) = q;
+                    });
                 if (l > 1 || want_dx) es.release();
             }
             if (want_dx) {
@@ -295,7 +417,7 @@ static int add_phase(MlpTcPlan& pl, uint8_t* wbase, int kchunks, int npad, const
     return DRM_OK;
 }
 
-static int finish_plan(MlpTcPlan& pl, int act_chunks) {
+static int finish_plan(MlpTcPlan& pl, int act_chunks, bool double_act = false) {
     MlpTcDev& d = pl.dev;
     TcProgram& pg = d.pg;
     d.bias_off = 256;
@@ -303,8 +425,11 @@ static int finish_plan(MlpTcPlan& pl, int act_chunks) {
     if (rup(d.out_dim, 16) > widest) widest = rup(d.out_dim, 16);
     d.bstride = widest;
     d.act_off = (uint32_t)rup_sz(d.bias_off + (size_t)d.n_linear * d.bstride * sizeof(float), 1024);
-    pg.stage_off = (uint32_t)rup_sz(d.act_off + (size_t)act_chunks * kChunkBytes, 1024);
+    pg.a_alt = 0;
     pg.stage_bytes = 32 * 1024;
+    if (double_act && d.act_off + 2 * (size_t)act_chunks * kChunkBytes + 2 * pg.stage_bytes <= kMaxSmem)
+        pg.a_alt = (uint32_t)act_chunks * kChunkBytes;  // second operand buffer: the next tile is staged under this one
+    pg.stage_off = (uint32_t)rup_sz(d.act_off + (size_t)act_chunks * kChunkBytes + pg.a_alt, 1024);
     int stages = (int)(((size_t)kMaxSmem - pg.stage_off) / pg.stage_bytes);
     if (stages > 4) stages = 4;
     DRM_REQUIRE(stages >= 2, DRM_E_SHAPE, "MLP too wide for the bf16 path's shared memory");
@@ -332,7 +457,7 @@ static int plan_fwd(const drm_mlp_call* c, uint8_t* wbase, MlpTcPlan& pl) {
         }
         if (rc) return rc;
     }
-    return finish_plan(pl, d.cin > d.ch ? d.cin : d.ch);
+    return finish_plan(pl, d.cin > d.ch ? d.cin : d.ch, true);
 }
 
 static int plan_bwd(const drm_mlp_call* c, bool want_dx, uint8_t* wbase, MlpTcPlan& pl) {
@@ -485,3 +610,15 @@ int mlp_tc_bwd(const drm_mlp_bwd_call* bc, cudaStream_t stream) {
 
 }  // namespace tc
 }  // namespace drm
+
+#ifdef DRM_TIMELINE
+// Debug only: handshake stamps CTA 0 of the batched-MLP kernels recorded (see tools/timeline.py).
+extern "C" int drm_debug_timeline_mlp(long long* stamps, int* counts) {
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(stamps, drm::tc::g_tl, sizeof(long long) * 4 * 4096);
+    cudaMemcpyFromSymbol(counts, drm::tc::g_tl_n, sizeof(int) * 4);
+    int zero[4] = {0, 0, 0, 0};
+    cudaMemcpyToSymbol(drm::tc::g_tl_n, zero, sizeof(zero));
+    return 0;
+}
+#endif

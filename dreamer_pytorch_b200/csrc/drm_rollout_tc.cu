@@ -138,7 +138,6 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
             es.release();
             for (int t = 0; t < p.T; ++t) {
                 const int ts = t * p.ntiles + tile;
-                const size_t trow = (size_t)t * p.n + grow;
                 // ------------------------------------------------------------ actor hidden layers
                 for (int l = 0; l < p.an - 1; ++l) {
                     es.wait_acc();

@@ -203,6 +203,9 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // Bulk L2 prefetch of a contiguous global range (any alignment: widened to 16-byte units; a prefetch never faults
 // inside the caller's allocation granule).  One thread, one instruction per range.
 __device__ __forceinline__ void l2_prefetch(const void* ptr, size_t bytes) {
+#ifdef DRM_NO_L2PF
+    return;
+#endif
     const uintptr_t a = reinterpret_cast<uintptr_t>(ptr) & ~(uintptr_t)15;
     const uintptr_t e = (reinterpret_cast<uintptr_t>(ptr) + bytes + 15) & ~(uintptr_t)15;
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a), "r"((uint32_t)(e - a)) : "memory");

@@ -45,6 +45,7 @@ struct TcProgram {
     int n_stages;
     int stage_bytes;
     uint32_t stage_off;  // byte offset of stage 0 in dynamic smem (1024-aligned)
+    uint32_t a_alt;      // added to every A offset on odd repetitions (double-buffered operand of the batched MLP)
     TcOp op[kMaxOps];
 };
 
@@ -150,6 +151,7 @@ __device__ __forceinline__ void chain_mma(const TcProgram& pg, ChainBars* bars, 
     uint32_t phase = 0, ready_phase = 0;
     bool phase_start = true;
     for (int rep = 0; rep < reps; ++rep) {
+        const uint32_t a_base = smem_base + ((rep & 1) ? pg.a_alt : 0u);
         for (int i = 0; i < n_ops; ++i) {
             const TcOp op = pg.op[i];
             if (phase_start) {
@@ -166,8 +168,8 @@ __device__ __forceinline__ void chain_mma(const TcProgram& pg, ChainBars* bars, 
             const uint32_t idesc = make_idesc_bf16(kTileRows, (int)n);
             const uint32_t b_flags = n << 16;                      // LBO = n * 16 B, in 16-byte units
             const uint32_t b_step = 2u * n;                        // two K chunks of the weight slab, 16-byte units
-            uint32_t a_lo = (((smem_base + op.a_off[0]) & 0x3FFFFu) >> 4) | a_lo_flags;
-            const uint32_t a_lo1 = (((smem_base + op.a_off[1]) & 0x3FFFFu) >> 4) | a_lo_flags;
+            uint32_t a_lo = (((a_base + op.a_off[0]) & 0x3FFFFu) >> 4) | a_lo_flags;
+            const uint32_t a_lo1 = (((a_base + op.a_off[1]) & 0x3FFFFu) >> 4) | a_lo_flags;
             const uint32_t d_addr = tmem_base + op.d_col;
             uint32_t acc = op.accumulate;
             int c = 0;
