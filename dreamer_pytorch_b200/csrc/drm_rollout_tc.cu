@@ -16,6 +16,7 @@
 //   an+2     i_n accumulated onto r*h_n, z A = HB, HB|ST[deter]          -> deter' -> ST[deter], deter out
 //   an+3     prior hidden                 A = ST[deter]                  -> HB
 //   an+4     prior mean | std, sample     A = HB                         -> ST[stoch], prior_* out
+#include <stdlib.h>
 #include <string.h>
 #include "drm_rollout.cuh"
 #include "drm_tc_chain.cuh"
@@ -26,7 +27,7 @@ namespace tc {
 constexpr int kMaxPerD = 8;  // deter chunks per epilogue thread (cdp <= 32)
 
 struct RollTcDev {
-    int T, n, ntiles, act_dist, training;
+    int T, n, ntiles, tr, act_dist, training;  // tr: rows per tile (64 or 128)
     int A, S, D, Hd, ah, an, Aout;
     int cs, cd, cdp, ca, chh, cha;  // chunk counts: stoch, deter (exact / even), action, Hd (even), actor hidden (even)
     int Sp;                         // column of the first std accumulator in the prior's last Linear (S rounded up to 8)
@@ -71,7 +72,15 @@ __host__ __device__ inline BiasLayout bias_layout(int an, int Ap, int Hp, int Dp
     return b;
 }
 
+template <int TR>
 __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const __grid_constant__ RollTcDev p) {
+    // tile geometry of this instantiation (shadows the 128-row constants of drm_tc_chain.cuh)
+    constexpr int kTileRows = TR;
+    constexpr int kChunkBytes = TR * 16;
+    constexpr bool kHalf = TR == 64;
+    auto tcm_at = [](auto* base, int chunks_per_tile, int tile, int chunk, int row) {
+        return base + (((size_t)tile * chunks_per_tile + chunk) * TR + row) * 8;
+    };
     extern __shared__ __align__(1024) uint8_t smem[];
     ChainBars* bars = reinterpret_cast<ChainBars*>(smem);
     const int S = p.S, D = p.D, A = p.A;
@@ -95,22 +104,32 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
     if (warp == kEpiWarps) {
         chain_producer(p.pg, bars, smem, p.wstream, reps);
     } else if (warp == kEpiWarps + 1) {
-        chain_mma(p.pg, bars, smem, tmem_base, reps);
+        chain_mma<TR>(p.pg, bars, smem, tmem_base, reps);
     } else {
         EpiSync es(bars);
         uint8_t* st = smem + p.st_off;
         uint8_t* hb = smem + p.hb_off;
-        const int row = epi_row(), grp = epi_group();
+        const EpiGeo<TR> geo;
+        const int row = geo.row, grp = epi_group();
+        const bool lead = geo.half == 0;  // half tiles: lanes 16..31 duplicate the rows of lanes 0..15
         const int cfeat = p.cs + p.cdp;
         const bool save = p.training != 0;
         const size_t lo_stride = (size_t)p.cdp * kTileRows * 8;
         const int tid = threadIdx.x, lane = threadIdx.x & 31;
         float* hbf = reinterpret_cast<float*>(hb);
         // this thread's chunk ranges for the three operand widths
-        const int per_a = (p.cha + kEpiGroups - 1) / kEpiGroups, a_beg = grp * per_a, a_end = min(p.cha, a_beg + per_a);
-        const int per_h = (p.chh + kEpiGroups - 1) / kEpiGroups, h_beg = grp * per_h, h_end = min(p.chh, h_beg + per_h);
-        const int per_d = (p.cdp + kEpiGroups - 1) / kEpiGroups, d_beg = grp * per_d, d_end = min(p.cdp, d_beg + per_d);
-        const int per_s = (p.cs + kEpiGroups - 1) / kEpiGroups, s_beg = grp * per_s, s_end = min(p.cs, s_beg + per_s);
+        // (ranges are TMEM chunk indices; x_go is this thread's offset to global chunk indices, see EpiGeo)
+        auto rng = [&](int nchunks, int& beg, int& end, int& go) {
+            const int nct = geo.tmem_chunks(nchunks), per = (nct + kEpiGroups - 1) / kEpiGroups;
+            beg = min(nct, grp * per); end = min(nct, beg + per); go = geo.goff(nchunks);
+        };
+        int a_beg, a_end, a_go, h_beg, h_end, h_go, d_beg, d_end, d_go;
+        rng(p.cha, a_beg, a_end, a_go);
+        rng(p.chh, h_beg, h_end, h_go);
+        rng(p.cdp, d_beg, d_end, d_go);
+        const int DpT = kHalf ? Dp / 2 : Dp;  // TMEM columns of a D-wide accumulator
+        // prior head: mean chunks; half tiles keep mean in lanes 0..15 and std in lanes 16..31 of the same columns
+        const int per_s = (p.cs + kEpiGroups - 1) / kEpiGroups, s_beg = min(p.cs, grp * per_s), s_end = min(p.cs, s_beg + per_s);
         for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
             const int row0 = tile * kTileRows;
             const int grow = row0 + row;
@@ -150,7 +169,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                         for (int i = 0; i < 8; ++i) v[i] = elu_fast(v[i] + b[i]);
                         st_chunk_bf16(hb + ((size_t)c * kTileRows + row) * 16, v);
                         if (sv) st_chunk_bf16(tcm_at(sv, p.cha, ts, c, row), v);
-                    });
+                    }, a_go);
                     es.release();
                 }
                 // ------------------------------------------------------------ actor output + action (agent.py:101-117)
@@ -159,37 +178,47 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                 // coalesced loads before the wait, and write action / raw blocks back coalesced after the release.
                 const int arows = min(kTileRows, p.n - row0);
                 float* sN = hbf;                       // [128][A] noise
-                float* sA = hbf + kTileRows * 16;      // [128][A] action
-                float* sR = hbf + 2 * kTileRows * 16;  // [128][Aout] pre-distribution actor output
+                float* sA = hbf + kTileRows * 16;      // [rows][A] action
+                float* sR = hbf + 2 * kTileRows * 16;  // [rows][Aout] pre-distribution actor output
+                constexpr int kG0 = 128;               // threads of column group 0
                 float nzr[16];
                 if (grp == 0) {
                     const float* nz_t = p.noise_act + ((size_t)t * p.n + row0) * A;
 #pragma unroll
                     for (int k = 0; k < 16; ++k) {
-                        const int i = tid + k * kTileRows;
+                        const int i = tid + k * kG0;
                         nzr[k] = (k < A && i < arows * A) ? __ldg(nz_t + i) : 0.f;
                     }
                 }
                 es.wait_acc();
                 if (grp == 0) {
 #pragma unroll
-                    for (int k = 0; k < 16; ++k) if (k < A) sN[tid + k * kTileRows] = nzr[k];
-                    named_bar<kTileRows, 2>();
+                    for (int k = 0; k < 16; ++k) if (k < A && tid + k * kG0 < kTileRows * A) sN[tid + k * kG0] = nzr[k];
+                    named_bar<kG0, 2>();
                     float raw[16];
                     {
                         float v0[8], v1[8], b0[8], b1[8];
                         tmem_ld8(epi_taddr(tmem_base, 0), v0);
-                        tmem_ld8(epi_taddr(tmem_base, 8), v1);
+                        if (!kHalf) tmem_ld8(epi_taddr(tmem_base, 8), v1);
                         lds8(sbias + bl.ba_last, b0);
                         lds8(sbias + bl.ba_last + 8, b1);
                         tmem_ld_wait();
+                        if (kHalf) {
+                            // columns 0..7 live in lanes 0..15, columns 8..15 in lanes 16..31 of the same TMEM columns
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                const float o = __shfl_xor_sync(0xffffffffu, v0[i], 16);
+                                v1[i] = lead ? o : v0[i];
+                                v0[i] = lead ? v0[i] : o;
+                            }
+                        }
 #pragma unroll
                         for (int i = 0; i < 8; ++i) { raw[i] = v0[i] + b0[i]; raw[8 + i] = v1[i] + b1[i]; }
                     }
                     float act[16];
 #pragma unroll
                     for (int j = 0; j < 16; ++j) act[j] = 0.f;
-                    if (live) {
+                    if (live && lead) {
                         const float* nz = sN + row * A;
                         if (p.act_dist == DRM_DIST_TANH_NORMAL) {
 #pragma unroll
@@ -236,27 +265,29 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                             }
                         }
                     }
+                    if (lead) {
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        if (j < A) sA[row * A + j] = act[j];
-                        if (j < p.Aout) sR[row * p.Aout + j] = raw[j];
-                    }
-                    uint8_t* sa = st + (size_t)cfeat * kChunkBytes;
-                    for (int c = 0; c < p.ca; ++c) {
-                        float v[8];
+                        for (int j = 0; j < 16; ++j) {
+                            if (j < A) sA[row * A + j] = act[j];
+                            if (j < p.Aout) sR[row * p.Aout + j] = raw[j];
+                        }
+                        uint8_t* sa = st + (size_t)cfeat * kChunkBytes;
+                        for (int c = 0; c < p.ca; ++c) {
+                            float v[8];
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) v[i] = c == 0 ? act[i] : act[8 + i];
-                        st_chunk_bf16(sa + ((size_t)c * kTileRows + row) * 16, v);
+                            for (int i = 0; i < 8; ++i) v[i] = c == 0 ? act[i] : act[8 + i];
+                            st_chunk_bf16(sa + ((size_t)c * kTileRows + row) * 16, v);
+                        }
                     }
                 }
                 es.release();
                 if (grp == 0) {
-                    named_bar<kTileRows, 2>();
+                    named_bar<kG0, 2>();
                     float* ao = p.action_out + ((size_t)t * p.n + row0) * A;
-                    for (int i = tid; i < arows * A; i += kTileRows) ao[i] = sA[i];
+                    for (int i = tid; i < arows * A; i += kG0) ao[i] = sA[i];
                     if (save) {
                         float* ro = p.sv_raw + ((size_t)t * p.n + row0) * p.Aout;
-                        for (int i = tid; i < arows * p.Aout; i += kTileRows) ro[i] = sR[i];
+                        for (int i = tid; i < arows * p.Aout; i += kG0) ro[i] = sR[i];
                     }
                 }
                 named_bar<kEpiThreads, 1>();  // the hidden buffer is written again by the next epilogue
@@ -272,12 +303,12 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                         for (int i = 0; i < 8; ++i) v[i] = elu_fast(v[i] + b[i]);
                         st_chunk_bf16(hb + ((size_t)c * kTileRows + row) * 16, v);
                         if (sv) st_chunk_bf16(tcm_at(sv, p.chh, ts, c, row), v);
-                    });
+                    }, h_go);
                 }
                 es.release();
                 // ------------------------------------------------------------ GRU, part 1: r and h_n  (torch GRUCell, rnns.py:102)
                 es.wait_acc();
-                epi_for_chunks2(tmem_base, 0, Dp, d_beg, d_end, [&](int c, float (&ar)[8], float (&ahn)[8]) {
+                epi_for_chunks2(tmem_base, 0, DpT, d_beg, d_end, [&](int c, float (&ar)[8], float (&ahn)[8]) {
                     float br[8], bh[8], rr[8], hn[8];
                     lds8(sbias + bl.r + c * 8, br);
                     lds8(sbias + bl.hn + c * 8, bh);
@@ -287,12 +318,12 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                         hn[i] = ahn[i] + bh[i];
                         ar[i] = rr[i] * hn[i];
                     }
-                    tmem_st8(epi_taddr(tmem_base, c * 8), ar);  // i_n is accumulated on top of r * h_n by the next phase
+                    tmem_st8(epi_taddr(tmem_base, (c - d_go) * 8), ar);  // i_n is accumulated on top of r * h_n by the next phase
                     if (save) {
                         st_chunk_bf16(tcm_at(p.sv_r, p.cdp, ts, c, row), rr);
                         st_chunk_bf16(tcm_at(p.sv_hn, p.cdp, ts, c, row), hn);
                     }
-                });
+                }, d_go);
                 tmem_st_wait();
                 es.release();
                 // ------------------------------------------------------------ GRU, part 2: n, z, h'
@@ -303,9 +334,9 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                     const __nv_bfloat16* lo_cur = p.sv_lo + (size_t)(p.lo_per_cta ? (int)blockIdx.x : ts) * lo_stride;
 #pragma unroll
                     for (int i = 0; i < kMaxPerD; ++i) {
-                        const int c = d_beg + i;
+                        const int c = d_beg + i + d_go;
                         lo_in[i] = make_uint4(0u, 0u, 0u, 0u);
-                        if (c < d_end) lo_in[i] = *reinterpret_cast<const uint4*>(lo_cur + ((size_t)c * kTileRows + row) * 8);
+                        if (d_beg + i < d_end) lo_in[i] = *reinterpret_cast<const uint4*>(lo_cur + ((size_t)c * kTileRows + row) * 8);
                     }
                 }
                 es.wait_acc();
@@ -315,11 +346,11 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                     __nv_bfloat16* lo_nxt = p.sv_lo + (size_t)(p.lo_per_cta ? (int)blockIdx.x : ts + p.ntiles) * lo_stride;
 #pragma unroll
                     for (int i = 0; i < kMaxPerD; ++i) {
-                        const int c = d_beg + i;
-                        if (c < d_end) {
+                        const int ct = d_beg + i, c = ct + d_go;  // TMEM chunk, global chunk
+                        if (ct < d_end) {
                             float an_[8], az[8], bn[8], bz[8], zz[8], nn[8], hv[8], hp[8], hl[8];
-                            tmem_ld8(epi_taddr(tmem_base, c * 8), an_);
-                            tmem_ld8(epi_taddr(tmem_base, Dp + c * 8), az);
+                            tmem_ld8(epi_taddr(tmem_base, ct * 8), an_);
+                            tmem_ld8(epi_taddr(tmem_base, DpT + ct * 8), az);
                             uint8_t* st_c = st + ((size_t)(p.cs + c) * kTileRows + row) * 16;
                             unpack_bf16x8(*reinterpret_cast<const uint4*>(st_c), hp);
                             unpack_bf16x8(lo_in[i], hl);
@@ -394,7 +425,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                         for (int i = 0; i < 8; ++i) v[i] = elu_fast(v[i] + b[i]);
                         st_chunk_bf16(hb + ((size_t)c * kTileRows + row) * 16, v);
                         if (sv) st_chunk_bf16(tcm_at(sv, p.chh, ts, c, row), v);
-                    });
+                    }, h_go);
                 }
                 es.release();
                 // ------------------------------------------------------------ prior mean | std, sample  (rnns.py:103-106)
@@ -412,7 +443,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                     }
                     named_bar<kEpiThreads, 1>();
                     const bool feat_next = save && t + 1 < p.T;
-                    epi_for_chunks2(tmem_base, 0, p.Sp, s_beg, s_end, [&](int c, float (&am)[8], float (&as_)[8]) {
+                    auto prior_chunk = [&](int c, float (&am)[8], float (&as_)[8]) {
                         float bm[8], bs[8], sv[8];
                         lds8(sbias + bl.p2m + c * 8, bm);
                         lds8(sbias + bl.p2s + c * 8, bs);
@@ -420,7 +451,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                         for (int i = 0; i < 8; ++i) {
                             const int j = c * 8 + i;
                             float st_ = 0.f;
-                            if (j < S) {
+                            if (j < S && lead) {
                                 const float mean = am[i] + bm[i];
                                 const float std = softplus_fast(as_[i] + bs[i]) + p.min_std;
                                 const int o = row * S + j;
@@ -429,9 +460,28 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                             }
                             sv[i] = st_;
                         }
-                        st_chunk_bf16(st + ((size_t)c * kTileRows + row) * 16, sv);
-                        if (feat_next) st_chunk_bf16(tcm_at(p.sv_feat, cfeat, ts + p.ntiles, c, row), sv);
-                    });
+                        if (lead) {
+                            st_chunk_bf16(st + ((size_t)c * kTileRows + row) * 16, sv);
+                            if (feat_next) st_chunk_bf16(tcm_at(p.sv_feat, cfeat, ts + p.ntiles, c, row), sv);
+                        }
+                    };
+                    if (kHalf) {
+                        // mean chunk c sits in lanes 0..15, std chunk c in lanes 16..31 of the same TMEM columns
+                        for (int c = s_beg; c < s_end; ++c) {
+                            float mine[8], am[8], as_[8];
+                            tmem_ld8(epi_taddr(tmem_base, c * 8), mine);
+                            tmem_ld_wait();
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                const float o = __shfl_xor_sync(0xffffffffu, mine[i], 16);
+                                am[i] = lead ? mine[i] : o;
+                                as_[i] = lead ? o : mine[i];
+                            }
+                            prior_chunk(c, am, as_);
+                        }
+                    } else {
+                        epi_for_chunks2(tmem_base, 0, p.Sp, s_beg, s_end, prior_chunk);
+                    }
                 }
                 if (t + 1 < p.T) es.release();
                 named_bar<kEpiThreads, 1>();
@@ -470,7 +520,14 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
 //   6  d actor hidden   = d raw . Wa[last]            A = G2              -> R_H
 //   7.. d actor hidden  = dh . Wa[l]                  A = GA (as HB)      -> R_H
 // ------------------------------------------------------------------------------------------------
+template <int TR>
 __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const __grid_constant__ RollTcDev p) {
+    constexpr int kTileRows = TR;  // tile geometry of this instantiation (see rollout_fwd_tc_kernel)
+    constexpr int kChunkBytes = TR * 16;
+    constexpr bool kHalf = TR == 64;
+    auto tcm_at = [](auto* base, int chunks_per_tile, int tile, int chunk, int row) {
+        return base + (((size_t)tile * chunks_per_tile + chunk) * TR + row) * 8;
+    };
     extern __shared__ __align__(1024) uint8_t smem[];
     ChainBars* bars = reinterpret_cast<ChainBars*>(smem);
     const uint32_t tmem_base = chain_setup(bars, p.pg);
@@ -480,17 +537,26 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
     if (warp == kEpiWarps) {
         chain_producer(p.pg, bars, smem, p.wstream, reps);
     } else if (warp == kEpiWarps + 1) {
-        chain_mma(p.pg, bars, smem, tmem_base, reps);
+        chain_mma<TR>(p.pg, bars, smem, tmem_base, reps);
     } else {
         EpiSync es(bars);
         uint8_t* ga = smem + p.ga_off;
         uint8_t* gb = smem + p.gb_off;
         uint8_t* g2 = smem + p.g2_off;
-        const int row = epi_row(), grp = epi_group(), lane = threadIdx.x & 31, tid = threadIdx.x;
+        const EpiGeo<TR> geo;
+        const int row = geo.row, grp = epi_group(), lane = threadIdx.x & 31, tid = threadIdx.x;
+        const bool lead = geo.half == 0;  // half tiles: lanes 16..31 see the second column half of every accumulator
         const int S = p.S, D = p.D, A = p.A;
         const int Dp = p.cdp * 8;
+        const int DpT = kHalf ? Dp / 2 : Dp;
         const int cfeat = p.cs + p.cdp;
-        const int colC = max(p.chh, p.cha) * 8, colAS = colC + Dp;
+        const int colC = max(p.chh, p.cha) * (kHalf ? 4 : 8), colAS = colC + DpT;
+        // R_AS: 128-row tiles [stoch Sp | action 16]; half tiles: stoch in lanes 0..15, action in lanes 16..31 of columns 0..Sp
+        const int colAct = kHalf ? colAS : colAS + p.Sp;
+        auto rng = [&](int nchunks, int& beg, int& end, int& go) {
+            const int nct = geo.tmem_chunks(nchunks), per = (nct + kEpiGroups - 1) / kEpiGroups;
+            beg = min(nct, grp * per); end = min(nct, beg + per); go = geo.goff(nchunks);
+        };
         __nv_bfloat16* stash_in = p.stash + (size_t)blockIdx.x * 2 * p.cdp * kTileRows * 8;
         __nv_bfloat16* stash_hn = stash_in + (size_t)p.cdp * kTileRows * 8;
         const int last = p.an - 1;
@@ -537,7 +603,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                 float z[8];
 #pragma unroll
                 for (int i = 0; i < 8; ++i) z[i] = 0.f;
-                for (int c = grp; c < p.cdp; c += kEpiGroups) tmem_st8(epi_taddr(tmem_base, colC + c * 8), z);
+                for (int c = grp; c < geo.tmem_chunks(p.cdp); c += kEpiGroups) tmem_st8(epi_taddr(tmem_base, colC + c * 8), z);
                 for (int c = grp; c < p.cs; c += kEpiGroups) tmem_st8(epi_taddr(tmem_base, colAS + c * 8), z);
                 tmem_st_wait();
             }
@@ -561,7 +627,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                         for (int i = 0; i < 8; ++i) {
                             const int j = c * 8 + i;
                             dm[i] = 0.f; ds[i] = 0.f;
-                            if (live && j < S) {
+                            if (live && lead && j < S) {
                                 const int o = row * S + j;
                                 const float dst = (p.g_prior_stoch ? sGst[o] : 0.f) + cs_[i];
                                 dm[i] = (p.g_prior_mean ? sGm[o] : 0.f) + dst;
@@ -569,15 +635,17 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                                 ds[i] = dsd * (1.f - __expf(-(sStd[o] - p.min_std)));  // sigmoid(raw) from softplus(raw)
                             }
                         }
-                        st_chunk_bf16(g2 + ((size_t)c * kTileRows + row) * 16, dm);
-                        st_chunk_bf16(g2 + ((size_t)(p.cs + c) * kTileRows + row) * 16, ds);
+                        if (lead) {
+                            st_chunk_bf16(g2 + ((size_t)c * kTileRows + row) * 16, dm);
+                            st_chunk_bf16(g2 + ((size_t)(p.cs + c) * kTileRows + row) * 16, ds);
+                        }
                     }
                 }
                 es.release();
                 // ------------------------------------------------------------ d prior hidden
                 {
-                    const int per = (p.chh + kEpiGroups - 1) / kEpiGroups;
-                    const int cbeg = grp * per, cend = min(p.chh, cbeg + per);
+                    int cbeg, cend, go;
+                    rng(p.chh, cbeg, cend, go);
                     epi_for_chunks_saved(es, tmem_base, 0, cbeg, cend,
                         [&](int c) { return *reinterpret_cast<const uint4*>(tcm_at(p.sv_hid, p.chh, ts, c, row)); },
                         [&](int c, float (&v)[8], const uint4 hq) {
@@ -586,7 +654,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
 #pragma unroll
                             for (int i = 0; i < 8; ++i) v[i] = live ? v[i] * (h[i] > 0.f ? 1.f : h[i] + 1.f) : 0.f;
                             st_chunk_bf16(ga + ((size_t)c * kTileRows + row) * 16, v);
-                        });
+                        }, [] {}, go);
                 }
                 es.release();
                 // ------------------------------------------------------------ GRU cell (pointwise)
@@ -607,8 +675,8 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                     named_bar<kEpiThreads, 1>();
                 }
                 {
-                    const int per = (p.cdp + kEpiGroups - 1) / kEpiGroups;
-                    const int cbeg = grp * per, cend = min(p.cdp, cbeg + per);
+                    int cbeg, cend, go;
+                    rng(p.cdp, cbeg, cend, go);
                     epi_for_chunks(tmem_base, colC, cbeg, cend, [&](int c, float (&dh)[8]) {
                         float rr[8], zz[8], nn[8], hn[8], dpr[8], dpz[8], din[8], dhn[8], gd[8], hpv[8], hlo[8];
                         ld_chunk_bf16(tcm_at(p.sv_r, p.cdp, ts, c, row), rr);
@@ -641,19 +709,20 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                             dpz[i] = dz * zz[i] * (1.f - zz[i]);
                             dh[i] = d * zz[i];  // carry through h' = (1-z) n + z h
                         }
-                        tmem_st8(epi_taddr(tmem_base, colC + c * 8), dh);
+                        tmem_st8(epi_taddr(tmem_base, colC + (c - go) * 8), dh);
                         st_chunk_bf16(ga + ((size_t)c * kTileRows + row) * 16, dpr);
                         st_chunk_bf16(gb + ((size_t)c * kTileRows + row) * 16, dpz);
                         st_chunk_bf16(stash_in + ((size_t)c * kTileRows + row) * 8, din);
                         st_chunk_bf16(stash_hn + ((size_t)c * kTileRows + row) * 8, dhn);
-                    });
+                    }, go);
                     tmem_st_wait();
                 }
                 es.release();
                 // ------------------------------------------------------------ reload d i_n, d h_n (own writes) -> GA, GB
                 {
-                    const int per = (p.cdp + kEpiGroups - 1) / kEpiGroups;
-                    const int cbeg = grp * per, cend = min(p.cdp, cbeg + per);
+                    int tb, te, go;
+                    rng(p.cdp, tb, te, go);
+                    const int cbeg = tb + go, cend = te + go;  // global chunks
                     es.wait_acc();
 #pragma unroll 2
                     for (int c = cbeg; c < cend; ++c) {
@@ -666,8 +735,8 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                 es.release();
                 // ------------------------------------------------------------ d rnn-input pre-activation
                 {
-                    const int per = (p.chh + kEpiGroups - 1) / kEpiGroups;
-                    const int cbeg = grp * per, cend = min(p.chh, cbeg + per);
+                    int cbeg, cend, go;
+                    rng(p.chh, cbeg, cend, go);
                     epi_for_chunks_saved(es, tmem_base, 0, cbeg, cend,
                         [&](int c) { return *reinterpret_cast<const uint4*>(tcm_at(p.sv_x, p.chh, ts, c, row)); },
                         [&](int c, float (&v)[8], const uint4 hq) {
@@ -676,7 +745,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
 #pragma unroll
                             for (int i = 0; i < 8; ++i) v[i] = live ? v[i] * (h[i] > 0.f ? 1.f : h[i] + 1.f) : 0.f;
                             st_chunk_bf16(ga + ((size_t)c * kTileRows + row) * 16, v);
-                        });
+                        }, [] {}, go);
                     if (p.want_actor && tid == 0) l2_prefetch(tcm_at(p.sv_ah[last - 1], p.cha, ts, 0, 0), p.cha * chunk_img * 2);
                 }
                 es.release();
@@ -689,15 +758,22 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                         float da[16], draw[16];
                         {
                             float v0[8], v1[8];
-                            tmem_ld8(epi_taddr(tmem_base, colAS + p.Sp), v0);
-                            tmem_ld8(epi_taddr(tmem_base, colAS + p.Sp + 8), v1);
+                            tmem_ld8(epi_taddr(tmem_base, colAct), v0);
+                            tmem_ld8(epi_taddr(tmem_base, colAct + 8), v1);
                             tmem_ld_wait();
+                            if (kHalf) {  // the action columns of this row sit in the partner lane (lanes 16..31)
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) {
+                                    v0[i] = __shfl_xor_sync(0xffffffffu, v0[i], 16);
+                                    v1[i] = __shfl_xor_sync(0xffffffffu, v1[i], 16);
+                                }
+                            }
 #pragma unroll
                             for (int i = 0; i < 8; ++i) { da[i] = v0[i]; da[8 + i] = v1[i]; }
                         }
 #pragma unroll
                         for (int j = 0; j < 16; ++j) draw[j] = 0.f;
-                        if (live) {
+                        if (live && lead) {
                             const float* go = p.g_action_out ? p.g_action_out + trow * A : nullptr;
                             const float* raw = p.sv_raw + trow * p.Aout;
                             const float* av = p.action_out + trow * A;
@@ -737,8 +813,10 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                             float v[8];
 #pragma unroll
                             for (int i = 0; i < 8; ++i) v[i] = c == 0 ? draw[i] : draw[8 + i];
-                            st_chunk_bf16(g2 + ((size_t)c * kTileRows + row) * 16, v);
-                            st_chunk_bf16(tcm_at(p.dys_a[last], 2, ts, c, row), v);
+                            if (lead) {
+                                st_chunk_bf16(g2 + ((size_t)c * kTileRows + row) * 16, v);
+                                st_chunk_bf16(tcm_at(p.dys_a[last], 2, ts, c, row), v);
+                            }
                         }
 #pragma unroll
                         for (int j = 0; j < 16; ++j) {
@@ -749,8 +827,8 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                     es.release();
                     // actor hidden layers, last Linear first; layer 0's input (feat) is detached (rnns.py:238)
                     for (int l = last; l >= 1; --l) {
-                        const int per = (p.cha + kEpiGroups - 1) / kEpiGroups;
-                        const int cbeg = grp * per, cend = min(p.cha, cbeg + per);
+                        int cbeg, cend, go;
+                        rng(p.cha, cbeg, cend, go);
                         epi_for_chunks_saved(es, tmem_base, 0, cbeg, cend,
                             [&](int c) { return *reinterpret_cast<const uint4*>(tcm_at(p.sv_ah[l - 1], p.cha, ts, c, row)); },
                             [&](int c, float (&v)[8], const uint4 hq) {
@@ -769,7 +847,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                                     fetch_prior(t - 1);
                                     pf_hid(t - 1);
                                 }
-                            });
+                            }, go);
                         if (l > 1) es.release();
                     }
                 }
@@ -817,10 +895,23 @@ int rollout_tc_supported(const drm_rollout* r) {
     return 1;
 }
 
+// Rows per CTA: 64-row half tiles (see chain_mma) while they put more CTAs on the 148 SMs than 128-row tiles would.
+static int tile_rows_for(int n) {
+    static int forced = -1;
+    if (forced < 0) {
+        const char* e = getenv("DRM_ROLLOUT_TR");  // developer override (64 / 128)
+        forced = e ? atoi(e) : 0;
+    }
+    if (forced == 64 || forced == 128) return forced;
+    const int t128 = (n + 127) / 128;
+    return t128 < kNumSM ? 64 : 128;
+}
+static size_t tcm_bytes_r(int tr, size_t tiles, int chunks) { return tiles * (size_t)chunks * tr * 16; }
+
 static void set_dims(const drm_rollout* r, RollTcDev& d) {
     const drm_rssm& w = r->rssm;
     memset(&d, 0, sizeof(d));
-    d.T = r->steps; d.n = r->n; d.ntiles = (r->n + kTileRows - 1) / kTileRows;
+    d.T = r->steps; d.n = r->n; d.tr = tile_rows_for(r->n); d.ntiles = (r->n + d.tr - 1) / d.tr;
     d.act_dist = r->act_dist; d.training = r->training;
     d.A = w.A; d.S = w.S; d.D = w.D; d.Hd = w.Hd; d.ah = r->actor.hidden; d.an = r->actor.n_linear; d.Aout = r->actor.out_dim;
     d.cs = rup((w.S + 7) / 8, 2); d.cd = (w.D + 7) / 8; d.cdp = rup(d.cd, 2); d.ca = rup((w.A + 7) / 8, 2);
@@ -836,11 +927,12 @@ struct ProgBuilder {
     uint8_t* wbase;
     size_t woff;
     bool ok;
+    int tr;  // 64: every op runs as two column halves into the same TMEM columns (chain_mma), so columns halve
     TcOp* add_op(uint32_t a0, int c0, uint32_t a1, int c1, int n, int d_col, int accumulate, int phase_end) {
         if (pg->n_ops >= kMaxOps) { ok = false; return nullptr; }
         TcOp& op = pg->op[pg->n_ops++];
         op.a_off[0] = a0; op.a_off[1] = a1; op.a_chunks[0] = (uint16_t)c0; op.a_chunks[1] = (uint16_t)c1;
-        op.n = (uint16_t)n; op.d_col = (uint16_t)d_col; op.accumulate = (uint16_t)accumulate; op.phase_end = (uint16_t)phase_end;
+        op.n = (uint16_t)n; op.d_col = (uint16_t)(tr == 64 ? d_col / 2 : d_col); op.accumulate = (uint16_t)accumulate; op.phase_end = (uint16_t)phase_end;
         if (phase_end) pg->n_phases++;
         return &op;
     }
@@ -865,9 +957,9 @@ static int finish_smem(RollTcDev& d, size_t& smem_bytes) {
     d.bias_off = 256;
     const BiasLayout bl = bias_layout(d.an, d.cha * 8, d.chh * 8, d.cdp * 8, d.Sp);
     d.st_off = (uint32_t)rup_sz(d.bias_off + (size_t)bl.total * sizeof(float), 1024);
-    d.hb_off = d.st_off + (uint32_t)(d.cs + d.cdp + d.ca) * kChunkBytes;
+    d.hb_off = d.st_off + (uint32_t)(d.cs + d.cdp + d.ca) * (d.tr * 16);
     const int hb_chunks = d.chh > d.cha ? d.chh : d.cha;
-    pg.stage_off = (uint32_t)rup_sz(d.hb_off + (size_t)hb_chunks * kChunkBytes, 1024);
+    pg.stage_off = (uint32_t)rup_sz(d.hb_off + (size_t)hb_chunks * (d.tr * 16), 1024);
     pg.stage_bytes = 32 * 1024;
     int stages = (int)(((size_t)kMaxSmem - pg.stage_off) / pg.stage_bytes);
     if (stages > 4) stages = 4;
@@ -885,10 +977,11 @@ static int plan_fwd(const drm_rollout* r, uint8_t* wbase, RollTcPlan& pl) {
     int rc = finish_smem(d, pl.smem_bytes); if (rc) return rc;
     const int S = w.S, D = w.D, Hd = w.Hd, A = w.A;
     const int Dp = d.cdp * 8, Hp = d.chh * 8, Ap = d.cha * 8;
-    const uint32_t st_stoch = d.st_off, st_deter = d.st_off + (uint32_t)d.cs * kChunkBytes;
-    const uint32_t st_act = d.st_off + (uint32_t)(d.cs + d.cdp) * kChunkBytes, hb = d.hb_off;
+    const uint32_t cb = (uint32_t)d.tr * 16;  // bytes of one operand chunk
+    const uint32_t st_stoch = d.st_off, st_deter = d.st_off + (uint32_t)d.cs * cb;
+    const uint32_t st_act = d.st_off + (uint32_t)(d.cs + d.cdp) * cb, hb = d.hb_off;
     pl.jobs.n = 0; d.pg.n_ops = 0; d.pg.n_phases = 0;
-    ProgBuilder b{&d.pg, &pl.jobs, wbase, 0, true};
+    ProgBuilder b{&d.pg, &pl.jobs, wbase, 0, true, d.tr};
     PackTcJob* j;
     // actor layer 0 on [stoch | deter]
     b.add_op(st_stoch, d.cs + d.cdp, 0, 0, Ap, 0, 0, 1);
@@ -939,15 +1032,15 @@ static size_t carve_save_tc(const RollTcDev& dd, uint8_t* base, RollTcDev* out) 
         return ptr;
     };
     RollTcDev tmp = dd;
-    tmp.sv_feat = (__nv_bfloat16*)take(tcm_bytes(TS, dd.cs + dd.cdp));
-    for (int l = 0; l < dd.an - 1; ++l) tmp.sv_ah[l] = (__nv_bfloat16*)take(tcm_bytes(TS, dd.cha));
-    tmp.sv_x = (__nv_bfloat16*)take(tcm_bytes(TS, dd.chh));
-    tmp.sv_r = (__nv_bfloat16*)take(tcm_bytes(TS, dd.cdp));
-    tmp.sv_z = (__nv_bfloat16*)take(tcm_bytes(TS, dd.cdp));
-    tmp.sv_n = (__nv_bfloat16*)take(tcm_bytes(TS, dd.cdp));
-    tmp.sv_hn = (__nv_bfloat16*)take(tcm_bytes(TS, dd.cdp));
-    tmp.sv_hid = (__nv_bfloat16*)take(tcm_bytes(TS, dd.chh));
-    tmp.sv_lo = (__nv_bfloat16*)take(tcm_bytes(TS, dd.cdp));
+    tmp.sv_feat = (__nv_bfloat16*)take(tcm_bytes_r(dd.tr, TS, dd.cs + dd.cdp));
+    for (int l = 0; l < dd.an - 1; ++l) tmp.sv_ah[l] = (__nv_bfloat16*)take(tcm_bytes_r(dd.tr, TS, dd.cha));
+    tmp.sv_x = (__nv_bfloat16*)take(tcm_bytes_r(dd.tr, TS, dd.chh));
+    tmp.sv_r = (__nv_bfloat16*)take(tcm_bytes_r(dd.tr, TS, dd.cdp));
+    tmp.sv_z = (__nv_bfloat16*)take(tcm_bytes_r(dd.tr, TS, dd.cdp));
+    tmp.sv_n = (__nv_bfloat16*)take(tcm_bytes_r(dd.tr, TS, dd.cdp));
+    tmp.sv_hn = (__nv_bfloat16*)take(tcm_bytes_r(dd.tr, TS, dd.cdp));
+    tmp.sv_hid = (__nv_bfloat16*)take(tcm_bytes_r(dd.tr, TS, dd.chh));
+    tmp.sv_lo = (__nv_bfloat16*)take(tcm_bytes_r(dd.tr, TS, dd.cdp));
     tmp.sv_raw = (float*)take((size_t)dd.T * dd.n * dd.Aout * sizeof(float));
     if (out) *out = tmp;
     return off;
@@ -991,9 +1084,14 @@ int rollout_tc_fwd(const drm_rollout* r, cudaStream_t stream) {
         d.lo_per_cta = 1;
     }
     rc = launch_pack_tc(pl.jobs, stream); if (rc) return rc;
-    DRM_CUDA_OK(cudaFuncSetAttribute(rollout_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
     ProfScope prof(PROF_ROLLOUT_FWD, stream);
-    rollout_fwd_tc_kernel<<<grid, kChainThreads, pl.smem_bytes, stream>>>(d);
+    if (d.tr == 64) {
+        DRM_CUDA_OK(cudaFuncSetAttribute(rollout_fwd_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
+        rollout_fwd_tc_kernel<64><<<grid, kChainThreads, pl.smem_bytes, stream>>>(d);
+    } else {
+        DRM_CUDA_OK(cudaFuncSetAttribute(rollout_fwd_tc_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
+        rollout_fwd_tc_kernel<128><<<grid, kChainThreads, pl.smem_bytes, stream>>>(d);
+    }
     DRM_CUDA_OK(cudaGetLastError());
     return DRM_OK;
 }
@@ -1002,10 +1100,10 @@ static int finish_smem_bwd(RollTcDev& d, size_t& smem_bytes) {
     TcProgram& pg = d.pg;
     const int hb_chunks = max(max(d.chh, d.cha), d.cdp);
     d.ga_off = 1024;
-    d.gb_off = d.ga_off + (uint32_t)hb_chunks * kChunkBytes;
-    d.g2_off = d.gb_off + (uint32_t)d.cdp * kChunkBytes;
+    d.gb_off = d.ga_off + (uint32_t)hb_chunks * (d.tr * 16);
+    d.g2_off = d.gb_off + (uint32_t)d.cdp * (d.tr * 16);
     const int g2_chunks = 2 * d.cs > 2 ? 2 * d.cs : 2;
-    pg.stage_off = (uint32_t)rup_sz(d.g2_off + (size_t)g2_chunks * kChunkBytes, 1024);
+    pg.stage_off = (uint32_t)rup_sz(d.g2_off + (size_t)g2_chunks * (d.tr * 16), 1024);
     pg.stage_bytes = 32 * 1024;
     int stages = (int)(((size_t)kMaxSmem - pg.stage_off) / pg.stage_bytes);
     if (stages > 4) stages = 4;
@@ -1025,11 +1123,13 @@ static int plan_bwd(const drm_rollout* r, bool want_actor, uint8_t* wbase, RollT
     const int S = w.S, D = w.D, Hd = w.Hd, A = w.A;
     const int Dp = d.cdp * 8, Hp = d.chh * 8, Ap = d.cha * 8;
     const int colC = (d.chh > d.cha ? d.chh : d.cha) * 8, colAS = colC + Dp;
-    const int nAS = rup(d.Sp + 16, 16);
+    // half tiles: the stoch columns must fill the first column half exactly (lanes 0..15), the action the second
+    const int nAS = d.tr == 64 ? 2 * d.Sp : rup(d.Sp + 16, 16);
+    DRM_REQUIRE(d.tr != 64 || d.Sp >= 16, DRM_E_SHAPE, "stoch too narrow for half tiles");
     DRM_REQUIRE(colAS + nAS <= kTmemCols, DRM_E_SHAPE, "model too wide for the bf16 rollout's tensor memory");
     const uint32_t ga = d.ga_off, gb = d.gb_off, g2 = d.g2_off;
     pl.jobs.n = 0; d.pg.n_ops = 0; d.pg.n_phases = 0;
-    ProgBuilder b{&d.pg, &pl.jobs, wbase, 0, true};
+    ProgBuilder b{&d.pg, &pl.jobs, wbase, 0, true, d.tr};
     PackTcJob* j;
     // 1: d prior hidden = d[mean|std] . W_p2
     b.add_op(g2, 2 * d.cs, 0, 0, Hp, 0, 0, 1);
@@ -1078,9 +1178,9 @@ static size_t carve_bwd_ws(const RollTcDev& dd, size_t wbytes, uint8_t* base, Ro
         return ptr;
     };
     RollTcDev tmp = dd;
-    for (int l = 0; l < dd.an; ++l) tmp.dys_a[l] = (__nv_bfloat16*)take(tcm_bytes(TS, l == dd.an - 1 ? 2 : dd.cha));
+    for (int l = 0; l < dd.an; ++l) tmp.dys_a[l] = (__nv_bfloat16*)take(tcm_bytes_r(dd.tr, TS, l == dd.an - 1 ? 2 : dd.cha));
     const int grid = dd.ntiles < kNumSM ? dd.ntiles : kNumSM;
-    tmp.stash = (__nv_bfloat16*)take((size_t)grid * 2 * dd.cdp * kChunkBytes);
+    tmp.stash = (__nv_bfloat16*)take((size_t)grid * 2 * dd.cdp * (dd.tr * 16));
     if (out) *out = tmp;
     return off;
 }
@@ -1130,15 +1230,20 @@ int rollout_tc_bwd(const drm_rollout* r, const drm_rollout_grad* g, cudaStream_t
     rc = launch_pack_tc(pl.jobs, stream); if (rc) return rc;
     {
         const int grid = d.ntiles < kNumSM ? d.ntiles : kNumSM;
-        DRM_CUDA_OK(cudaFuncSetAttribute(rollout_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
         ProfScope prof(PROF_ROLLOUT_BWD, stream);
-        rollout_bwd_tc_kernel<<<grid, kChainThreads, pl.smem_bytes, stream>>>(d);
+        if (d.tr == 64) {
+            DRM_CUDA_OK(cudaFuncSetAttribute(rollout_bwd_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
+            rollout_bwd_tc_kernel<64><<<grid, kChainThreads, pl.smem_bytes, stream>>>(d);
+        } else {
+            DRM_CUDA_OK(cudaFuncSetAttribute(rollout_bwd_tc_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
+            rollout_bwd_tc_kernel<128><<<grid, kChainThreads, pl.smem_bytes, stream>>>(d);
+        }
         DRM_CUDA_OK(cudaGetLastError());
     }
     if (want_actor) {
         WgParams wg;
         memset(&wg, 0, sizeof(wg));
-        wg.n_layers = a.n_linear; wg.row_tiles = d.T * d.ntiles;
+        wg.n_layers = a.n_linear; wg.row_tiles = d.T * d.ntiles; wg.tile_rows = d.tr;
         const int last = a.n_linear - 1;
         for (int l = 0; l <= last; ++l) {
             WgLayer& L = wg.L[l];
@@ -1167,7 +1272,7 @@ size_t rollout_tc_fwd_workspace_bytes(const drm_rollout* r) {
     RollTcPlan pl;
     if (!rollout_tc_supported(r) || plan_fwd(r, nullptr, pl) != DRM_OK) return 0;
     const int grid = pl.dev.ntiles < kNumSM ? pl.dev.ntiles : kNumSM;
-    return rup_sz(pl.wbytes, 256) + tcm_bytes((size_t)grid, pl.dev.cdp) + 1024;
+    return rup_sz(pl.wbytes, 256) + tcm_bytes_r(pl.dev.tr, (size_t)kNumSM, pl.dev.cdp) + 1024;
 }
 
 }  // namespace tc

@@ -138,7 +138,16 @@ __device__ __forceinline__ void chain_producer(const TcProgram& pg, ChainBars* b
 // loop is kept to a handful of instructions per MMA: the 64-bit shared-memory descriptors are built once per op
 // (constant high word; the low word = address | LBO advances by plain 32-bit adds) and a weight slab is issued
 // by a branch-light inner loop.
+//
+// TR = 64 ("half tiles"): a CTA owns 64 rows.  tcgen05.mma with M = 64 fills only lanes 0..15 of each TMEM lane quadrant,
+// which would idle half of every epilogue warp, so each op is issued as TWO M = 64 MMAs per K step: columns [0, n/2) of
+// the weight slab accumulate into lanes 0..15, columns [n/2, n) into lanes 16..31 of the SAME TMEM columns.  An epilogue
+// warp then holds 16 rows x 2 column halves in its 32 lanes and the thread-per-(row, chunk) epilogues run unchanged.
+// The tensor core does the work of a 128-row tile for 64 rows -- it is not what bounds these kernels.
+template <int TR = 128>
 __device__ __forceinline__ void chain_mma(const TcProgram& pg, ChainBars* bars, uint8_t* smem, uint32_t tmem_base, int reps) {
+    constexpr bool kHalf = TR == 64;
+    constexpr int kChunkBytes = TR * 16;
     // The whole warp runs the (warp-uniform) control flow so that descriptors and counters live in uniform
     // registers; only the tcgen05 instructions themselves are issued by one elected lane.
     tmem_base = __shfl_sync(0xffffffffu, tmem_base, 0);
@@ -165,7 +174,7 @@ __device__ __forceinline__ void chain_mma(const TcProgram& pg, ChainBars* bars, 
             const int total = op.a_chunks[0] + op.a_chunks[1];
             const int seg0 = op.a_chunks[0];
             const int kc = slab_chunks(stage_bytes, (int)n);
-            const uint32_t idesc = make_idesc_bf16(kTileRows, (int)n);
+            const uint32_t idesc = make_idesc_bf16(TR, kHalf ? (int)(n >> 1) : (int)n);
             const uint32_t b_flags = n << 16;                      // LBO = n * 16 B, in 16-byte units
             const uint32_t b_step = 2u * n;                        // two K chunks of the weight slab, 16-byte units
             uint32_t a_lo = (((a_base + op.a_off[0]) & 0x3FFFFu) >> 4) | a_lo_flags;
@@ -184,6 +193,10 @@ __device__ __forceinline__ void chain_mma(const TcProgram& pg, ChainBars* bars, 
                     const uint64_t adesc = ((uint64_t)desc_hi << 32) | a_lo;
                     const uint64_t bdesc = ((uint64_t)desc_hi << 32) | b_lo;
                     if (elect_one()) umma_bf16(d_addr, adesc, bdesc, idesc, acc);
+                    if (kHalf) {  // second column half of the slab -> lanes 16..31
+                        const uint64_t bdesc2 = ((uint64_t)desc_hi << 32) | (b_lo + (n >> 1));
+                        if (elect_one()) umma_bf16(d_addr + (16u << 16), adesc, bdesc2, idesc, acc);
+                    }
                     acc = 1;
                     a_lo += (2 * kChunkBytes) >> 4;
                     b_lo += b_step;
@@ -225,6 +238,22 @@ struct EpiSync {
     }
 };
 
+// Geometry of an epilogue thread for TR-row tiles.  TR = 128: row = TMEM lane, all chunks.  TR = 64: row = lane % 16 of
+// the quadrant, and the upper 16 lanes of a warp see the second column half of every op (chunk index + n/16).
+template <int TR>
+struct EpiGeo {
+    int row, half;
+    __device__ __forceinline__ EpiGeo() {
+        const int w4 = (threadIdx.x >> 5) & 3, ln = threadIdx.x & 31;
+        if (TR == 64) { row = 16 * w4 + (ln & 15); half = ln >> 4; }
+        else { row = 32 * w4 + ln; half = 0; }
+    }
+    // number of accumulator chunks (8 TMEM columns) an op with `nchunks` output chunks occupies
+    __device__ __forceinline__ static int tmem_chunks(int nchunks) { return TR == 64 ? nchunks >> 1 : nchunks; }
+    // global chunk index of TMEM chunk 0 as seen by this thread
+    __device__ __forceinline__ int goff(int nchunks) const { return TR == 64 ? half * (nchunks >> 1) : 0; }
+};
+
 // Row / column ownership of an epilogue thread: TMEM lane quadrant = warp % 4, column group = warp / 4.
 __device__ __forceinline__ int epi_row() { return 32 * ((threadIdx.x >> 5) & 3) + (threadIdx.x & 31); }
 __device__ __forceinline__ int epi_group() { return (threadIdx.x >> 5) >> 2; }
@@ -236,27 +265,28 @@ __device__ __forceinline__ uint32_t epi_taddr(uint32_t tmem_base, int col) {
 // Walks this thread's accumulator chunks [cbeg, cend) of the region starting at TMEM column col0, four chunks
 // (32 columns) per tcgen05.wait::ld so that the TMEM loads and the pointwise math of a batch overlap.
 // f(chunk, v[8]) is called for every chunk.
+// [cbeg, cend) are TMEM chunk indices; f receives the GLOBAL chunk index c + goff (goff != 0 only for half tiles).
 template <class F>
-__device__ __forceinline__ void epi_for_chunks(uint32_t tmem_base, int col0, int cbeg, int cend, F&& f) {
+__device__ __forceinline__ void epi_for_chunks(uint32_t tmem_base, int col0, int cbeg, int cend, F&& f, int goff = 0) {
     for (int c = cbeg; c < cend; c += 2) {
         float v[2][8];
         const bool two = c + 1 < cend;
         tmem_ld8(epi_taddr(tmem_base, col0 + c * 8), v[0]);
         if (two) tmem_ld8(epi_taddr(tmem_base, col0 + c * 8 + 8), v[1]);
         tmem_ld_wait();
-        f(c, v[0]);
-        if (two) f(c + 1, v[1]);
+        f(c + goff, v[0]);
+        if (two) f(c + 1 + goff, v[1]);
     }
 }
 // Same for two accumulator regions read together (two chunks of each per wait).
 template <class F>
-__device__ __forceinline__ void epi_for_chunks2(uint32_t tmem_base, int colA, int colB, int cbeg, int cend, F&& f) {
+__device__ __forceinline__ void epi_for_chunks2(uint32_t tmem_base, int colA, int colB, int cbeg, int cend, F&& f, int goff = 0) {
     for (int c = cbeg; c < cend; ++c) {
         float a[8], b[8];
         tmem_ld8(epi_taddr(tmem_base, colA + c * 8), a);
         tmem_ld8(epi_taddr(tmem_base, colB + c * 8), b);
         tmem_ld_wait();
-        f(c, a, b);
+        f(c + goff, a, b);
     }
 }
 // ELU-backward style epilogue: walks accumulator chunks like epi_for_chunks, but each chunk also needs a saved
@@ -265,10 +295,10 @@ __device__ __forceinline__ void epi_for_chunks2(uint32_t tmem_base, int colA, in
 // ld(c) -> uint4, f(c, v[8], uint4 saved); after_wait() runs once, right after the accumulator wait.
 template <class L, class F, class W>
 __device__ __forceinline__ void epi_for_chunks_saved(EpiSync& es, uint32_t tmem_base, int col0, int cbeg, int cend, L&& ld, F&& f,
-                                                     W&& after_wait) {
+                                                     W&& after_wait, int goff = 0) {
     const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
-    uint4 h0 = cbeg < cend ? ld(cbeg) : zero;
-    uint4 h1 = cbeg + 1 < cend ? ld(cbeg + 1) : zero;
+    uint4 h0 = cbeg < cend ? ld(cbeg + goff) : zero;
+    uint4 h1 = cbeg + 1 < cend ? ld(cbeg + 1 + goff) : zero;
     es.wait_acc();
     after_wait();
     for (int c = cbeg; c < cend; c += 2) {
@@ -276,17 +306,17 @@ __device__ __forceinline__ void epi_for_chunks_saved(EpiSync& es, uint32_t tmem_
         const bool two = c + 1 < cend;
         tmem_ld8(epi_taddr(tmem_base, col0 + c * 8), v[0]);
         if (two) tmem_ld8(epi_taddr(tmem_base, col0 + c * 8 + 8), v[1]);
-        const uint4 n0 = c + 2 < cend ? ld(c + 2) : zero;
-        const uint4 n1 = c + 3 < cend ? ld(c + 3) : zero;
+        const uint4 n0 = c + 2 < cend ? ld(c + 2 + goff) : zero;
+        const uint4 n1 = c + 3 < cend ? ld(c + 3 + goff) : zero;
         tmem_ld_wait();
-        f(c, v[0], h0);
-        if (two) f(c + 1, v[1], h1);
+        f(c + goff, v[0], h0);
+        if (two) f(c + 1 + goff, v[1], h1);
         h0 = n0; h1 = n1;
     }
 }
 template <class L, class F>
 __device__ __forceinline__ void epi_for_chunks_saved(EpiSync& es, uint32_t tmem_base, int col0, int cbeg, int cend, L&& ld, F&& f) {
-    epi_for_chunks_saved(es, tmem_base, col0, cbeg, cend, ld, f, [] {});
+    epi_for_chunks_saved(es, tmem_base, col0, cbeg, cend, ld, f, [] {}, 0);
 }
 
 // 8 consecutive fp32 values from a 32-byte aligned shared-memory vector (bias blocks are zero padded)
@@ -413,6 +443,7 @@ struct WgLayer {
 constexpr int kMaxWgLayers = 10;
 struct WgParams {
     int n_layers, row_tiles, total_ctas;
+    int tile_rows;  // rows per TCM tile of the images (0 = 128)
     WgLayer L[kMaxWgLayers];
 };
 // fills n_tiles_n / parts / splits / cta0 / total_ctas from the rest

@@ -32,6 +32,10 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_tc_kernel(const __grid_co
     extern __shared__ __align__(1024) uint8_t smem[];
     WgBars* bars = reinterpret_cast<WgBars*>(smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // rows per TCM tile of the images (128, or 64 for the half-tile rollouts) and bytes of one chunk of such a tile;
+    // the shared-memory regions keep their 128-row capacity
+    const int tr = w.tile_rows ? w.tile_rows : kTileRows;
+    const int cb = tr * 16;
     // ---- which job is mine
     int li = 0;
     for (int i = 1; i < w.n_layers; ++i) if ((int)blockIdx.x >= w.L[i].cta0) li = i;
@@ -59,12 +63,12 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_tc_kernel(const __grid_co
         const int ones_pos = (L.db && f_end == ft) ? npc - 1 : -1;
         for (int s = 0; s < kWgStages; ++s) {
             uint8_t* B = smem + 1024 + s * kWgStageBytes + kWgAChunks * kChunkBytes;
-            for (int r = threadIdx.x; r < kTileRows; r += 128) {
+            for (int r = threadIdx.x; r < tr; r += 128) {
                 if (ones_pos >= 0) {
                     uint4 q = make_uint4(0x00003F80u, 0u, 0u, 0u);  // bf16 1.0 in element 0
-                    *reinterpret_cast<uint4*>(B + ((size_t)ones_pos * kTileRows + r) * 16) = q;
+                    *reinterpret_cast<uint4*>(B + ((size_t)ones_pos * tr + r) * 16) = q;
                 }
-                if (npc & 1) *reinterpret_cast<uint4*>(B + ((size_t)npc * kTileRows + r) * 16) = make_uint4(0u, 0u, 0u, 0u);
+                if (npc & 1) *reinterpret_cast<uint4*>(B + ((size_t)npc * tr + r) * 16) = make_uint4(0u, 0u, 0u, 0u);
             }
         }
         fence_proxy_async_smem();
@@ -80,9 +84,9 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_tc_kernel(const __grid_co
             // data chunk ranges of the two segments inside this part
             const int s0b = max(f_begin, 0), s0e = min(f_end, nch0);
             const int s1b = max(f_begin, nch0), s1e = min(f_end, nch0 + nch1);
-            uint32_t bytes = (uint32_t)a_chunks * kChunkBytes;
-            if (s0e > s0b) bytes += (uint32_t)(s0e - s0b) * kChunkBytes;
-            if (s1e > s1b) bytes += (uint32_t)(s1e - s1b) * kChunkBytes;
+            uint32_t bytes = (uint32_t)a_chunks * cb;
+            if (s0e > s0b) bytes += (uint32_t)(s0e - s0b) * cb;
+            if (s1e > s1b) bytes += (uint32_t)(s1e - s1b) * cb;
             int stage = 0; uint32_t phase = 0;
             for (int it = 0; it < my_tiles; ++it) {
                 const int tile = split + it * L.splits;
@@ -90,31 +94,30 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_tc_kernel(const __grid_co
                 uint8_t* B = A + kWgAChunks * kChunkBytes;
                 mbar_wait(&bars->empty[stage], phase ^ 1);
                 mbar_expect_tx(&bars->full[stage], bytes);
-                bulk_g2s(A, tcm_at(L.dy, L.dy_cpt, tile, ntile * kWgAChunks, 0), (uint32_t)a_chunks * kChunkBytes, &bars->full[stage]);
+                auto img = [&](const __nv_bfloat16* base, int cpt, int chunk) {  // chunk of TCM tile `tile` (tr rows per tile)
+                    return base + ((size_t)tile * cpt + chunk) * tr * 8;
+                };
+                bulk_g2s(A, img(L.dy, L.dy_cpt, ntile * kWgAChunks), (uint32_t)a_chunks * cb, &bars->full[stage]);
                 if (s0e > s0b)
-                    bulk_g2s(B + (size_t)(s0b - f_begin) * kChunkBytes,
-                             tcm_at(L.seg[0].base, L.seg[0].cpt, tile, L.seg[0].chunk0 + s0b, 0),
-                             (uint32_t)(s0e - s0b) * kChunkBytes, &bars->full[stage]);
+                    bulk_g2s(B + (size_t)(s0b - f_begin) * cb, img(L.seg[0].base, L.seg[0].cpt, L.seg[0].chunk0 + s0b),
+                             (uint32_t)(s0e - s0b) * cb, &bars->full[stage]);
                 if (s1e > s1b)
-                    bulk_g2s(B + (size_t)(s1b - f_begin) * kChunkBytes,
-                             tcm_at(L.seg[1].base, L.seg[1].cpt, tile, L.seg[1].chunk0 + (s1b - nch0), 0),
-                             (uint32_t)(s1e - s1b) * kChunkBytes, &bars->full[stage]);
+                    bulk_g2s(B + (size_t)(s1b - f_begin) * cb, img(L.seg[1].base, L.seg[1].cpt, L.seg[1].chunk0 + (s1b - nch0)),
+                             (uint32_t)(s1e - s1b) * cb, &bars->full[stage]);
                 if (++stage == kWgStages) { stage = 0; phase ^= 1; }
             }
         }
     } else if (warp == 5) {
         if (lane == 0) {
-            const uint32_t idesc = make_idesc_bf16_mn(kTileRows, n_mma);
+            const uint32_t idesc = make_idesc_bf16_mn(128, n_mma);  // M = 128 output features of this n-tile
             int stage = 0; uint32_t phase = 0;
             for (int it = 0; it < my_tiles; ++it) {
                 const uint32_t A = smem_u32(smem + 1024 + stage * kWgStageBytes);
                 const uint32_t B = A + kWgAChunks * kChunkBytes;
                 mbar_wait(&bars->full[stage], phase);
                 tc_fence_after_sync();
-#pragma unroll
-                for (int k = 0; k < kTileRows / 16; ++k)
-                    umma_bf16(tmem_base, make_desc(A + k * 256, 128, kChunkBytes), make_desc(B + k * 256, 128, kChunkBytes), idesc,
-                              it > 0 || k > 0);
+                for (int k = 0; k < tr / 16; ++k)  // K = rows of the tile, 16 per instruction
+                    umma_bf16(tmem_base, make_desc(A + k * 256, 128, cb), make_desc(B + k * 256, 128, cb), idesc, it > 0 || k > 0);
                 umma_commit(&bars->empty[stage]);
                 if (++stage == kWgStages) { stage = 0; phase ^= 1; }
             }
