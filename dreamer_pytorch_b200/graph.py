@@ -50,6 +50,7 @@ class ImaginationGraph:
         n0 = lib.drm_launch_count()
         with torch.cuda.graph(self.graph):
             self.actor_loss, self.value_loss, self.grads = self._eager()
+            self.losses = torch.stack([self.actor_loss, self.value_loss])  # [2], one device->host read per step
         self.launches_per_replay = int(lib.drm_launch_count() - n0)  # kernels of this library inside the graph
         for p, g in zip(self.params, self.grads):
             p.grad = g  # static tensors from the graph's pool, refreshed by every replay
