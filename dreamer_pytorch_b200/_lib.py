@@ -53,7 +53,7 @@ class drm_rollout(C.Structure):
         + [(k, P) for k in ("start_stoch", "start_deter", "action_in", "obs_embed", "eps_prior", "eps_post",
                             "noise_act", "prior_mean", "prior_std", "prior_stoch", "deter", "post_mean", "post_std",
                             "post_stoch", "action_out")]
-        + [("save", P), ("save_bytes", C.c_size_t), ("workspace", P), ("workspace_bytes", C.c_size_t)]
+        + [("save", P), ("save_bytes", C.c_size_t), ("workspace", P), ("workspace_bytes", C.c_size_t), ("step_flags", P)]
     )
 
 
@@ -70,7 +70,9 @@ class drm_rollout_grad(C.Structure):
 class drm_mlp_call(C.Structure):
     _fields_ = [("mlp", drm_mlp), ("M", C.c_int32), ("k0", C.c_int32), ("k1", C.c_int32), ("precision", C.c_int32),
                 ("training", C.c_int32), ("x0", P), ("ld0", C.c_int64), ("x1", P), ("ld1", C.c_int64), ("y", P),
-                ("save", P), ("save_bytes", C.c_size_t), ("workspace", P), ("workspace_bytes", C.c_size_t)]
+                ("save", P), ("save_bytes", C.c_size_t), ("workspace", P), ("workspace_bytes", C.c_size_t),
+                ("wait_flags", P), ("wait_target", C.c_int32), ("wait_rows", C.c_int32), ("wait_steps", C.c_int32),
+                ("max_ctas", C.c_int32)]
 
 
 class drm_mlp_bwd_call(C.Structure):
@@ -104,6 +106,7 @@ SYMBOLS = {
     "drm_rollout_save_bytes": (C.c_size_t, [C.POINTER(drm_rollout)]),
     "drm_rollout_workspace_bytes": (C.c_size_t, [C.POINTER(drm_rollout)]),
     "drm_rollout_fwd": (C.c_int, [C.POINTER(drm_rollout), P]),
+    "drm_rollout_tiles": (C.c_int, [C.POINTER(drm_rollout)]),
     "drm_rollout_bwd": (C.c_int, [C.POINTER(drm_rollout), C.POINTER(drm_rollout_grad), P]),
     "drm_mlp_save_bytes": (C.c_size_t, [C.POINTER(drm_mlp_call)]),
     "drm_mlp_workspace_bytes": (C.c_size_t, [C.POINTER(drm_mlp_call)]),

@@ -27,11 +27,22 @@ from .functional import (KLFn, RolloutCfg, _f32c, mlp_backward_raw, mlp_forward_
 _SIDE = {}
 
 
-def _side_stream(device) -> "torch.cuda.Stream":
-    key = (device.type, device.index)
+_PIPELINE_HEADS = True  # heads beside the rollout when SMs are idle (see _ActorLossFn.forward)
+
+
+def _side_stream(device, k: int = 0) -> "torch.cuda.Stream":
+    key = (device.type, device.index, k)
     if key not in _SIDE:
         _SIDE[key] = torch.cuda.Stream(device=device)
     return _SIDE[key]
+
+
+def _sm_count(device) -> int:
+    return torch.cuda.get_device_properties(device).multi_processor_count
+
+
+def stoch_dev(t):
+    return t["start_stoch"].device
 
 
 ImagInfo = namedtuple("ImagInfo", ["imag", "actions", "reward", "value", "returns", "discount"])
@@ -50,17 +61,42 @@ class _ActorLossFn(torch.autograd.Function):
         (cfg, t, rssm, reward_w, value_w, pcont_w, discount, lambda_, shared) = pack
         actor = [_f32c(w) for w in actor_w]
         training = any(ctx.needs_input_grad)
-        save = rollout_forward_raw(cfg, t, rssm, actor, training)
         H, N = cfg.steps, cfg.n
         S, D = cfg.dims[1], cfg.dims[2]
+        prec = get_precision()
+        heads = [(reward_w, training), (value_w, True)] + ([(pcont_w, training)] if pcont_w else [])
+        # The rollout occupies one SM per 64 (or 128) start states.  When that leaves SMs idle, the heads run BESIDE it
+        # on side streams, gated per time step by the completion counters the rollout kernel publishes: the heads of
+        # step t overlap the rollout of step t+1 (drm_rollout.step_flags / drm_mlp_call.wait_flags).
+        flags = tiles = fork = None
+        if prec == "bf16" and _PIPELINE_HEADS:
+            flags = torch.zeros(H, dtype=torch.int32, device=stoch_dev(t))
+            tiles = []
+            fork = torch.cuda.Event()
+            fork.record(torch.cuda.current_stream())  # the side streams branch off BEFORE the rollout is enqueued
+        save = rollout_forward_raw(cfg, t, rssm, actor, training, step_flags=flags, tiles_out=tiles)
         x0 = t["prior_stoch"].view(H * N, S)
         x1 = t["deter"].view(H * N, D)
         # heads over all imagined states; hidden activations are kept: the actor path needs their
         # data-gradients, the value loss the value head's weight-gradients
-        prec = get_precision()
-        reward, rsave = mlp_forward_raw(x0, x1, reward_w, training, prec)
-        value, vsave = mlp_forward_raw(x0, x1, value_w, True, prec)
-        pc, psave = (mlp_forward_raw(x0, x1, pcont_w, training, prec) if pcont_w else (None, None))
+        free = (_sm_count(x0.device) - tiles[0]) // len(heads) if tiles else 0
+        if flags is not None and free >= 16:
+            main = torch.cuda.current_stream()
+            outs = []
+            for i, (w, keep) in enumerate(heads):
+                side = _side_stream(x0.device, 1 + i)
+                side.wait_event(fork)  # grids are capped (max_ctas): rollout and heads are resident together
+                with torch.cuda.stream(side):
+                    outs.append(mlp_forward_raw(x0, x1, w, keep, prec, wait=(flags, tiles[0], N), max_ctas=free))
+                    for o in outs[-1]:
+                        if o is not None:
+                            o.record_stream(main)
+            for i in range(len(heads)):
+                main.wait_stream(_side_stream(x0.device, 1 + i))
+        else:
+            outs = [mlp_forward_raw(x0, x1, w, keep, prec) for (w, keep) in heads]
+        (reward, rsave), (value, vsave) = outs[0], outs[1]
+        pc, psave = outs[2] if pcont_w else (None, None)
         out = returns_loss_raw(reward.view(H, N), value.view(H, N), None if pc is None else pc.view(H, N), discount,
                                lambda_)
         ctx.pack = (cfg, t, rssm, actor, save, reward_w, value_w, pcont_w, rsave, vsave, psave, out, x0, x1, prec, shared)

@@ -367,6 +367,19 @@ size_t drm_mlp_workspace_bytes(const drm_mlp_call* c) {
     return bytes;
 }
 
+// fp32 path + producer gating: the FFMA kernels do not poll, so one thread waits for the LAST step's flag first
+__global__ void wait_flag_kernel(const int* flag, int target) {
+    unsigned spins = 0;
+    int v;
+    do {
+        asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+        if (v < target) {
+            __nanosleep(500);
+            if (++spins > (1u << 24)) __trap();
+        }
+    } while (v < target);
+}
+
 int drm_mlp_fwd(const drm_mlp_call* c, void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     int rc = validate(c); if (rc) return rc;
@@ -376,6 +389,11 @@ int drm_mlp_fwd(const drm_mlp_call* c, void* stream_) {
     DRM_REQUIRE(c->x0 && c->y && (c->k1 == 0 || c->x1), DRM_E_ARG, "null io pointer");
     DRM_REQUIRE(c->workspace && c->workspace_bytes >= drm_mlp_workspace_bytes(c), DRM_E_WORKSPACE, "workspace too small");
     if (c->precision == DRM_BF16) return tc::mlp_tc_fwd(c, stream);
+    if (c->wait_flags) {
+        DRM_REQUIRE(c->wait_steps > 0, DRM_E_ARG, "wait_flags need wait_steps");
+        wait_flag_kernel<<<1, 1, 0, stream>>>(c->wait_flags + c->wait_steps - 1, c->wait_target);
+        DRM_CUDA_OK(cudaGetLastError());
+    }
     const bool save = c->training && m.n_linear > 1;
     if (save) DRM_REQUIRE(c->save && c->save_bytes >= drm_mlp_save_bytes(c), DRM_E_WORKSPACE, "save buffer too small");
     MlpDev p; fill_common(p, c);

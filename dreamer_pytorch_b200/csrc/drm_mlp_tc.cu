@@ -66,6 +66,7 @@ struct MlpTcDev {
     float* dx0; float* dx1; int accumulate_dx;
     __nv_bfloat16* dys[DRM_MAX_LINEAR];   // TCM images of dY_l (ch chunks; cout for the last layer) or nullptr
     float* db_last;                       // bias gradient of the last Linear, reduced in fp32 from the exact dY
+    const int* wait_flags; int wait_target, wait_rows, wait_steps;  // producer gating of the input rows (forward)
     TcProgram pg;
 };
 
@@ -190,6 +191,28 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_fwd_tc_kernel(const __gr
             }
         };
         auto stage_part = [&](int tile, uint8_t* dst, int part) { stage_issue(tile, part); stage_commit(tile, dst, part); };
+        // Producer gating (drm_mlp_call.wait_flags): the rows of step t exist once wait_flags[t] >= wait_target.  Lane 0
+        // of each warp polls with an acquire load before the warp touches a tile it has not checked yet.
+        int ready_tile = -1;
+        auto wait_tile = [&](int tile) {
+            if (!p.wait_flags || tile <= ready_tile) return;
+            if (ln == 0) {
+                const int last_row = min(p.M, (tile + 1) * kTileRows) - 1;
+                const int t_hi = min(p.wait_steps - 1, last_row / p.wait_rows);
+                const int* f = p.wait_flags + t_hi;
+                unsigned spins = 0;
+                int v;
+                do {
+                    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+                    if (v < p.wait_target) {
+                        __nanosleep(200);
+                        if (++spins > (1u << 24)) __trap();  // ~ seconds: the producer is not running
+                    }
+                } while (v < p.wait_target);
+            }
+            __syncwarp();
+            ready_tile = tile;
+        };
         auto l2_pull = [&](int tile) {  // one thread: the rows of `tile` into L2
             if (tile < tiles && threadIdx.x == 0) {
                 const int nrows = min(kTileRows, p.M - tile * kTileRows);
@@ -199,7 +222,8 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_fwd_tc_kernel(const __gr
         };
         const bool dbl = p.pg.a_alt != 0;  // second operand buffer available
         if ((int)blockIdx.x < tiles) {
-            l2_pull(blockIdx.x + gridDim.x);
+            wait_tile(blockIdx.x);
+            if (!p.wait_flags) l2_pull(blockIdx.x + gridDim.x);
             for (int part = 0; part < n_parts; ++part) stage_part(blockIdx.x, act, part);
             es.release();
         }
@@ -211,7 +235,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_fwd_tc_kernel(const __gr
             const int nxt = tile + gridDim.x;
             const bool has_next = nxt < tiles;
             int parts_done = 0;
-            l2_pull(nxt + gridDim.x);
+            if (!p.wait_flags) l2_pull(nxt + gridDim.x);
             const int grow = row0 + row;
             const bool live = grow < p.M;
             for (int l = 0; l <= last; ++l) {
@@ -220,7 +244,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_fwd_tc_kernel(const __gr
                 if (l < last) {
                     // a slice of the next tile's input: loads in flight across this epilogue, stored after its release
                     const bool slice = dbl && has_next && parts_done < n_parts;
-                    if (slice) stage_issue(nxt, parts_done);
+                    if (slice) { wait_tile(nxt); stage_issue(nxt, parts_done); }
                     // hidden layer: h = ELU(acc + b) -> bf16 A operand of the next layer (in place) [+ TCM save]
                     const int per = (p.ch + kEpiGroups - 1) / kEpiGroups;
                     const int cbeg = grp * per, cend = min(p.ch, cbeg + per);
@@ -257,6 +281,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_fwd_tc_kernel(const __gr
                 // whatever is left of the next tile's input (everything when there is no second buffer: the operand
                 // buffer is free now that the output GEMM has retired); release() also covers the TMEM loads above
                 uint8_t* dst = dbl ? act_nxt : act;
+                wait_tile(nxt);
                 while (parts_done < n_parts) stage_part(nxt, dst, parts_done++);
                 es.release();
             }
@@ -542,7 +567,11 @@ int mlp_tc_fwd(const drm_mlp_call* c, cudaStream_t stream) {
         carve_save(c, pl, d);
     }
     rc = launch_pack_tc(pl.jobs, stream); if (rc) return rc;
-    const int grid = pl.tiles < kNumSM ? pl.tiles : kNumSM;
+    int cap = kNumSM;
+    if (c->max_ctas > 0 && c->max_ctas < cap) cap = c->max_ctas;
+    const int grid = pl.tiles < cap ? pl.tiles : cap;
+    d.wait_flags = c->wait_flags; d.wait_target = c->wait_target; d.wait_rows = c->wait_rows; d.wait_steps = c->wait_steps;
+    if (d.wait_flags) DRM_REQUIRE(d.wait_rows > 0 && d.wait_steps > 0, DRM_E_ARG, "wait_flags need wait_rows and wait_steps");
     DRM_CUDA_OK(cudaFuncSetAttribute(mlp_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
     ProfScope prof(PROF_MLP_FWD, stream);
     mlp_fwd_tc_kernel<<<grid, kChainThreads, pl.smem_bytes, stream>>>(d);

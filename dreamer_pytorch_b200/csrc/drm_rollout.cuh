@@ -71,6 +71,7 @@ namespace tc {
 int rollout_tc_supported(const drm_rollout* r);
 size_t rollout_tc_save_bytes(const drm_rollout* r);
 size_t rollout_tc_fwd_workspace_bytes(const drm_rollout* r);
+int rollout_tc_tiles(const drm_rollout* r);
 size_t rollout_tc_bwd_workspace_bytes(const drm_rollout* r);
 int rollout_tc_fwd(const drm_rollout* r, cudaStream_t stream);
 int rollout_tc_bwd(const drm_rollout* r, const drm_rollout_grad* g, cudaStream_t stream);

@@ -208,6 +208,11 @@ size_t drm_rollout_workspace_bytes(const drm_rollout* r) {
     return (f > b ? f : b) * sizeof(float) + 256;
 }
 
+int drm_rollout_tiles(const drm_rollout* r) {
+    if (!r || validate(r) != DRM_OK) return 0;
+    return use_tc(r) ? tc::rollout_tc_tiles(r) : 1;  // fp32 kernels: flags are set wholesale after the launch
+}
+
 int drm_rollout_fwd(const drm_rollout* r, void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     int rc = validate(r); if (rc) return rc;
@@ -234,7 +239,10 @@ int drm_rollout_fwd(const drm_rollout* r, void* stream_) {
         if (rc) return rc;
         p.embproj = embproj;
     }
-    return launch_rollout_fwd(p, stream);
+    rc = launch_rollout_fwd(p, stream); if (rc) return rc;
+    // fp32 kernels do not signal per step: every flag passes any target once the whole rollout is in global memory
+    if (r->step_flags) DRM_CUDA_OK(cudaMemsetAsync(r->step_flags, 0x7F, sizeof(int32_t) * r->steps, stream));
+    return DRM_OK;
 }
 
 int drm_rollout_bwd(const drm_rollout* r, const drm_rollout_grad* g, void* stream_) {

@@ -47,6 +47,7 @@ struct RollTcDev {
     int lo_per_cta;
     float* sv_raw;                          // actor output before the distribution, fp32 [T*n][Aout]
     const uint8_t* wstream;
+    int* step_flags;                        // optional: += 1 per row tile once every output of step t is in global memory
     uint32_t st_off, hb_off, bias_off;
     // backward
     const float *g_prior_mean, *g_prior_std, *g_prior_stoch, *g_deter, *g_action_out;
@@ -496,7 +497,9 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                         p.prior_stoch[o0 + i] = sE[i];
                     }
                 }
+                if (p.step_flags) __threadfence();  // this thread's stores of step t (deter, action, prior) before the signal
                 named_bar<kEpiThreads, 1>();  // the hidden buffer is written again by the next epilogue
+                if (p.step_flags && tid == 0) atomicAdd(p.step_flags + t, 1);
             }
         }
     }
@@ -1059,6 +1062,7 @@ static void fill_io_tc(const drm_rollout* r, RollTcDev& d) {
     d.start_stoch = r->start_stoch; d.start_deter = r->start_deter; d.eps_prior = r->eps_prior; d.noise_act = r->noise_act;
     d.prior_mean = r->prior_mean; d.prior_std = r->prior_std; d.prior_stoch = r->prior_stoch; d.deter = r->deter;
     d.action_out = r->action_out;
+    d.step_flags = r->step_flags;
 }
 
 int rollout_tc_fwd(const drm_rollout* r, cudaStream_t stream) {
@@ -1266,6 +1270,11 @@ int rollout_tc_bwd(const drm_rollout* r, const drm_rollout_grad* g, cudaStream_t
         rc = launch_wgrad_tc(wg, stream); if (rc) return rc;
     }
     return DRM_OK;
+}
+
+int rollout_tc_tiles(const drm_rollout* r) {
+    const int tr = tile_rows_for(r->n);
+    return (r->n + tr - 1) / tr;
 }
 
 size_t rollout_tc_fwd_workspace_bytes(const drm_rollout* r) {

@@ -120,7 +120,7 @@ OUT_KEYS = {
 }
 
 
-def rollout_forward_raw(cfg: RolloutCfg, t: dict, rssm, actor, training: bool):
+def rollout_forward_raw(cfg: RolloutCfg, t: dict, rssm, actor, training: bool, step_flags=None, tiles_out=None):
     """Validates shapes, allocates the outputs into ``t`` and runs drm_rollout_fwd.
     Returns the save buffer (None unless training)."""
     lib = _lib.load()
@@ -151,6 +151,11 @@ def rollout_forward_raw(cfg: RolloutCfg, t: dict, rssm, actor, training: bool):
     r.workspace, r.workspace_bytes = ws.data_ptr(), ws.numel() * 4
     if save is not None:
         r.save, r.save_bytes = save.data_ptr(), save.numel() * 4
+    if step_flags is not None:
+        # per-step completion counters for a consumer running beside the rollout (drm_rollout.step_flags)
+        r.step_flags = step_flags.data_ptr()
+        if tiles_out is not None:
+            tiles_out.append(int(lib.drm_rollout_tiles(C.byref(r))))
     _lib.check(lib.drm_rollout_fwd(C.byref(r), _stream()), "drm_rollout_fwd")
     _count()
     return save
@@ -277,8 +282,10 @@ def _build_mlp_call(x0, x1, weights, M, training, precision=None) -> _lib.drm_ml
     return c
 
 
-def mlp_forward_raw(x0, x1, weights, training, precision=None):
-    """Runs drm_mlp_fwd; returns (y [M,out], save tensor or None)."""
+def mlp_forward_raw(x0, x1, weights, training, precision=None, wait=None, max_ctas=0):
+    """Runs drm_mlp_fwd; returns (y [M,out], save tensor or None).
+    wait = (flags int32 [steps], target, rows_per_step) gates the input rows on a producer kernel running beside this
+    one (drm_mlp_call.wait_flags); max_ctas bounds the grid so that producer and consumer stay resident together."""
     lib = _lib.load()
     M = x0.shape[0]
     c = _build_mlp_call(x0, x1, weights, M, training, precision)
@@ -291,6 +298,10 @@ def mlp_forward_raw(x0, x1, weights, training, precision=None):
     if training:
         save = _buf(lib.drm_mlp_save_bytes(C.byref(c)), dev)
         c.save, c.save_bytes = save.data_ptr(), save.numel() * 4
+    if wait is not None:
+        flags, target, rows = wait
+        c.wait_flags, c.wait_target, c.wait_rows, c.wait_steps = flags.data_ptr(), int(target), int(rows), int(flags.numel())
+    c.max_ctas = int(max_ctas)
     _lib.check(lib.drm_mlp_fwd(C.byref(c), _stream()), "drm_mlp_fwd")
     _count()
     return y, save

@@ -128,6 +128,11 @@ typedef struct drm_rollout {
     size_t save_bytes;
     void* workspace;    /* drm_rollout_workspace_bytes(); contents undefined after the call */
     size_t workspace_bytes;
+    /* optional (POLICY, may be NULL): int32 [steps], zeroed by the caller.  The forward adds 1 to step_flags[t]
+       (device-scope release) whenever one row tile has stored every output of step t, so that a consumer kernel
+       running BESIDE the rollout (drm_mlp_call.wait_flags) can start on step t while step t+1 is computed.
+       drm_rollout_tiles() is the count each flag reaches. */
+    int32_t* step_flags;
 } drm_rollout;
 
 /* Upstream gradients (NULL = zero) and gradient sinks (NULL = not wanted) of a rollout. */
@@ -158,6 +163,11 @@ typedef struct drm_mlp_call {
     float* y;                  /* [M,out_dim] */
     void* save; size_t save_bytes;           /* drm_mlp_save_bytes() */
     void* workspace; size_t workspace_bytes; /* drm_mlp_workspace_bytes() */
+    /* optional producer/consumer gating (NULL = none): rows [t*wait_rows, (t+1)*wait_rows) of x0/x1 may be read once
+       wait_flags[t] >= wait_target (acquire).  The producer must already be running or be guaranteed SMs:
+       max_ctas (0 = all SMs) bounds this call's grid so that both kernels stay resident. */
+    const int32_t* wait_flags; int32_t wait_target; int32_t wait_rows; int32_t wait_steps; int32_t max_ctas;
+
 } drm_mlp_call;
 
 typedef struct drm_mlp_bwd_call {
@@ -212,6 +222,8 @@ int drm_prof_read(int slot, double* total_ms, int* count);
 
 size_t drm_rollout_save_bytes(const drm_rollout* r);
 size_t drm_rollout_workspace_bytes(const drm_rollout* r);
+/* Row tiles the forward of `r` works on (what every step_flags entry counts up to). */
+int drm_rollout_tiles(const drm_rollout* r);
 int drm_rollout_fwd(const drm_rollout* r, void* stream);
 int drm_rollout_bwd(const drm_rollout* r, const drm_rollout_grad* g, void* stream);
 
