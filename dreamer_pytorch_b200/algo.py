@@ -79,7 +79,7 @@ class _ActorLossFn(torch.autograd.Function):
         x1 = t["deter"].view(H * N, D)
         # heads over all imagined states; hidden activations are kept: the actor path needs their
         # data-gradients, the value loss the value head's weight-gradients
-        free = (_sm_count(x0.device) - tiles[0]) // len(heads) if tiles else 0
+        free = (_sm_count(x0.device) - tiles[0]) // len(heads) if tiles and tiles[0] > 0 else 0
         if flags is not None and free >= 16:
             main = torch.cuda.current_stream()
             outs = []

@@ -210,7 +210,7 @@ size_t drm_rollout_workspace_bytes(const drm_rollout* r) {
 
 int drm_rollout_tiles(const drm_rollout* r) {
     if (!r || validate(r) != DRM_OK) return 0;
-    return use_tc(r) ? tc::rollout_tc_tiles(r) : 1;  // fp32 kernels: flags are set wholesale after the launch
+    return use_tc(r) ? tc::rollout_tc_tiles(r) : 0;  // 0: fp32 kernels, no per-step signal (flags are set wholesale after the launch)
 }
 
 int drm_rollout_fwd(const drm_rollout* r, void* stream_) {

@@ -900,11 +900,8 @@ int rollout_tc_supported(const drm_rollout* r) {
 
 // Rows per CTA: 64-row half tiles (see chain_mma) while they put more CTAs on the 148 SMs than 128-row tiles would.
 static int tile_rows_for(int n) {
-    static int forced = -1;
-    if (forced < 0) {
-        const char* e = getenv("DRM_ROLLOUT_TR");  // developer override (64 / 128)
-        forced = e ? atoi(e) : 0;
-    }
+    const char* e = getenv("DRM_ROLLOUT_TR");  // developer / test override (64 or 128), read on every call
+    const int forced = e ? atoi(e) : 0;
     if (forced == 64 || forced == 128) return forced;
     const int t128 = (n + 127) / 128;
     return t128 < kNumSM ? 64 : 128;

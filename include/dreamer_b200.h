@@ -222,7 +222,8 @@ int drm_prof_read(int slot, double* total_ms, int* count);
 
 size_t drm_rollout_save_bytes(const drm_rollout* r);
 size_t drm_rollout_workspace_bytes(const drm_rollout* r);
-/* Row tiles the forward of `r` works on (what every step_flags entry counts up to). */
+/* Row tiles the forward of `r` works on (what every step_flags entry counts up to); 0 when this call runs on the
+   fp32 kernels, which publish no per-step progress (every flag is then set past any target after the launch). */
 int drm_rollout_tiles(const drm_rollout* r);
 int drm_rollout_fwd(const drm_rollout* r, void* stream);
 int drm_rollout_bwd(const drm_rollout* r, const drm_rollout_grad* g, void* stream);

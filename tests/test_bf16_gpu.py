@@ -157,6 +157,14 @@ def test_rollout_policy_bf16(cuda, sz):
     assert max(gerrs.values()) < tol, gerrs
 
 
+@pytest.mark.parametrize("tile_rows", [64, 128])
+def test_rollout_policy_bf16_both_tile_sizes(cuda, tile_rows, monkeypatch):
+    """The rollout kernels are templates on the rows per CTA (64-row half tiles for small batches, 128 otherwise);
+    DRM_ROLLOUT_TR forces one instantiation so that both are held to the same parity bar at a test-sized batch."""
+    monkeypatch.setenv("DRM_ROLLOUT_TR", str(tile_rows))
+    test_rollout_policy_bf16(cuda, ROLL_SIZES[2])
+
+
 def test_rollout_policy_bf16_all_cotangents(cuda):
     """Upstream gradients on every output (mean, std, stoch, deter, action), as RolloutFn allows."""
     from oracle import dreamer_oracle as O

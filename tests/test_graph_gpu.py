@@ -49,3 +49,43 @@ def test_graph_step_matches_eager(prec):
     assert rel_err(gal, ref_losses[0]) < 1e-5 and rel_err(gvl, ref_losses[1]) < 1e-5
     for p, r in zip(params, ref):
         assert rel_err(p.grad, r) < 1e-4, (p.shape, rel_err(p.grad, r))  # fp32 atomics reorder between runs
+
+
+def test_heads_beside_the_rollout_match_stream_order():
+    """The head MLPs gated by the rollout's per-step completion counters (side streams, capped grids) must give the
+    results of the plain stream-ordered launch sequence: same kernels, same data, only the schedule differs."""
+    from dreamer_pytorch_b200 import algo, noise
+    from dreamer_pytorch_b200.dropin.agent import AtariDreamerModel
+    from dreamer_pytorch_b200.dropin.rnns import RSSMState
+    from dreamer_pytorch_b200.precision import precision
+
+    dev = torch.device("cuda:0")
+    torch.manual_seed(3)
+    A, N, H = 6, 1000, 15
+    model = AtariDreamerModel(action_shape=(A,), action_dist="tanh_normal").to(dev).train()
+    g = torch.Generator().manual_seed(4)
+    stoch = torch.randn(N, 30, generator=g).to(dev)
+    deter = torch.tanh(torch.randn(N, 200, generator=g)).to(dev)
+    eps = torch.randn(H, N, 30, generator=g).to(dev)
+    nza = torch.randn(H, N, A, generator=g).to(dev)
+    params = list(model.action_decoder.parameters()) + list(model.value_model.parameters())
+    res = {}
+    old = algo._PIPELINE_HEADS
+    try:
+        for mode in (True, False):
+            algo._PIPELINE_HEADS = mode
+            for p in params:
+                p.grad = None
+            with precision("bf16"), noise.injected(eps_prior=[eps], noise_act=[nza]):
+                al, vl, info = algo.imagination_losses(model, RSSMState(stoch, stoch, stoch, deter), H)
+                al.backward(); vl.backward()
+            torch.cuda.synchronize()
+            res[mode] = (al.detach().clone(), vl.detach().clone(), info.reward.clone(), info.value.clone(),
+                         [p.grad.clone() for p in params])
+    finally:
+        algo._PIPELINE_HEADS = old
+    a, b = res[True], res[False]
+    assert torch.equal(a[2], b[2]) and torch.equal(a[3], b[3])          # head outputs: bit-identical
+    assert rel_err(a[0], b[0]) < 1e-6 and rel_err(a[1], b[1]) < 1e-6
+    for ga, gb in zip(a[4], b[4]):
+        assert rel_err(ga, gb) < 1e-4                                     # fp32 atomics reorder between runs
