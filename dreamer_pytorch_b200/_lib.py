@@ -92,7 +92,14 @@ class drm_kl_call(C.Structure):
                          "d_prior_mean", "d_prior_std")]
 
 
-STRUCTS = {s.__name__: s for s in (drm_mlp, drm_mlp_grad, drm_rssm, drm_rssm_grad, drm_rollout, drm_rollout_grad,
+class drm_clip_adam_call(C.Structure):
+    _fields_ = ([("n_tensors", C.c_int32), ("pad_", C.c_int32)]
+                + [(k, C.c_float) for k in ("max_norm", "beta1", "beta2", "eps", "one_minus_beta1", "one_minus_beta2", "step_size", "bias2_sqrt")]
+                + [(k, P * 64) for k in ("param", "grad", "exp_avg", "exp_avg_sq")]
+                + [("numel", C.c_int64 * 64), ("norm_out", P), ("workspace", P), ("workspace_bytes", C.c_size_t)])
+
+
+STRUCTS = {s.__name__: s for s in (drm_clip_adam_call, drm_mlp, drm_mlp_grad, drm_rssm, drm_rssm_grad, drm_rollout, drm_rollout_grad,
                                    drm_mlp_call, drm_mlp_bwd_call, drm_returns_loss_call, drm_kl_call)}
 
 # every symbol include/dreamer_b200.h declares: name -> (restype, argtypes)
@@ -113,6 +120,7 @@ SYMBOLS = {
     "drm_mlp_fwd": (C.c_int, [C.POINTER(drm_mlp_call), P]),
     "drm_mlp_bwd": (C.c_int, [C.POINTER(drm_mlp_bwd_call), P]),
     "drm_returns_loss": (C.c_int, [C.POINTER(drm_returns_loss_call), P]),
+    "drm_clip_adam": (C.c_int, [C.POINTER(drm_clip_adam_call), P]),
     "drm_kl_fwd": (C.c_int, [C.POINTER(drm_kl_call), P]),
     "drm_kl_bwd": (C.c_int, [C.POINTER(drm_kl_call), P]),
 }

@@ -1,0 +1,82 @@
+// Optimizer tail of one parameter group: torch.nn.utils.clip_grad_norm_ followed by torch.optim.Adam.step
+// (dreamer_algo.py:182-194) as two launches.  HBM-bound, tiny (an actor or value group is ~0.13 M parameters): what
+// matters is that it is 2 launches instead of ~16 and needs no host synchronisation.
+#include "drm_common.cuh"
+
+namespace drm {
+
+constexpr int kOptBlocksPerTensor = 16;
+constexpr int kOptThreads = 256;
+
+// sum of squares of every gradient element of the group -> acc[0] (double)
+__global__ void __launch_bounds__(kOptThreads) grad_sumsq_kernel(const drm_clip_adam_call c, double* acc) {
+    const int t = blockIdx.y;
+    const float* g = c.grad[t];
+    const int64_t n = c.numel[t];
+    float s = 0.f;
+    for (int64_t i = (int64_t)blockIdx.x * kOptThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kOptThreads) {
+        const float v = g[i];
+        s = fmaf(v, v, s);
+    }
+    s = warp_sum(s);
+    __shared__ float part[kOptThreads / 32];
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        float v = threadIdx.x < kOptThreads / 32 ? part[threadIdx.x] : 0.f;
+        v = warp_sum(v);
+        if (threadIdx.x == 0 && v != 0.f) atomicAdd(acc, (double)v);
+    }
+}
+
+__global__ void __launch_bounds__(kOptThreads) clip_adam_kernel(const drm_clip_adam_call c, const double* acc) {
+    const float total = (float)sqrt(*acc);
+    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0 && c.norm_out) *c.norm_out = total;
+    float coef = 1.f;
+    if (c.max_norm > 0.f) coef = fminf(c.max_norm / (total + 1e-6f), 1.f);  // clip_grad.py: clamp(max_norm / (norm + 1e-6), max=1)
+    const int t = blockIdx.y;
+    float* p = c.param[t];
+    float* g = c.grad[t];
+    float* m = c.exp_avg[t];
+    float* v = c.exp_avg_sq[t];
+    const int64_t n = c.numel[t];
+    const float w1 = c.one_minus_beta1, w2 = c.one_minus_beta2;
+    for (int64_t i = (int64_t)blockIdx.x * kOptThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kOptThreads) {
+        const float gi = g[i] * coef;
+        const float mi = m[i] + w1 * (gi - m[i]);         // exp_avg.lerp_(grad, 1 - beta1)
+        const float vi = v[i] * c.beta2 + w2 * gi * gi;   // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, value=1 - beta2)
+        const float denom = sqrtf(vi) / c.bias2_sqrt + c.eps;
+        g[i] = gi;
+        m[i] = mi;
+        v[i] = vi;
+        p[i] = p[i] - c.step_size * (mi / denom);         // param.addcdiv_(exp_avg, denom, value=-step_size)
+    }
+}
+
+}  // namespace drm
+
+extern "C" int drm_clip_adam(const drm_clip_adam_call* c, void* stream_) {
+    using namespace drm;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    DRM_REQUIRE(c != nullptr, DRM_E_ARG, "null call");
+    DRM_REQUIRE(c->n_tensors >= 1 && c->n_tensors <= DRM_MAX_OPT_TENSORS, DRM_E_SHAPE, "1..64 tensors per call");
+    DRM_REQUIRE(c->workspace && c->workspace_bytes >= 16, DRM_E_WORKSPACE, "workspace too small");
+    for (int t = 0; t < c->n_tensors; ++t)
+        DRM_REQUIRE(c->param[t] && c->grad[t] && c->exp_avg[t] && c->exp_avg_sq[t] && c->numel[t] >= 0, DRM_E_ARG,
+                    "null tensor pointer");
+    int rc = check_device(); if (rc) return rc;
+    double* acc = reinterpret_cast<double*>(rup_sz((size_t)c->workspace, 8));
+    DRM_CUDA_OK(cudaMemsetAsync(acc, 0, sizeof(double), stream));
+    dim3 grid(kOptBlocksPerTensor, c->n_tensors);
+    {
+        ProfScope prof(PROF_LOSS, stream);
+        grad_sumsq_kernel<<<grid, kOptThreads, 0, stream>>>(*c, acc);
+        DRM_CUDA_OK(cudaGetLastError());
+    }
+    {
+        ProfScope prof(PROF_LOSS, stream);
+        clip_adam_kernel<<<grid, kOptThreads, 0, stream>>>(*c, acc);
+        DRM_CUDA_OK(cudaGetLastError());
+    }
+    return DRM_OK;
+}

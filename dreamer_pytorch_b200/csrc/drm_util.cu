@@ -127,6 +127,7 @@ size_t drm_sizeof(const char* name) {
     DRM_SZ(drm_mlp_bwd_call)
     DRM_SZ(drm_returns_loss_call)
     DRM_SZ(drm_kl_call)
+    DRM_SZ(drm_clip_adam_call)
 #undef DRM_SZ
     return 0;
 }

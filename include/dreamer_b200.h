@@ -19,6 +19,7 @@
  *   drm_mlp_fwd / drm_mlp_bwd    DenseModel.forward (the nn.Sequential) dreamer/models/dense.py:28-43
  *                                ActionDecoder.feedforward_model        dreamer/models/action.py:37-52
  *   drm_returns_loss             Dreamer.compute_return + actor/value loss
+ *   drm_clip_adam                clip_grad_norm_ + Adam.step of one optimizer group (dreamer_algo.py:182-194)
  *                                dreamer/algos/dreamer_algo.py:314-337,398-422
  *   drm_kl_loss                  KL(post||prior), free nats, entropies
  *                                dreamer/algos/dreamer_algo.py:270-273,342-343
@@ -234,6 +235,35 @@ int drm_mlp_fwd(const drm_mlp_call* c, void* stream);
 int drm_mlp_bwd(const drm_mlp_bwd_call* c, void* stream);
 
 int drm_returns_loss(const drm_returns_loss_call* c, void* stream);
+
+/* ---- optimizer tail of one parameter group: clip_grad_norm_ + Adam.step ---------------------------
+ * Replaces, for one optimizer group, dreamer_algo.py:182-194:
+ *     grad_norm = torch.nn.utils.clip_grad_norm_(params, grad_clip)      (torch/nn/utils/clip_grad.py)
+ *     optimizer.step()                                                    (torch/optim/adam.py, foreach path,
+ *                                                                          amsgrad=False, weight_decay=0, maximize=False)
+ * in two launches (sum of squares; clip + update) instead of ~16, without a host sync.  Arithmetic, per element:
+ *     g *= min(1, max_norm / (total_norm + 1e-6));  m += (1-beta1) (g - m);  v = beta2 v + (1-beta2) g g;
+ *     p -= step_size * m / (sqrt(v) / bias2_sqrt + eps),   step_size = lr / (1 - beta1^step), bias2_sqrt = sqrt(1 - beta2^step)
+ * (step_size and bias2_sqrt are computed by the caller in double, as torch does).  Gradients are scaled in place, like
+ * clip_grad_norm_ does.  norm_out receives the total 2-norm BEFORE clipping (clip_grad_norm_'s return value). */
+#define DRM_MAX_OPT_TENSORS 64
+typedef struct drm_clip_adam_call {
+    int32_t n_tensors;
+    int32_t pad_;
+    float max_norm;   /* <= 0: no clipping (the norm is still reported) */
+    float beta1, beta2, eps;
+    float one_minus_beta1, one_minus_beta2;  /* computed in double by the host (1 - 0.999f in fp32 is off by 5e-5) */
+    float step_size, bias2_sqrt;
+    float* param[DRM_MAX_OPT_TENSORS];
+    float* grad[DRM_MAX_OPT_TENSORS];
+    float* exp_avg[DRM_MAX_OPT_TENSORS];
+    float* exp_avg_sq[DRM_MAX_OPT_TENSORS];
+    int64_t numel[DRM_MAX_OPT_TENSORS];
+    float* norm_out;   /* device scalar */
+    void* workspace;   /* >= 16 bytes: sum-of-squares accumulator */
+    size_t workspace_bytes;
+} drm_clip_adam_call;
+int drm_clip_adam(const drm_clip_adam_call* c, void* stream);
 int drm_kl_fwd(const drm_kl_call* c, void* stream);
 int drm_kl_bwd(const drm_kl_call* c, void* stream);
 

@@ -508,3 +508,21 @@ def normwise_err(x: torch.Tensor, ref: torch.Tensor) -> float:
     x = x.detach().double().cpu()
     ref = ref.detach().double().cpu()
     return float((x - ref).abs().max() / max(float(ref.abs().max()), 1e-30))
+
+
+# ------------------------------------------------------------------------------------------------
+# optimizer tail: dreamer_algo.py:182-194 = clip_grad_norm_ + Adam.step, on CPU tensors.
+# The arithmetic lives in torch (clip_grad.py, adam.py); the oracle simply runs it.
+# ------------------------------------------------------------------------------------------------
+def clip_adam_steps(params, grads_per_step, lr, grad_clip, betas=(0.9, 0.999), eps=1e-8):
+    """params: list of CPU fp32 tensors (cloned); grads_per_step: list (one entry per step) of lists of gradients.
+    Returns (final params, list of the total norms clip_grad_norm_ reported, final exp_avg, final exp_avg_sq)."""
+    ps = [torch.nn.Parameter(p.detach().clone().float()) for p in params]
+    opt = torch.optim.Adam(ps, lr=lr, betas=betas, eps=eps)
+    norms = []
+    for grads in grads_per_step:
+        for p, g in zip(ps, grads):
+            p.grad = g.detach().clone().float()
+        norms.append(torch.nn.utils.clip_grad_norm_(ps, grad_clip).detach().clone())
+        opt.step()
+    return ([p.detach() for p in ps], norms, [opt.state[p]["exp_avg"] for p in ps], [opt.state[p]["exp_avg_sq"] for p in ps])
