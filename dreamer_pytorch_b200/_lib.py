@@ -57,13 +57,16 @@ class drm_rollout(C.Structure):
     )
 
 
+PHASE_ALL, PHASE_PREPARE, PHASE_RUN = 0, 1, 2
+
+
 class drm_rollout_grad(C.Structure):
     _fields_ = (
         [(k, P) for k in ("g_prior_mean", "g_prior_std", "g_prior_stoch", "g_deter", "g_post_mean", "g_post_std",
                           "g_post_stoch", "g_action_out", "d_start_stoch", "d_start_deter", "d_action_in",
                           "d_obs_embed")]
         + [("rssm", drm_rssm_grad), ("want_rssm_grad", C.c_int32), ("want_actor_grad", C.c_int32),
-           ("actor", drm_mlp_grad)]
+           ("actor", drm_mlp_grad), ("phase", C.c_int32), ("pad_", C.c_int32)]
     )
 
 
@@ -77,7 +80,8 @@ class drm_mlp_call(C.Structure):
 
 class drm_mlp_bwd_call(C.Structure):
     _fields_ = [("fwd", drm_mlp_call), ("dy", P), ("dy_scale", P), ("dx0", P), ("dx1", P),
-                ("accumulate_dx", C.c_int32), ("want_wgrad", C.c_int32), ("grad", drm_mlp_grad)]
+                ("accumulate_dx", C.c_int32), ("want_wgrad", C.c_int32), ("grad", drm_mlp_grad),
+                ("phase", C.c_int32), ("pad_", C.c_int32)]
 
 
 class drm_returns_loss_call(C.Structure):

@@ -28,6 +28,7 @@ _SIDE = {}
 
 
 _PIPELINE_HEADS = True  # heads beside the rollout when SMs are idle (see _ActorLossFn.forward)
+_PREPARE_BACKWARD = True  # weight packing / zero-filled sinks of the backward pass issued beside the forward pass
 
 
 def _side_stream(device, k: int = 0) -> "torch.cuda.Stream":
@@ -68,12 +69,14 @@ class _ActorLossFn(torch.autograd.Function):
         # The rollout occupies one SM per 64 (or 128) start states.  When that leaves SMs idle, the heads run BESIDE it
         # on side streams, gated per time step by the completion counters the rollout kernel publishes: the heads of
         # step t overlap the rollout of step t+1 (drm_rollout.step_flags / drm_mlp_call.wait_flags).
+        ctx.set_materialize_grads(False)  # 12 by-products: no zero tensors for their (unused) gradients
         flags = tiles = fork = None
+        if prec == "bf16" and (_PIPELINE_HEADS or _PREPARE_BACKWARD):
+            fork = torch.cuda.Event()
+            fork.record(torch.cuda.current_stream())  # the side streams branch off BEFORE the rollout is enqueued
         if prec == "bf16" and _PIPELINE_HEADS:
             flags = torch.zeros(H, dtype=torch.int32, device=stoch_dev(t))
             tiles = []
-            fork = torch.cuda.Event()
-            fork.record(torch.cuda.current_stream())  # the side streams branch off BEFORE the rollout is enqueued
         save = rollout_forward_raw(cfg, t, rssm, actor, training, step_flags=flags, tiles_out=tiles)
         x0 = t["prior_stoch"].view(H * N, S)
         x1 = t["deter"].view(H * N, D)
@@ -97,9 +100,35 @@ class _ActorLossFn(torch.autograd.Function):
             outs = [mlp_forward_raw(x0, x1, w, keep, prec) for (w, keep) in heads]
         (reward, rsave), (value, vsave) = outs[0], outs[1]
         pc, psave = outs[2] if pcont_w else (None, None)
+        # The backward pass starts by re-packing the weights for the transposed products and zero-filling the gradient
+        # sinks.  None of that depends on the forward results, so it is issued now, on its own stream, beside the rollout
+        # (DRM_PHASE_PREPARE); backward() then only launches the compute kernels (DRM_PHASE_RUN).
+        plans = None
+        if training and fork is not None and _PREPARE_BACKWARD:
+            main = torch.cuda.current_stream()
+            prep = _side_stream(x0.device, 0)
+            prep.wait_event(fork)
+            with torch.cuda.stream(prep):  # buffers are allocated on `prep` too: it runs ahead of the main stream
+                plans = dict(g_stoch=torch.empty_like(t["prior_stoch"]), g_deter=torch.empty_like(t["deter"]),
+                             reward={}, value={}, pcont={}, vw={}, roll={})
+                gs, gd = plans["g_stoch"].view(H * N, -1), plans["g_deter"].view(H * N, -1)
+                P = _lib.PHASE_PREPARE
+                mlp_backward_raw(x0, x1, reward_w, rsave, None, None, gs, gd, False, False, prec, P, plans["reward"])
+                mlp_backward_raw(x0, x1, value_w, vsave, None, None, gs, gd, True, False, prec, P, plans["value"])
+                if pcont_w:
+                    mlp_backward_raw(x0, x1, pcont_w, psave, None, None, gs, gd, True, False, prec, P, plans["pcont"])
+                mlp_backward_raw(x0, x1, value_w, vsave, None, None, None, None, False, True, prec, P, plans["vw"])
+                rollout_backward_raw(cfg, t, rssm, actor, save, {}, want_actor=True, phase=P, plan=plans["roll"])
+                plans["ev"] = torch.cuda.Event()
+                plans["ev"].record(prep)
+            held = [plans["g_stoch"], plans["g_deter"], plans["roll"]["ws"]] + plans["roll"]["gactor"] + [plans["vw"]["grads"][0]._base]
+            held += [plans[k]["ws"] for k in ("reward", "value", "vw")] + ([plans["pcont"]["ws"]] if pcont_w else [])
+            for x in held:
+                x.record_stream(main)
         out = returns_loss_raw(reward.view(H, N), value.view(H, N), None if pc is None else pc.view(H, N), discount,
                                lambda_)
-        ctx.pack = (cfg, t, rssm, actor, save, reward_w, value_w, pcont_w, rsave, vsave, psave, out, x0, x1, prec, shared)
+        ctx.pack = (cfg, t, rssm, actor, save, reward_w, value_w, pcont_w, rsave, vsave, psave, out, x0, x1, prec, shared,
+                    plans)
         aux = (t["prior_mean"], t["prior_std"], t["prior_stoch"], t["deter"], t["action_out"], reward.view(H, N, 1),
                value.view(H, N, 1), out["returns"].view(H - 1, N, 1), out["disc"].view(H - 1, N, 1),
                out["losses"][1].clone(), out["d_value_pred"], vsave if vsave is not None else torch.empty(0))
@@ -108,36 +137,47 @@ class _ActorLossFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g_loss, *_):
-        (cfg, t, rssm, actor, save, reward_w, value_w, pcont_w, rsave, vsave, psave, out, x0, x1, prec, shared) = ctx.pack
+        (cfg, t, rssm, actor, save, reward_w, value_w, pcont_w, rsave, vsave, psave, out, x0, x1, prec, shared,
+         plans) = ctx.pack
+        ctx.pack = None
+        if g_loss is None:
+            return (None,) * (1 + len(actor))
         H, N = cfg.steps, cfg.n
         g_loss = _f32c(g_loss)
-        g_stoch = torch.empty_like(t["prior_stoch"])
-        g_deter = torch.empty_like(t["deter"])
-        gs, gd = g_stoch.view(H * N, -1), g_deter.view(H * N, -1)
-        mlp_backward_raw(x0, x1, reward_w, rsave, out["d_reward"].view(H * N, 1), g_loss, gs, gd, False, False, prec)
-        mlp_backward_raw(x0, x1, value_w, vsave, out["d_value"].view(H * N, 1), g_loss, gs, gd, True, False, prec)
-        if pcont_w:
-            mlp_backward_raw(x0, x1, pcont_w, psave, out["d_pcont"].view(H * N, 1), g_loss, gs, gd, True, False, prec)
-        # The reverse-time rollout kernel occupies one SM per 128 start states; the value loss' weight-gradient pass
-        # (dreamer_algo.py:331-337) depends on nothing computed here, so it runs beside it on a side stream and
-        # _ValueLossFn.backward only has to scale the result (it recomputes if this backward never ran).
         main = torch.cuda.current_stream()
+        if plans is not None:
+            main.wait_event(plans["ev"])
+            g_stoch, g_deter = plans["g_stoch"], plans["g_deter"]
+            ph = _lib.PHASE_RUN
+            pr, pv, pp, pvw, proll = (plans[k] for k in ("reward", "value", "pcont", "vw", "roll"))
+        else:
+            g_stoch = torch.empty_like(t["prior_stoch"])
+            g_deter = torch.empty_like(t["deter"])
+            ph, pr, pv, pp, pvw, proll = _lib.PHASE_ALL, None, None, None, None, None
+        gs, gd = g_stoch.view(H * N, -1), g_deter.view(H * N, -1)
+        mlp_backward_raw(x0, x1, reward_w, rsave, out["d_reward"].view(H * N, 1), g_loss, gs, gd, False, False, prec, ph, pr)
+        mlp_backward_raw(x0, x1, value_w, vsave, out["d_value"].view(H * N, 1), g_loss, gs, gd, True, False, prec, ph, pv)
+        if pcont_w:
+            mlp_backward_raw(x0, x1, pcont_w, psave, out["d_pcont"].view(H * N, 1), g_loss, gs, gd, True, False, prec, ph,
+                             pp)
+        # The reverse-time rollout kernel occupies one SM per 64 (or 128) start states; the value loss' weight-gradient
+        # pass (dreamer_algo.py:331-337) depends on nothing computed here, so it runs beside it on a side stream and
+        # _ValueLossFn.backward only has to scale the result (it recomputes if this backward never ran).
         side = None
         if shared is not None and not shared.get("value_done") and "value_grads" not in shared:
             side = _side_stream(g_loss.device)
             side.wait_stream(main)
         _, _, gactor = rollout_backward_raw(cfg, t, rssm, actor, save, dict(g_prior_stoch=g_stoch, g_deter=g_deter),
-                                            want_actor=True)
+                                            want_actor=True, phase=ph, plan=proll)
         if side is not None:
             with torch.cuda.stream(side):
                 vg = mlp_backward_raw(x0, x1, value_w, vsave, out["d_value_pred"].view(H * N, 1), None, None, None, False,
-                                      True, prec)
+                                      True, prec, ph, pvw)
                 ev = torch.cuda.Event()
                 ev.record(side)
             for g in vg:
                 g.record_stream(main)
             shared["value_grads"] = (vg, ev)
-        ctx.pack = None
         return (None, *gactor)
 
 
@@ -149,6 +189,7 @@ class _ValueLossFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, pack, *value_w):
         (x0, x1, vsave, d_value_pred, loss, prec, shared) = pack
+        ctx.set_materialize_grads(False)
         ctx.pack = (x0, x1, vsave, d_value_pred, [_f32c(w) for w in value_w], prec, shared)
         return loss.clone()
 
@@ -156,13 +197,19 @@ class _ValueLossFn(torch.autograd.Function):
     def backward(ctx, g_loss):
         x0, x1, vsave, d_value_pred, value_w, prec, shared = ctx.pack
         ctx.pack = None
+        if g_loss is None:
+            return (None,) * (1 + len(value_w))
         cached = shared.pop("value_grads", None) if shared is not None else None
         if shared is not None:
             shared["value_done"] = True
         if cached is not None:
             grads, ev = cached  # computed beside the rollout backward with unit upstream gradient
             torch.cuda.current_stream().wait_event(ev)
-            torch._foreach_mul_(grads, _f32c(g_loss))
+            base = grads[0]._base  # mlp_backward_raw hands out views of one flat buffer: one kernel rescales them all
+            if base is not None:
+                base.mul_(_f32c(g_loss))
+            else:
+                torch._foreach_mul_(grads, _f32c(g_loss))
             return (None, *grads)
         grads = mlp_backward_raw(x0, x1, value_w, vsave, d_value_pred.view(-1, 1), _f32c(g_loss), None, None, False,
                                  True, prec)

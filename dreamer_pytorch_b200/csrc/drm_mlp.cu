@@ -421,7 +421,10 @@ int drm_mlp_bwd(const drm_mlp_bwd_call* bc, void* stream_) {
     int rc = validate(c); if (rc) return rc;
     rc = check_device(); if (rc) return rc;
     const drm_mlp& m = c->mlp;
-    DRM_REQUIRE(bc->dy, DRM_E_ARG, "null dy");
+    DRM_REQUIRE(bc->phase >= DRM_PHASE_ALL && bc->phase <= DRM_PHASE_RUN, DRM_E_ARG, "bad phase");
+    const bool tc_path = c->precision == DRM_BF16;
+    if (bc->phase == DRM_PHASE_PREPARE && !tc_path) return DRM_OK;  // fp32: everything happens in RUN
+    DRM_REQUIRE(bc->dy || bc->phase == DRM_PHASE_PREPARE, DRM_E_ARG, "null dy");
     DRM_REQUIRE(c->workspace && c->workspace_bytes >= drm_mlp_workspace_bytes(c), DRM_E_WORKSPACE, "workspace too small");
     if (m.n_linear > 1) DRM_REQUIRE(c->save && c->save_bytes >= drm_mlp_save_bytes(c), DRM_E_WORKSPACE, "save buffer missing");
     const bool want_dx = bc->dx0 || bc->dx1;
@@ -431,12 +434,13 @@ int drm_mlp_bwd(const drm_mlp_bwd_call* bc, void* stream_) {
             const int nout = l == m.n_linear - 1 ? m.out_dim : m.hidden;
             const int nin = l == 0 ? m.in_dim : m.hidden;
             DRM_REQUIRE(bc->grad.dW[l] && bc->grad.db[l], DRM_E_ARG, "null weight-gradient sink");
+            if (tc_path && c->M > 0) continue;  // zero-filled by the weight packing launch
             DRM_CUDA_OK(cudaMemsetAsync(bc->grad.dW[l], 0, (size_t)nout * nin * sizeof(float), stream));
             DRM_CUDA_OK(cudaMemsetAsync(bc->grad.db[l], 0, (size_t)nout * sizeof(float), stream));
         }
     }
     if (c->M == 0) return DRM_OK;
-    if (c->precision == DRM_BF16) return tc::mlp_tc_bwd(bc, stream);
+    if (tc_path) return tc::mlp_tc_bwd(bc, stream);
     MlpDev p; fill_common(p, c);
     Packer pk((float*)c->workspace);
     for (int l = 0; l < m.n_linear; ++l) {

@@ -12,6 +12,13 @@ namespace tc {
 // weight image packing
 // ------------------------------------------------------------------------------------------------
 __global__ void pack_tc_kernel(PackTcJobs jobs) {
+    if ((int)blockIdx.y == jobs.n) {  // the extra grid row zero-fills the gradient sinks
+        for (int q = 0; q < jobs.nz; ++q) {
+            float* z = jobs.z[q];
+            for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < jobs.zn[q]; i += gridDim.x * blockDim.x) z[i] = 0.f;
+        }
+        return;
+    }
     const PackTcJob j = jobs.j[blockIdx.y];
     const int total = j.k_chunks * j.n_pad * 8;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -37,9 +44,10 @@ __global__ void pack_tc_kernel(PackTcJobs jobs) {
 }
 
 int launch_pack_tc(const PackTcJobs& jobs, cudaStream_t stream) {
-    if (jobs.n == 0) return DRM_OK;
+    if (jobs.n == 0 && jobs.nz == 0) return DRM_OK;
     DRM_REQUIRE(jobs.n <= kMaxPackTcJobs, DRM_E_SHAPE, "too many tensor-core pack jobs");
-    dim3 grid(24, jobs.n);
+    DRM_REQUIRE(jobs.nz <= kMaxZeroJobs, DRM_E_SHAPE, "too many zero-fill jobs");
+    dim3 grid(24, jobs.n + (jobs.nz > 0 ? 1 : 0));
     ProfScope prof(PROF_PACK, stream);
     pack_tc_kernel<<<grid, 256, 0, stream>>>(jobs);
     DRM_CUDA_OK(cudaGetLastError());
@@ -603,7 +611,18 @@ int mlp_tc_bwd(const drm_mlp_bwd_call* bc, cudaStream_t stream) {
         }
     }
     if (!want_dx && !bc->want_wgrad) return DRM_OK;
-    rc = launch_pack_tc(pl.jobs, stream); if (rc) return rc;
+    if (bc->phase != DRM_PHASE_RUN) {
+        if (bc->want_wgrad) {
+            for (int l = 0; l <= last; ++l) {
+                const int nout = l == last ? m.out_dim : m.hidden;
+                const int nin = l == 0 ? m.in_dim : m.hidden;
+                pl.jobs.zero(bc->grad.dW[l], (size_t)nout * nin);
+                pl.jobs.zero(bc->grad.db[l], (size_t)nout);
+            }
+        }
+        rc = launch_pack_tc(pl.jobs, stream); if (rc) return rc;
+        if (bc->phase == DRM_PHASE_PREPARE) return DRM_OK;
+    }
     {
         const int grid = pl.tiles < kNumSM ? pl.tiles : kNumSM;
         DRM_CUDA_OK(cudaFuncSetAttribute(mlp_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));

@@ -1223,12 +1223,15 @@ int rollout_tc_bwd(const drm_rollout* r, const drm_rollout_grad* g, cudaStream_t
             const int nout = l == a.n_linear - 1 ? a.out_dim : a.hidden;
             const int nin = l == 0 ? a.in_dim : a.hidden;
             DRM_REQUIRE(g->actor.dW[l] && g->actor.db[l], DRM_E_ARG, "null actor gradient sink");
-            DRM_CUDA_OK(cudaMemsetAsync(g->actor.dW[l], 0, sizeof(float) * nout * nin, stream));
-            DRM_CUDA_OK(cudaMemsetAsync(g->actor.db[l], 0, sizeof(float) * nout, stream));
+            pl.jobs.zero(g->actor.dW[l], (size_t)nout * nin);
+            pl.jobs.zero(g->actor.db[l], (size_t)nout);
         }
         d.db_a_last = g->actor.db[a.n_linear - 1];
     }
-    rc = launch_pack_tc(pl.jobs, stream); if (rc) return rc;
+    if (g->phase != DRM_PHASE_RUN) {
+        rc = launch_pack_tc(pl.jobs, stream); if (rc) return rc;
+        if (g->phase == DRM_PHASE_PREPARE) return DRM_OK;
+    }
     {
         const int grid = d.ntiles < kNumSM ? d.ntiles : kNumSM;
         ProfScope prof(PROF_ROLLOUT_BWD, stream);

@@ -467,9 +467,15 @@ struct PackTcJob {
     int seg_kstart[3], seg_len[3], seg_src0[3];
 };
 constexpr int kMaxPackTcJobs = 28;
+constexpr int kMaxZeroJobs = 16;
 struct PackTcJobs {
     PackTcJob j[kMaxPackTcJobs];
-    int n;
+    int n = 0;
+    // gradient sinks to zero-fill in the same launch (they are accumulated with atomics by the weight-gradient kernel)
+    float* z[kMaxZeroJobs];
+    int zn[kMaxZeroJobs];
+    int nz = 0;
+    void zero(float* p, size_t count) { if (nz < kMaxZeroJobs) { z[nz] = p; zn[nz] = (int)count; } ++nz; }
 };
 int launch_pack_tc(const PackTcJobs& jobs, cudaStream_t stream);
 

@@ -162,49 +162,59 @@ def rollout_forward_raw(cfg: RolloutCfg, t: dict, rssm, actor, training: bool, s
 
 
 def rollout_backward_raw(cfg: RolloutCfg, t: dict, rssm, actor, save, gouts: dict, want_inputs=(False,) * 4,
-                         want_rssm=False, want_actor=False):
+                         want_rssm=False, want_actor=False, phase: int = 0, plan: Optional[dict] = None):
     """Runs drm_rollout_bwd.  gouts: name ('g_prior_mean', ...) -> tensor or None.
     want_inputs: (start_stoch, start_deter, action_in, obs_embed).
-    Returns (input grads [4], rssm grads list or None, actor grads list or None)."""
+    Returns (input grads [4], rssm grads list or None, actor grads list or None).
+
+    phase / plan: a PHASE_PREPARE call (weight packing + zero-filled sinks, may be issued early on another stream)
+    stores the call description, workspace and sinks in the dict `plan`; the later PHASE_RUN call with the same dict
+    reuses them (include/dreamer_b200.h, DRM_PHASE_*)."""
     lib = _lib.load()
     dev = t["start_stoch"].device
     if save is None:
         raise RuntimeError("rollout was run without grad; cannot backpropagate")
-    r = _build_rollout(cfg, t, rssm, actor, True)
-    ws = _buf(lib.drm_rollout_workspace_bytes(C.byref(r)), dev)
-    r.workspace, r.workspace_bytes = ws.data_ptr(), ws.numel() * 4
-    r.save, r.save_bytes = save.data_ptr(), save.numel() * 4
-    g = _lib.drm_rollout_grad()
+    if plan is not None and "r" in plan:
+        r, g, ws, din, grssm, gactor = (plan[k] for k in ("r", "g", "ws", "din", "grssm", "gactor"))
+    else:
+        r = _build_rollout(cfg, t, rssm, actor, True)
+        ws = _buf(lib.drm_rollout_workspace_bytes(C.byref(r)), dev)
+        r.workspace, r.workspace_bytes = ws.data_ptr(), ws.numel() * 4
+        r.save, r.save_bytes = save.data_ptr(), save.numel() * 4
+        g = _lib.drm_rollout_grad()
+        policy = cfg.mode == _lib.MODE_POLICY
+        din: List[Optional[torch.Tensor]] = [None] * 4
+        if not policy:
+            if want_inputs[0]:
+                din[0] = torch.empty_like(t["start_stoch"]); g.d_start_stoch = din[0].data_ptr()
+            if want_inputs[1]:
+                din[1] = torch.empty_like(t["start_deter"]); g.d_start_deter = din[1].data_ptr()
+            if want_inputs[2]:
+                din[2] = torch.empty_like(t["action_in"]); g.d_action_in = din[2].data_ptr()
+            if want_inputs[3] and cfg.mode == _lib.MODE_REPRESENTATION:
+                din[3] = torch.empty_like(t["obs_embed"]); g.d_obs_embed = din[3].data_ptr()
+        n_rssm = 14 if cfg.mode == _lib.MODE_REPRESENTATION else 10
+        g.want_rssm_grad = 1 if want_rssm else 0
+        grssm = None
+        if want_rssm:
+            grssm = [torch.empty_like(rssm[i]) for i in range(n_rssm)] + [None] * (14 - n_rssm)
+            for i in range(n_rssm):
+                setattr(g.rssm, _lib._RSSM_G[i], grssm[i].data_ptr())
+        want_actor = policy and want_actor
+        g.want_actor_grad = 1 if want_actor else 0
+        gactor = None
+        if want_actor:
+            gactor = [torch.empty_like(w) for w in actor]
+            for l in range(len(actor) // 2):
+                g.actor.dW[l], g.actor.db[l] = gactor[2 * l].data_ptr(), gactor[2 * l + 1].data_ptr()
+        if plan is not None:
+            plan.update(r=r, g=g, ws=ws, din=din, grssm=grssm, gactor=gactor)
     keep = []
     for k, x in gouts.items():
         x = _f32c(x)
         keep.append(x)
         setattr(g, k, _lib.ptr(x))
-    policy = cfg.mode == _lib.MODE_POLICY
-    din: List[Optional[torch.Tensor]] = [None] * 4
-    if not policy:
-        if want_inputs[0]:
-            din[0] = torch.empty_like(t["start_stoch"]); g.d_start_stoch = din[0].data_ptr()
-        if want_inputs[1]:
-            din[1] = torch.empty_like(t["start_deter"]); g.d_start_deter = din[1].data_ptr()
-        if want_inputs[2]:
-            din[2] = torch.empty_like(t["action_in"]); g.d_action_in = din[2].data_ptr()
-        if want_inputs[3] and cfg.mode == _lib.MODE_REPRESENTATION:
-            din[3] = torch.empty_like(t["obs_embed"]); g.d_obs_embed = din[3].data_ptr()
-    n_rssm = 14 if cfg.mode == _lib.MODE_REPRESENTATION else 10
-    g.want_rssm_grad = 1 if want_rssm else 0
-    grssm = None
-    if want_rssm:
-        grssm = [torch.empty_like(rssm[i]) for i in range(n_rssm)] + [None] * (14 - n_rssm)
-        for i in range(n_rssm):
-            setattr(g.rssm, _lib._RSSM_G[i], grssm[i].data_ptr())
-    want_actor = policy and want_actor
-    g.want_actor_grad = 1 if want_actor else 0
-    gactor = None
-    if want_actor:
-        gactor = [torch.empty_like(w) for w in actor]
-        for l in range(len(actor) // 2):
-            g.actor.dW[l], g.actor.db[l] = gactor[2 * l].data_ptr(), gactor[2 * l + 1].data_ptr()
+    g.phase = phase
     _lib.check(lib.drm_rollout_bwd(C.byref(r), C.byref(g), _stream()), "drm_rollout_bwd")
     _count()
     return din, grssm, gactor
@@ -308,29 +318,41 @@ def mlp_forward_raw(x0, x1, weights, training, precision=None, wait=None, max_ct
 
 
 def mlp_backward_raw(x0, x1, weights, save, dy, dy_scale=None, dx0=None, dx1=None, accumulate_dx=False,
-                     want_wgrad=False, precision="fp32"):
-    """Runs drm_mlp_bwd; returns the list of weight grads [dW0, db0, dW1, ...] (or None)."""
+                     want_wgrad=False, precision="fp32", phase: int = 0, plan: Optional[dict] = None):
+    """Runs drm_mlp_bwd; returns the list of weight grads [dW0, db0, dW1, ...] (or None).
+    phase / plan: as in rollout_backward_raw (dy / dx may be None in the PHASE_PREPARE call)."""
     lib = _lib.load()
     M = x0.shape[0]
-    b = _lib.drm_mlp_bwd_call()
-    c = _build_mlp_call(x0, x1, weights, M, True, precision)
-    dev = x0.device
-    ws = _buf(lib.drm_mlp_workspace_bytes(C.byref(c)), dev)
-    c.workspace, c.workspace_bytes = ws.data_ptr(), ws.numel() * 4
-    if save is not None:
-        c.save, c.save_bytes = save.data_ptr(), save.numel() * 4
-    b.fwd = c
+    if plan is not None and "b" in plan:
+        b, ws, grads = plan["b"], plan["ws"], plan["grads"]
+    else:
+        b = _lib.drm_mlp_bwd_call()
+        c = _build_mlp_call(x0, x1, weights, M, True, precision)
+        ws = _buf(lib.drm_mlp_workspace_bytes(C.byref(c)), x0.device)
+        c.workspace, c.workspace_bytes = ws.data_ptr(), ws.numel() * 4
+        if save is not None:
+            c.save, c.save_bytes = save.data_ptr(), save.numel() * 4
+        b.fwd = c
+        b.want_wgrad = 1 if want_wgrad else 0
+        grads = None
+        if want_wgrad:
+            # views of one flat buffer (16-byte aligned pieces): a caller can rescale all of them with one kernel
+            sizes = [(w.numel() + 3) // 4 * 4 for w in weights]
+            flat = torch.empty(sum(sizes), dtype=torch.float32, device=x0.device)
+            grads, o = [], 0
+            for w, n in zip(weights, sizes):
+                grads.append(flat[o:o + w.numel()].view(w.shape))
+                o += n
+            for l in range(len(weights) // 2):
+                b.grad.dW[l], b.grad.db[l] = grads[2 * l].data_ptr(), grads[2 * l + 1].data_ptr()
+        if plan is not None:
+            plan.update(b=b, ws=ws, grads=grads, keep=(x0, x1, weights, save))
     b.dy = _lib.ptr(dy)
     b.dy_scale = _lib.ptr(dy_scale)
     b.dx0 = _lib.ptr(dx0)
     b.dx1 = _lib.ptr(dx1)
     b.accumulate_dx = 1 if accumulate_dx else 0
-    b.want_wgrad = 1 if want_wgrad else 0
-    grads = None
-    if want_wgrad:
-        grads = [torch.empty_like(w) for w in weights]
-        for l in range(len(weights) // 2):
-            b.grad.dW[l], b.grad.db[l] = grads[2 * l].data_ptr(), grads[2 * l + 1].data_ptr()
+    b.phase = phase
     _lib.check(lib.drm_mlp_bwd(C.byref(b), _stream()), "drm_mlp_bwd")
     _count()
     return grads

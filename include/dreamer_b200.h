@@ -136,6 +136,15 @@ typedef struct drm_rollout {
     int32_t* step_flags;
 } drm_rollout;
 
+/* Backward calls in two halves.  A backward pass first re-packs the (unchanged) weights for the transposed products and
+ * zero-fills the weight-gradient sinks -- work that depends on nothing the forward pass computes.  PREPARE issues only
+ * that part (the caller may put it on another stream, beside the forward pass); RUN issues the rest and requires a
+ * completed PREPARE with the same workspace, weights and sinks.  ALL (0, the default) does both.  The fp32 kernels
+ * treat PREPARE as a no-op and RUN as ALL. */
+#define DRM_PHASE_ALL 0
+#define DRM_PHASE_PREPARE 1
+#define DRM_PHASE_RUN 2
+
 /* Upstream gradients (NULL = zero) and gradient sinks (NULL = not wanted) of a rollout. */
 typedef struct drm_rollout_grad {
     const float *g_prior_mean, *g_prior_std, *g_prior_stoch, *g_deter; /* [steps,n,.] */
@@ -149,6 +158,8 @@ typedef struct drm_rollout_grad {
     int32_t want_rssm_grad;  /* 0: weights frozen (FreezeParameters), skip all RSSM weight grads */
     int32_t want_actor_grad;
     drm_mlp_grad actor;
+    int32_t phase;   /* DRM_PHASE_*: lets the weight packing + zero-filling of the sinks be issued early (another stream) */
+    int32_t pad_;
 } drm_rollout_grad;
 
 /* Batched MLP over M rows; the input is the concatenation of two column segments
@@ -179,6 +190,8 @@ typedef struct drm_mlp_bwd_call {
     int32_t accumulate_dx;     /* 1: dx += , 0: dx = */
     int32_t want_wgrad;
     drm_mlp_grad grad;
+    int32_t phase;   /* DRM_PHASE_* */
+    int32_t pad_;
 } drm_mlp_bwd_call;
 
 /* lambda-returns + actor loss + value loss over imagined heads, forward AND the gradients of
