@@ -15,8 +15,10 @@ constexpr int kWgThreads = 192;          // warps 0-3 epilogue, 4 producer, 5 MM
 constexpr int kWgStages = 2;
 constexpr int kWgAChunks = 16;           // 128 out-features
 constexpr int kWgBChunks = 32;           // <= 256 in-features per part
-constexpr int kWgStageBytes = (kWgAChunks + kWgBChunks) * kChunkBytes;  // 96 KB
-constexpr int kWgSmem = 1024 + kWgStages * kWgStageBytes;
+// one stage holds a tile of dY (16 chunks) and of X (32 chunks): 96 KB with 128-row tiles, 48 KB with 64-row tiles --
+// the half-tile images therefore leave room for two CTAs per SM (2 x 256 TMEM columns)
+__host__ __device__ inline int wg_stage_bytes(int tr) { return (kWgAChunks + kWgBChunks) * tr * 16; }
+__host__ __device__ inline int wg_smem(int tr) { return 1024 + kWgStages * wg_stage_bytes(tr); }
 constexpr int kWgTmemCols = 256;
 
 struct WgBars {
@@ -26,9 +28,16 @@ struct WgBars {
     uint32_t tmem_slot;
 };
 
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ void red_add_v2(float* p, float a, float b) {
+    asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(p), "f"(a), "f"(b) : "memory");
+}
+
 __host__ __device__ inline uint32_t make_idesc_bf16_mn(int M, int N) { return make_idesc_bf16(M, N) | (1u << 15) | (1u << 16); }
 
-__global__ void __launch_bounds__(kWgThreads, 1) wgrad_tc_kernel(const __grid_constant__ WgParams w) {
+__global__ void __launch_bounds__(kWgThreads, 2) wgrad_tc_kernel(const __grid_constant__ WgParams w) {
     extern __shared__ __align__(1024) uint8_t smem[];
     WgBars* bars = reinterpret_cast<WgBars*>(smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -36,6 +45,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_tc_kernel(const __grid_co
     // the shared-memory regions keep their 128-row capacity
     const int tr = w.tile_rows ? w.tile_rows : kTileRows;
     const int cb = tr * 16;
+    const int stage_bytes = wg_stage_bytes(tr), a_bytes = kWgAChunks * cb;
     // ---- which job is mine
     int li = 0;
     for (int i = 1; i < w.n_layers; ++i) if ((int)blockIdx.x >= w.L[i].cta0) li = i;
@@ -62,7 +72,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_tc_kernel(const __grid_co
     if (warp < 4) {
         const int ones_pos = (L.db && f_end == ft) ? npc - 1 : -1;
         for (int s = 0; s < kWgStages; ++s) {
-            uint8_t* B = smem + 1024 + s * kWgStageBytes + kWgAChunks * kChunkBytes;
+            uint8_t* B = smem + 1024 + s * stage_bytes + a_bytes;
             for (int r = threadIdx.x; r < tr; r += 128) {
                 if (ones_pos >= 0) {
                     uint4 q = make_uint4(0x00003F80u, 0u, 0u, 0u);  // bf16 1.0 in element 0
@@ -90,8 +100,8 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_tc_kernel(const __grid_co
             int stage = 0; uint32_t phase = 0;
             for (int it = 0; it < my_tiles; ++it) {
                 const int tile = split + it * L.splits;
-                uint8_t* A = smem + 1024 + stage * kWgStageBytes;
-                uint8_t* B = A + kWgAChunks * kChunkBytes;
+                uint8_t* A = smem + 1024 + stage * stage_bytes;
+                uint8_t* B = A + a_bytes;
                 mbar_wait(&bars->empty[stage], phase ^ 1);
                 mbar_expect_tx(&bars->full[stage], bytes);
                 auto img = [&](const __nv_bfloat16* base, int cpt, int chunk) {  // chunk of TCM tile `tile` (tr rows per tile)
@@ -112,8 +122,8 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_tc_kernel(const __grid_co
             const uint32_t idesc = make_idesc_bf16_mn(128, n_mma);  // M = 128 output features of this n-tile
             int stage = 0; uint32_t phase = 0;
             for (int it = 0; it < my_tiles; ++it) {
-                const uint32_t A = smem_u32(smem + 1024 + stage * kWgStageBytes);
-                const uint32_t B = A + kWgAChunks * kChunkBytes;
+                const uint32_t A = smem_u32(smem + 1024 + stage * stage_bytes);
+                const uint32_t B = A + a_bytes;
                 mbar_wait(&bars->full[stage], phase);
                 tc_fence_after_sync();
                 for (int k = 0; k < tr / 16; ++k)  // K = rows of the tile, 16 per instruction
@@ -138,8 +148,19 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_tc_kernel(const __grid_co
                 const WgSeg& sg = f < nch0 ? L.seg[0] : L.seg[1];
                 const int fc = f < nch0 ? f : f - nch0;
                 float* dst = L.dW + (size_t)gn * L.ld_dw + sg.col0 + fc * 8;
+                // vector reductions (one L2 operation per 8 / 16 bytes): the partial sums of ~40 row splits land on the
+                // same addresses, and the L2 atomic rate -- not the GEMM -- bounds this kernel
+                const bool full = fc * 8 + 8 <= sg.kvalid;
+                if (full && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+                    red_add_v4(dst, v[0], v[1], v[2], v[3]);
+                    red_add_v4(dst + 4, v[4], v[5], v[6], v[7]);
+                } else if (full && (reinterpret_cast<uintptr_t>(dst) & 7) == 0) {
 #pragma unroll
-                for (int i = 0; i < 8; ++i) if (fc * 8 + i < sg.kvalid) atomicAdd(dst + i, v[i]);
+                    for (int i = 0; i < 8; i += 2) red_add_v2(dst + i, v[i], v[i + 1]);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) if (fc * 8 + i < sg.kvalid) atomicAdd(dst + i, v[i]);
+                }
             } else {
                 atomicAdd(L.db + gn, v[0]);
             }
@@ -160,8 +181,9 @@ void wgrad_tc_plan(WgParams& w) {
         L.part_chunks = (ft + L.n_parts - 1) / L.n_parts;
         base += L.n_tiles_n * L.n_parts;
     }
-    // row-tile splits: fill about two waves of the chip, but keep >= 4 row tiles per CTA
-    int splits = base > 0 ? (2 * kNumSM + base - 1) / base : 1;
+    // row-tile splits: at most two CTAs per SM in total (one wave of co-resident pairs with 64-row tiles, two full waves
+    // with 128-row tiles -- never a third, nearly empty one), but keep >= 4 row tiles per CTA
+    int splits = base > 0 ? (2 * kNumSM) / base : 1;
     const int max_splits = (w.row_tiles + 3) / 4;
     if (splits > max_splits) splits = max_splits;
     if (splits < 1) splits = 1;
@@ -178,9 +200,10 @@ void wgrad_tc_plan(WgParams& w) {
 int launch_wgrad_tc(const WgParams& w, cudaStream_t stream) {
     if (w.n_layers == 0 || w.total_ctas == 0 || w.row_tiles == 0) return DRM_OK;
     DRM_REQUIRE(w.n_layers <= kMaxWgLayers, DRM_E_SHAPE, "too many layers in one weight-gradient launch");
-    DRM_CUDA_OK(cudaFuncSetAttribute(wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmem));
+    const int smem = wg_smem(w.tile_rows ? w.tile_rows : kTileRows);
+    DRM_CUDA_OK(cudaFuncSetAttribute(wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     ProfScope prof(PROF_WGRAD, stream);
-    wgrad_tc_kernel<<<w.total_ctas, kWgThreads, kWgSmem, stream>>>(w);
+    wgrad_tc_kernel<<<w.total_ctas, kWgThreads, smem, stream>>>(w);
     DRM_CUDA_OK(cudaGetLastError());
     return DRM_OK;
 }
