@@ -66,7 +66,7 @@ class drm_rollout_grad(C.Structure):
                           "g_post_stoch", "g_action_out", "d_start_stoch", "d_start_deter", "d_action_in",
                           "d_obs_embed")]
         + [("rssm", drm_rssm_grad), ("want_rssm_grad", C.c_int32), ("want_actor_grad", C.c_int32),
-           ("actor", drm_mlp_grad), ("phase", C.c_int32), ("pad_", C.c_int32)]
+           ("actor", drm_mlp_grad), ("phase", C.c_int32), ("g_wait_target", C.c_int32), ("g_wait_flags", P)]
     )
 
 
@@ -81,7 +81,8 @@ class drm_mlp_call(C.Structure):
 class drm_mlp_bwd_call(C.Structure):
     _fields_ = [("fwd", drm_mlp_call), ("dy", P), ("dy_scale", P), ("dx0", P), ("dx1", P),
                 ("accumulate_dx", C.c_int32), ("want_wgrad", C.c_int32), ("grad", drm_mlp_grad),
-                ("phase", C.c_int32), ("pad_", C.c_int32)]
+                ("phase", C.c_int32), ("reverse_tiles", C.c_int32), ("tile_done", P), ("tile_wait", P),
+                ("step_rows_done", P), ("step_rows", C.c_int32), ("step_count", C.c_int32)]
 
 
 class drm_returns_loss_call(C.Structure):

@@ -29,6 +29,7 @@ _SIDE = {}
 
 _PIPELINE_HEADS = True  # heads beside the rollout when SMs are idle (see _ActorLossFn.forward)
 _PREPARE_BACKWARD = True  # weight packing / zero-filled sinks of the backward pass issued beside the forward pass
+_PIPELINE_BACKWARD = True  # head data-gradient kernels beside the reverse-time rollout (see _ActorLossFn.backward)
 
 
 def _side_stream(device, k: int = 0) -> "torch.cuda.Stream":
@@ -128,7 +129,7 @@ class _ActorLossFn(torch.autograd.Function):
         out = returns_loss_raw(reward.view(H, N), value.view(H, N), None if pc is None else pc.view(H, N), discount,
                                lambda_)
         ctx.pack = (cfg, t, rssm, actor, save, reward_w, value_w, pcont_w, rsave, vsave, psave, out, x0, x1, prec, shared,
-                    plans)
+                    plans, tiles[0] if tiles else 0)
         aux = (t["prior_mean"], t["prior_std"], t["prior_stoch"], t["deter"], t["action_out"], reward.view(H, N, 1),
                value.view(H, N, 1), out["returns"].view(H - 1, N, 1), out["disc"].view(H - 1, N, 1),
                out["losses"][1].clone(), out["d_value_pred"], vsave if vsave is not None else torch.empty(0))
@@ -138,7 +139,7 @@ class _ActorLossFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_loss, *_):
         (cfg, t, rssm, actor, save, reward_w, value_w, pcont_w, rsave, vsave, psave, out, x0, x1, prec, shared,
-         plans) = ctx.pack
+         plans, roll_tiles) = ctx.pack
         ctx.pack = None
         if g_loss is None:
             return (None,) * (1 + len(actor))
@@ -155,11 +156,35 @@ class _ActorLossFn(torch.autograd.Function):
             g_deter = torch.empty_like(t["deter"])
             ph, pr, pv, pp, pvw, proll = _lib.PHASE_ALL, None, None, None, None, None
         gs, gd = g_stoch.view(H * N, -1), g_deter.view(H * N, -1)
-        mlp_backward_raw(x0, x1, reward_w, rsave, out["d_reward"].view(H * N, 1), g_loss, gs, gd, False, False, prec, ph, pr)
-        mlp_backward_raw(x0, x1, value_w, vsave, out["d_value"].view(H * N, 1), g_loss, gs, gd, True, False, prec, ph, pv)
+        heads = [(reward_w, rsave, out["d_reward"], pr), (value_w, vsave, out["d_value"], pv)]
         if pcont_w:
-            mlp_backward_raw(x0, x1, pcont_w, psave, out["d_pcont"].view(H * N, 1), g_loss, gs, gd, True, False, prec, ph,
-                             pp)
+            heads.append((pcont_w, psave, out["d_pcont"], pp))
+        # The reverse-time rollout needs the heads' data gradients of step t only when it gets to step t, and it leaves
+        # most SMs idle: the head kernels run BESIDE it on side streams, last step first, each accumulating into the rows
+        # the previous head has finished (tile_done / tile_wait) and the last one publishing per-step row counters the
+        # rollout kernel waits on (step_rows_done / g_wait_flags).  Grids are capped so that all of them are resident.
+        free = (_sm_count(g_loss.device) - roll_tiles) // len(heads) if roll_tiles > 0 else 0
+        g_wait = None
+        if prec == "bf16" and _PIPELINE_BACKWARD and free >= 16:
+            mlp_tiles = (H * N + 127) // 128
+            cnt = torch.zeros(len(heads) * mlp_tiles + H, dtype=torch.int32, device=g_loss.device)
+            steps_done = cnt[len(heads) * mlp_tiles:]
+            fork = torch.cuda.Event()
+            fork.record(main)
+            for i, (w, sv, dy, pl) in enumerate(heads):
+                gate = dict(max_ctas=free, reverse=True, tile_done=cnt[i * mlp_tiles:(i + 1) * mlp_tiles],
+                            tile_wait=cnt[(i - 1) * mlp_tiles:i * mlp_tiles] if i > 0 else None,
+                            step_done=(steps_done, N, H) if i == len(heads) - 1 else None)
+                hs = _side_stream(g_loss.device, 1 + i)
+                hs.wait_event(fork)
+                with torch.cuda.stream(hs):
+                    mlp_backward_raw(x0, x1, w, sv, dy.view(H * N, 1), g_loss, gs, gd, i > 0, False, prec, ph, pl, gate)
+            g_wait = (steps_done, N)
+            joins = [_side_stream(g_loss.device, 1 + i) for i in range(len(heads))]
+        else:
+            for i, (w, sv, dy, pl) in enumerate(heads):
+                mlp_backward_raw(x0, x1, w, sv, dy.view(H * N, 1), g_loss, gs, gd, i > 0, False, prec, ph, pl)
+            joins = []
         # The reverse-time rollout kernel occupies one SM per 64 (or 128) start states; the value loss' weight-gradient
         # pass (dreamer_algo.py:331-337) depends on nothing computed here, so it runs beside it on a side stream and
         # _ValueLossFn.backward only has to scale the result (it recomputes if this backward never ran).
@@ -167,8 +192,12 @@ class _ActorLossFn(torch.autograd.Function):
         if shared is not None and not shared.get("value_done") and "value_grads" not in shared:
             side = _side_stream(g_loss.device)
             side.wait_stream(main)
+            for hs in joins:  # not critical: starts once the head kernels have left, so that the rollout is never kept waiting
+                side.wait_stream(hs)
         _, _, gactor = rollout_backward_raw(cfg, t, rssm, actor, save, dict(g_prior_stoch=g_stoch, g_deter=g_deter),
-                                            want_actor=True, phase=ph, plan=proll)
+                                            want_actor=True, phase=ph, plan=proll, g_wait=g_wait)
+        for hs in joins:
+            main.wait_stream(hs)
         if side is not None:
             with torch.cuda.stream(side):
                 vg = mlp_backward_raw(x0, x1, value_w, vsave, out["d_value_pred"].view(H * N, 1), None, None, None, False,

@@ -423,6 +423,8 @@ int drm_mlp_bwd(const drm_mlp_bwd_call* bc, void* stream_) {
     const drm_mlp& m = c->mlp;
     DRM_REQUIRE(bc->phase >= DRM_PHASE_ALL && bc->phase <= DRM_PHASE_RUN, DRM_E_ARG, "bad phase");
     const bool tc_path = c->precision == DRM_BF16;
+    DRM_REQUIRE(tc_path || !(bc->tile_done || bc->tile_wait || bc->step_rows_done), DRM_E_ARG,
+                "tile_done / tile_wait / step_rows_done are honoured by the bf16 kernels only");
     if (bc->phase == DRM_PHASE_PREPARE && !tc_path) return DRM_OK;  // fp32: everything happens in RUN
     DRM_REQUIRE(bc->dy || bc->phase == DRM_PHASE_PREPARE, DRM_E_ARG, "null dy");
     DRM_REQUIRE(c->workspace && c->workspace_bytes >= drm_mlp_workspace_bytes(c), DRM_E_WORKSPACE, "workspace too small");

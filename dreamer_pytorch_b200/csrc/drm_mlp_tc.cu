@@ -75,6 +75,8 @@ struct MlpTcDev {
     __nv_bfloat16* dys[DRM_MAX_LINEAR];   // TCM images of dY_l (ch chunks; cout for the last layer) or nullptr
     float* db_last;                       // bias gradient of the last Linear, reduced in fp32 from the exact dY
     const int* wait_flags; int wait_target, wait_rows, wait_steps;  // producer gating of the input rows (forward)
+    // backward hand-over between kernels on different streams (drm_mlp_bwd_call)
+    int reverse_tiles; int* tile_done; const int* tile_wait; int* step_rows_done; int step_rows, step_count;
     TcProgram pg;
 };
 
@@ -320,7 +322,8 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_bwd_tc_kernel(const __gr
         const int last = p.n_linear - 1;
         const float scale = p.dy_scale ? __ldg(p.dy_scale) : 1.f;
         const bool want_dx = p.dx0 != nullptr || p.dx1 != nullptr;
-        for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        for (int ti = blockIdx.x; ti < tiles; ti += gridDim.x) {
+            const int tile = p.reverse_tiles ? tiles - 1 - ti : ti;
             const int row0 = tile * kTileRows;
             // ---- stage dY of the last Linear (scaled) as the first A operand [+ TCM copy for its wgrad]
             for (int idx = threadIdx.x; idx < p.cout * kTileRows; idx += kEpiThreads) {
@@ -348,8 +351,8 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_bwd_tc_kernel(const __gr
             const bool live = grow < p.M;
             // the next tile's saved activations are pulled into L2 while this tile is processed
             {
-                const int nxt = tile + gridDim.x;
-                if (nxt < tiles && threadIdx.x == 0)
+                const int nti = ti + gridDim.x, nxt = p.reverse_tiles ? tiles - 1 - nti : nti;
+                if (nti < tiles && threadIdx.x == 0)
                     for (int l = 0; l < last; ++l) l2_prefetch(tcm_at(p.sh[l], p.ch, nxt, 0, 0), (size_t)p.ch * kChunkBytes);
             }
             for (int l = last; l >= 1; --l) {
@@ -372,6 +375,20 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_bwd_tc_kernel(const __gr
             }
             if (want_dx) {
                 es.wait_acc();
+                if (p.tile_wait) {  // the previous head's rows of this tile (we accumulate into them)
+                    if ((threadIdx.x & 31) == 0) {
+                        unsigned spins = 0;
+                        int v;
+                        do {
+                            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p.tile_wait + tile) : "memory");
+                            if (v == 0) {
+                                __nanosleep(100);
+                                if (++spins > (1u << 24)) __trap();  // ~ seconds: the producer is not running
+                            }
+                        } while (v == 0);
+                    }
+                    __syncwarp();
+                }
                 // accumulator columns: [x0: c0 chunks][x1: c1 chunks] (the dX weight image is laid out per segment)
                 for (int c = grp; c < p.c0 + p.c1; c += kEpiGroups) {
                     float v[8];
@@ -380,6 +397,22 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_bwd_tc_kernel(const __gr
                     if (!live) continue;
                     if (c < p.c0) { if (p.dx0) stg_row8(p.dx0 + (size_t)grow * p.ld0, c * 8, p.k0, v, p.accumulate_dx != 0); }
                     else if (p.dx1) stg_row8(p.dx1 + (size_t)grow * p.ld1, (c - p.c0) * 8, p.k1, v, p.accumulate_dx != 0);
+                }
+                if (p.tile_done || p.step_rows_done) {
+                    __threadfence();  // this thread's dx stores before the signal
+                    named_bar<kEpiThreads, 1>();
+                    if (threadIdx.x == 0) {
+                        if (p.tile_done) atomicExch(p.tile_done + tile, 1);
+                        if (p.step_rows_done) {
+                            const int r_end = min(p.M, row0 + kTileRows);
+                            for (int r = row0; r < r_end;) {
+                                const int s_ = min(r / p.step_rows, p.step_count - 1);
+                                const int e = s_ == p.step_count - 1 ? r_end : min(r_end, (s_ + 1) * p.step_rows);
+                                atomicAdd(p.step_rows_done + s_, e - r);
+                                r = e;
+                            }
+                        }
+                    }
                 }
             }
         }
@@ -602,6 +635,10 @@ int mlp_tc_bwd(const drm_mlp_bwd_call* bc, cudaStream_t stream) {
     d.wstream = ws;
     carve_save(c, pl, d);
     d.dy = bc->dy; d.dy_scale = bc->dy_scale; d.dx0 = bc->dx0; d.dx1 = bc->dx1; d.accumulate_dx = bc->accumulate_dx;
+    d.reverse_tiles = bc->reverse_tiles; d.tile_done = bc->tile_done; d.tile_wait = bc->tile_wait;
+    d.step_rows_done = bc->step_rows_done; d.step_rows = bc->step_rows; d.step_count = bc->step_count;
+    DRM_REQUIRE(!d.step_rows_done || (d.step_rows > 0 && d.step_count > 0), DRM_E_ARG, "step_rows_done needs step_rows / step_count");
+    DRM_REQUIRE(!(d.tile_done || d.tile_wait || d.step_rows_done) || want_dx, DRM_E_ARG, "hand-over counters need dx0 / dx1");
     if (bc->want_wgrad) {
         d.db_last = bc->grad.db[last];
         uint8_t* s = ws + rup_sz(pl.wbytes, 256);
@@ -624,7 +661,8 @@ int mlp_tc_bwd(const drm_mlp_bwd_call* bc, cudaStream_t stream) {
         if (bc->phase == DRM_PHASE_PREPARE) return DRM_OK;
     }
     {
-        const int grid = pl.tiles < kNumSM ? pl.tiles : kNumSM;
+        int grid = pl.tiles < kNumSM ? pl.tiles : kNumSM;
+        if (c->max_ctas > 0 && c->max_ctas < grid) grid = c->max_ctas;
         DRM_CUDA_OK(cudaFuncSetAttribute(mlp_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
         ProfScope prof(PROF_MLP_BWD, stream);
         mlp_bwd_tc_kernel<<<grid, kChainThreads, pl.smem_bytes, stream>>>(d);

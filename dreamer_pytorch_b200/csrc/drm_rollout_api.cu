@@ -253,6 +253,7 @@ int drm_rollout_bwd(const drm_rollout* r, const drm_rollout_grad* g, void* strea
     DRM_REQUIRE(g->phase >= DRM_PHASE_ALL && g->phase <= DRM_PHASE_RUN, DRM_E_ARG, "bad phase");
     if (use_tc(r)) return tc::rollout_tc_bwd(r, g, stream);
     if (g->phase == DRM_PHASE_PREPARE) return DRM_OK;  // fp32: everything happens in RUN
+    DRM_REQUIRE(!g->g_wait_flags, DRM_E_ARG, "g_wait_flags is honoured by the bf16 policy rollout only");
     RollDev p{}; dims(r, p);
     const drm_rssm& w = r->rssm;
     const int A = w.A, S = w.S, D = w.D, Hd = w.Hd, T = r->steps, n = r->n;

@@ -51,6 +51,7 @@ struct RollTcDev {
     uint32_t st_off, hb_off, bias_off;
     // backward
     const float *g_prior_mean, *g_prior_std, *g_prior_stoch, *g_deter, *g_action_out;
+    const int* g_wait_flags; int g_wait_target;  // optional: g_* rows of step t exist once g_wait_flags[t] >= g_wait_target
     __nv_bfloat16* dys_a[DRM_MAX_LINEAR];   // dY of every actor Linear, TCM by tile-step (cha chunks; 2 for the last)
     __nv_bfloat16* stash;                   // per-CTA scratch: [grid][2][cdp chunks] (d i_n, d h_n between two phases)
     float* db_a_last;                       // fp32 bias gradient of the actor's last Linear
@@ -578,6 +579,20 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
             const int rows_live = min(kTileRows, p.n - row0);
             // asynchronous, coalesced fetch of step t2's prior-head blocks into the staging area
             auto fetch_prior = [&](int t2) {
+                if (p.g_wait_flags) {  // the head kernels producing g_* run beside this one (drm_rollout_grad.g_wait_flags)
+                    if (lane == 0) {
+                        unsigned spins = 0;
+                        int v;
+                        do {
+                            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p.g_wait_flags + t2) : "memory");
+                            if (v < p.g_wait_target) {
+                                __nanosleep(100);
+                                if (++spins > (1u << 24)) __trap();  // ~ seconds: the producer is not running
+                            }
+                        } while (v < p.g_wait_target);
+                    }
+                    __syncwarp();
+                }
                 const size_t o0 = ((size_t)t2 * p.n + row0) * S;
                 for (int i = tid; i < rows_live * S; i += kEpiThreads) {
                     cp_async4(sEps + i, p.eps_prior + o0 + i);
@@ -1218,6 +1233,7 @@ int rollout_tc_bwd(const drm_rollout* r, const drm_rollout_grad* g, cudaStream_t
     d.wstream = ws;
     d.g_prior_mean = g->g_prior_mean; d.g_prior_std = g->g_prior_std; d.g_prior_stoch = g->g_prior_stoch;
     d.g_deter = g->g_deter; d.g_action_out = g->g_action_out;
+    d.g_wait_flags = g->g_wait_flags; d.g_wait_target = g->g_wait_target;
     if (want_actor) {
         for (int l = 0; l < a.n_linear; ++l) {
             const int nout = l == a.n_linear - 1 ? a.out_dim : a.hidden;

@@ -183,6 +183,7 @@ void wgrad_tc_plan(WgParams& w) {
     }
     // row-tile splits: at most two CTAs per SM in total (one wave of co-resident pairs with 64-row tiles, two full waves
     // with 128-row tiles -- never a third, nearly empty one), but keep >= 4 row tiles per CTA
+    // (measured at 2 500 x 15: flat between one and two CTAs per SM, slower outside)
     int splits = base > 0 ? (2 * kNumSM) / base : 1;
     const int max_splits = (w.row_tiles + 3) / 4;
     if (splits > max_splits) splits = max_splits;

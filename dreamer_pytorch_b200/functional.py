@@ -162,7 +162,7 @@ def rollout_forward_raw(cfg: RolloutCfg, t: dict, rssm, actor, training: bool, s
 
 
 def rollout_backward_raw(cfg: RolloutCfg, t: dict, rssm, actor, save, gouts: dict, want_inputs=(False,) * 4,
-                         want_rssm=False, want_actor=False, phase: int = 0, plan: Optional[dict] = None):
+                         want_rssm=False, want_actor=False, phase: int = 0, plan: Optional[dict] = None, g_wait=None):
     """Runs drm_rollout_bwd.  gouts: name ('g_prior_mean', ...) -> tensor or None.
     want_inputs: (start_stoch, start_deter, action_in, obs_embed).
     Returns (input grads [4], rssm grads list or None, actor grads list or None).
@@ -215,6 +215,8 @@ def rollout_backward_raw(cfg: RolloutCfg, t: dict, rssm, actor, save, gouts: dic
         keep.append(x)
         setattr(g, k, _lib.ptr(x))
     g.phase = phase
+    if g_wait is not None:  # (int32 counters [steps], target): upstream gradients produced beside this kernel
+        g.g_wait_flags, g.g_wait_target = g_wait[0].data_ptr(), int(g_wait[1])
     _lib.check(lib.drm_rollout_bwd(C.byref(r), C.byref(g), _stream()), "drm_rollout_bwd")
     _count()
     return din, grssm, gactor
@@ -318,9 +320,11 @@ def mlp_forward_raw(x0, x1, weights, training, precision=None, wait=None, max_ct
 
 
 def mlp_backward_raw(x0, x1, weights, save, dy, dy_scale=None, dx0=None, dx1=None, accumulate_dx=False,
-                     want_wgrad=False, precision="fp32", phase: int = 0, plan: Optional[dict] = None):
+                     want_wgrad=False, precision="fp32", phase: int = 0, plan: Optional[dict] = None, gate: Optional[dict] = None):
     """Runs drm_mlp_bwd; returns the list of weight grads [dW0, db0, dW1, ...] (or None).
-    phase / plan: as in rollout_backward_raw (dy / dx may be None in the PHASE_PREPARE call)."""
+    phase / plan: as in rollout_backward_raw (dy / dx may be None in the PHASE_PREPARE call).
+    gate: hand-over between kernels on different streams (drm_mlp_bwd_call): dict(max_ctas=, reverse=, tile_done=,
+    tile_wait=, step_done=(counters, rows_per_step, steps))."""
     lib = _lib.load()
     M = x0.shape[0]
     if plan is not None and "b" in plan:
@@ -353,6 +357,14 @@ def mlp_backward_raw(x0, x1, weights, save, dy, dy_scale=None, dx0=None, dx1=Non
     b.dx1 = _lib.ptr(dx1)
     b.accumulate_dx = 1 if accumulate_dx else 0
     b.phase = phase
+    if gate:
+        b.fwd.max_ctas = int(gate.get("max_ctas", 0))
+        b.reverse_tiles = 1 if gate.get("reverse") else 0
+        b.tile_done = gate["tile_done"].data_ptr() if gate.get("tile_done") is not None else None
+        b.tile_wait = gate["tile_wait"].data_ptr() if gate.get("tile_wait") is not None else None
+        if gate.get("step_done") is not None:
+            cnt, rows, steps = gate["step_done"]
+            b.step_rows_done, b.step_rows, b.step_count = cnt.data_ptr(), int(rows), int(steps)
     _lib.check(lib.drm_mlp_bwd(C.byref(b), _stream()), "drm_mlp_bwd")
     _count()
     return grads

@@ -159,7 +159,10 @@ typedef struct drm_rollout_grad {
     int32_t want_actor_grad;
     drm_mlp_grad actor;
     int32_t phase;   /* DRM_PHASE_*: lets the weight packing + zero-filling of the sinks be issued early (another stream) */
-    int32_t pad_;
+    /* bf16 POLICY path, optional: g_* rows of step t are read only once g_wait_flags[t] >= g_wait_target (the
+     * step_rows_done counters of the head kernels producing them on other streams, target = n). */
+    int32_t g_wait_target;
+    const int32_t* g_wait_flags;
 } drm_rollout_grad;
 
 /* Batched MLP over M rows; the input is the concatenation of two column segments
@@ -191,7 +194,19 @@ typedef struct drm_mlp_bwd_call {
     int32_t want_wgrad;
     drm_mlp_grad grad;
     int32_t phase;   /* DRM_PHASE_* */
-    int32_t pad_;
+    /* Kernels running beside each other (bf16 path only; all optional).  The data-gradient kernels of several heads that
+     * accumulate into the same dx, and the reverse-time rollout that consumes dx step by step, can be launched on
+     * different streams and hand rows over through device counters instead of stream order:
+     *   reverse_tiles   process the 128-row tiles from the last to the first (the rollout backward wants step T-1 first)
+     *   tile_done[i]    set to 1 once rows [128 i, 128 i + 128) of dx are final for this call            (zeroed by the caller)
+     *   tile_wait[i]    spin until non-zero before touching those dx rows (the previous head's tile_done)
+     *   step_rows_done  [step_count] counters, += rows of step s (s = row / step_rows) finished            (zeroed by the caller)
+     * fwd.max_ctas bounds the grid; the caller must keep all gated kernels resident together. */
+    int32_t reverse_tiles;
+    int32_t* tile_done;
+    const int32_t* tile_wait;
+    int32_t* step_rows_done;
+    int32_t step_rows, step_count;
 } drm_mlp_bwd_call;
 
 /* lambda-returns + actor loss + value loss over imagined heads, forward AND the gradients of
