@@ -66,7 +66,8 @@ class drm_rollout_grad(C.Structure):
                           "g_post_stoch", "g_action_out", "d_start_stoch", "d_start_deter", "d_action_in",
                           "d_obs_embed")]
         + [("rssm", drm_rssm_grad), ("want_rssm_grad", C.c_int32), ("want_actor_grad", C.c_int32),
-           ("actor", drm_mlp_grad), ("phase", C.c_int32), ("g_wait_target", C.c_int32), ("g_wait_flags", P)]
+           ("actor", drm_mlp_grad), ("phase", C.c_int32), ("g_wait_target", C.c_int32), ("g_wait_flags", P),
+           ("wgrad_stream", P)]
     )
 
 

@@ -75,9 +75,10 @@ class _ActorLossFn(torch.autograd.Function):
         if prec == "bf16" and (_PIPELINE_HEADS or _PREPARE_BACKWARD):
             fork = torch.cuda.Event()
             fork.record(torch.cuda.current_stream())  # the side streams branch off BEFORE the rollout is enqueued
+        if prec == "bf16":
+            tiles = []
         if prec == "bf16" and _PIPELINE_HEADS:
             flags = torch.zeros(H, dtype=torch.int32, device=stoch_dev(t))
-            tiles = []
         save = rollout_forward_raw(cfg, t, rssm, actor, training, step_flags=flags, tiles_out=tiles)
         x0 = t["prior_stoch"].view(H * N, S)
         x1 = t["deter"].view(H * N, D)
@@ -188,17 +189,11 @@ class _ActorLossFn(torch.autograd.Function):
         # The reverse-time rollout kernel occupies one SM per 64 (or 128) start states; the value loss' weight-gradient
         # pass (dreamer_algo.py:331-337) depends on nothing computed here, so it runs beside it on a side stream and
         # _ValueLossFn.backward only has to scale the result (it recomputes if this backward never ran).
-        side = None
+        side = _side_stream(g_loss.device)
+        side.wait_stream(main)
+        for hs in joins:  # not critical: starts once the head kernels have left, so that the rollout is never kept waiting
+            side.wait_stream(hs)
         if shared is not None and not shared.get("value_done") and "value_grads" not in shared:
-            side = _side_stream(g_loss.device)
-            side.wait_stream(main)
-            for hs in joins:  # not critical: starts once the head kernels have left, so that the rollout is never kept waiting
-                side.wait_stream(hs)
-        _, _, gactor = rollout_backward_raw(cfg, t, rssm, actor, save, dict(g_prior_stoch=g_stoch, g_deter=g_deter),
-                                            want_actor=True, phase=ph, plan=proll, g_wait=g_wait)
-        for hs in joins:
-            main.wait_stream(hs)
-        if side is not None:
             with torch.cuda.stream(side):
                 vg = mlp_backward_raw(x0, x1, value_w, vsave, out["d_value_pred"].view(H * N, 1), None, None, None, False,
                                       True, prec, ph, pvw)
@@ -207,6 +202,14 @@ class _ActorLossFn(torch.autograd.Function):
             for g in vg:
                 g.record_stream(main)
             shared["value_grads"] = (vg, ev)
+        # the actor's weight-gradient GEMMs follow the rollout step by step on the side stream (behind the value pass)
+        follow = side if (g_wait is not None and plans is not None) else None
+        _, _, gactor = rollout_backward_raw(cfg, t, rssm, actor, save, dict(g_prior_stoch=g_stoch, g_deter=g_deter),
+                                            want_actor=True, phase=ph, plan=proll, g_wait=g_wait, wgrad_stream=follow)
+        for hs in joins:
+            main.wait_stream(hs)
+        if follow is not None:
+            main.wait_stream(side)
         return (None, *gactor)
 
 

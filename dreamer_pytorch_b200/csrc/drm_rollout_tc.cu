@@ -51,6 +51,7 @@ struct RollTcDev {
     uint32_t st_off, hb_off, bias_off;
     // backward
     const float *g_prior_mean, *g_prior_std, *g_prior_stoch, *g_deter, *g_action_out;
+    int* bwd_flags;                         // optional: += 1 per row tile once the dY images of step t are in global memory
     const int* g_wait_flags; int g_wait_target;  // optional: g_* rows of step t exist once g_wait_flags[t] >= g_wait_target
     __nv_bfloat16* dys_a[DRM_MAX_LINEAR];   // dY of every actor Linear, TCM by tile-step (cha chunks; 2 for the last)
     __nv_bfloat16* stash;                   // per-CTA scratch: [grid][2][cdp chunks] (d i_n, d h_n between two phases)
@@ -632,7 +633,9 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                 const size_t trow = (size_t)t * p.n + grow;
                 // ------------------------------------------------------------ prior head (pointwise) -> G2
                 cp_async_wait_all();
+                if (p.bwd_flags) __threadfence();  // this thread's dY image stores of step t + 1 before the signal below
                 named_bar<kEpiThreads, 1>();
+                if (p.bwd_flags && tid == 0 && t + 1 < p.T) atomicAdd(p.bwd_flags + t + 1, 1);
                 pf_gru(t);
                 {
                     const int per = (p.cs + kEpiGroups - 1) / kEpiGroups;
@@ -871,6 +874,11 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                 }
             }
             // the next tile's zero-fill of R_C / R_AS and its first release() come after these loads
+            if (p.bwd_flags) {
+                __threadfence();
+                named_bar<kEpiThreads, 1>();
+                if (tid == 0) atomicAdd(p.bwd_flags, 1);
+            }
         }
     }
     chain_teardown(tmem_base);
@@ -1197,6 +1205,7 @@ static size_t carve_bwd_ws(const RollTcDev& dd, size_t wbytes, uint8_t* base, Ro
     for (int l = 0; l < dd.an; ++l) tmp.dys_a[l] = (__nv_bfloat16*)take(tcm_bytes_r(dd.tr, TS, l == dd.an - 1 ? 2 : dd.cha));
     const int grid = dd.ntiles < kNumSM ? dd.ntiles : kNumSM;
     tmp.stash = (__nv_bfloat16*)take((size_t)grid * 2 * dd.cdp * (dd.tr * 16));
+    tmp.bwd_flags = (int*)take(sizeof(int) * dd.T);
     if (out) *out = tmp;
     return off;
 }
@@ -1244,6 +1253,16 @@ int rollout_tc_bwd(const drm_rollout* r, const drm_rollout_grad* g, cudaStream_t
         }
         d.db_a_last = g->actor.db[a.n_linear - 1];
     }
+    // The weight-gradient GEMMs can follow the rollout step by step on another stream (per-step counters) instead of
+    // starting when it has finished.  Only after a PREPARE call: the counters are zeroed there.
+    cudaStream_t wg_stream = stream;
+    int* flags = d.bwd_flags;
+    d.bwd_flags = nullptr;
+    if (want_actor) pl.jobs.zero(reinterpret_cast<float*>(flags), (size_t)d.T);
+    if (want_actor && g->wgrad_stream && g->phase == DRM_PHASE_RUN && d.ntiles + 16 <= kNumSM) {  // both grids resident
+        wg_stream = (cudaStream_t)g->wgrad_stream;
+        d.bwd_flags = flags;
+    }
     if (g->phase != DRM_PHASE_RUN) {
         rc = launch_pack_tc(pl.jobs, stream); if (rc) return rc;
         if (g->phase == DRM_PHASE_PREPARE) return DRM_OK;
@@ -1282,8 +1301,15 @@ int rollout_tc_bwd(const drm_rollout* r, const drm_rollout_grad* g, cudaStream_t
             L.dW = g->actor.dW[l];
             L.db = l == last ? nullptr : g->actor.db[l];
         }
-        wgrad_tc_plan(wg);
-        rc = launch_wgrad_tc(wg, stream); if (rc) return rc;
+        int slots = 0;
+        if (d.bwd_flags) {
+            // row tiles in reverse time order, each gated by its step's counter; the grid must be resident BESIDE the rollout
+            wg.wait_flags = d.bwd_flags; wg.wait_target = d.ntiles;
+            wg.tiles_per_step = d.ntiles; wg.reverse = 1;
+            slots = (kNumSM - d.ntiles) * (d.tr == 64 ? 2 : 1);
+        }
+        wgrad_tc_plan(wg, slots);
+        rc = launch_wgrad_tc(wg, wg_stream); if (rc) return rc;
     }
     return DRM_OK;
 }

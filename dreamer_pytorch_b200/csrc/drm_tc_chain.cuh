@@ -444,10 +444,13 @@ constexpr int kMaxWgLayers = 10;
 struct WgParams {
     int n_layers, row_tiles, total_ctas;
     int tile_rows;  // rows per TCM tile of the images (0 = 128)
+    // optional producer gating: row tile i belongs to step i / tiles_per_step and exists once wait_flags[step] >= wait_target;
+    // reverse = the producer runs from the last step to the first
+    const int* wait_flags; int wait_target, tiles_per_step, reverse;
     WgLayer L[kMaxWgLayers];
 };
-// fills n_tiles_n / parts / splits / cta0 / total_ctas from the rest
-void wgrad_tc_plan(WgParams& w);
+// fills n_tiles_n / parts / splits / cta0 / total_ctas from the rest; slots > 0 bounds the grid (CTAs resident at once)
+void wgrad_tc_plan(WgParams& w, int slots = 0);
 int launch_wgrad_tc(const WgParams& w, cudaStream_t stream);
 
 // ---------------------------------------------------------------------------------------------- weight images

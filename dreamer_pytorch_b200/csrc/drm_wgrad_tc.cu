@@ -99,7 +99,21 @@ __global__ void __launch_bounds__(kWgThreads, 2) wgrad_tc_kernel(const __grid_co
             if (s1e > s1b) bytes += (uint32_t)(s1e - s1b) * cb;
             int stage = 0; uint32_t phase = 0;
             for (int it = 0; it < my_tiles; ++it) {
-                const int tile = split + it * L.splits;
+                const int tile_i = split + it * L.splits;
+                const int tile = w.reverse ? w.row_tiles - 1 - tile_i : tile_i;
+                if (w.wait_flags) {  // the producer of the images runs beside this kernel
+                    const int* f = w.wait_flags + tile / w.tiles_per_step;
+                    unsigned spins = 0;
+                    int v;
+                    do {
+                        asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+                        if (v < w.wait_target) {
+                            __nanosleep(200);
+                            if (++spins > (1u << 24)) __trap();  // ~ seconds: the producer is not running
+                        }
+                    } while (v < w.wait_target);
+                    asm volatile("fence.proxy.async;" ::: "memory");  // generic-proxy writes of the producer -> bulk copies
+                }
                 uint8_t* A = smem + 1024 + stage * stage_bytes;
                 uint8_t* B = A + a_bytes;
                 mbar_wait(&bars->empty[stage], phase ^ 1);
@@ -171,7 +185,7 @@ __global__ void __launch_bounds__(kWgThreads, 2) wgrad_tc_kernel(const __grid_co
     if (warp == 4) tmem_dealloc(tmem_base, kWgTmemCols);
 }
 
-void wgrad_tc_plan(WgParams& w) {
+void wgrad_tc_plan(WgParams& w, int slots) {
     int base = 0;
     for (int i = 0; i < w.n_layers; ++i) {
         WgLayer& L = w.L[i];
@@ -184,7 +198,8 @@ void wgrad_tc_plan(WgParams& w) {
     // row-tile splits: at most two CTAs per SM in total (one wave of co-resident pairs with 64-row tiles, two full waves
     // with 128-row tiles -- never a third, nearly empty one), but keep >= 4 row tiles per CTA
     // (measured at 2 500 x 15: flat between one and two CTAs per SM, slower outside)
-    int splits = base > 0 ? (2 * kNumSM) / base : 1;
+    if (slots <= 0) slots = 2 * kNumSM;
+    int splits = base > 0 ? slots / base : 1;
     const int max_splits = (w.row_tiles + 3) / 4;
     if (splits > max_splits) splits = max_splits;
     if (splits < 1) splits = 1;

@@ -154,15 +154,16 @@ def rollout_forward_raw(cfg: RolloutCfg, t: dict, rssm, actor, training: bool, s
     if step_flags is not None:
         # per-step completion counters for a consumer running beside the rollout (drm_rollout.step_flags)
         r.step_flags = step_flags.data_ptr()
-        if tiles_out is not None:
-            tiles_out.append(int(lib.drm_rollout_tiles(C.byref(r))))
+    if tiles_out is not None:  # SMs the rollout kernels of this call occupy (0: fp32 kernels, no gating)
+        tiles_out.append(int(lib.drm_rollout_tiles(C.byref(r))))
     _lib.check(lib.drm_rollout_fwd(C.byref(r), _stream()), "drm_rollout_fwd")
     _count()
     return save
 
 
 def rollout_backward_raw(cfg: RolloutCfg, t: dict, rssm, actor, save, gouts: dict, want_inputs=(False,) * 4,
-                         want_rssm=False, want_actor=False, phase: int = 0, plan: Optional[dict] = None, g_wait=None):
+                         want_rssm=False, want_actor=False, phase: int = 0, plan: Optional[dict] = None, g_wait=None,
+                         wgrad_stream=None):
     """Runs drm_rollout_bwd.  gouts: name ('g_prior_mean', ...) -> tensor or None.
     want_inputs: (start_stoch, start_deter, action_in, obs_embed).
     Returns (input grads [4], rssm grads list or None, actor grads list or None).
@@ -217,6 +218,8 @@ def rollout_backward_raw(cfg: RolloutCfg, t: dict, rssm, actor, save, gouts: dic
     g.phase = phase
     if g_wait is not None:  # (int32 counters [steps], target): upstream gradients produced beside this kernel
         g.g_wait_flags, g.g_wait_target = g_wait[0].data_ptr(), int(g_wait[1])
+    if wgrad_stream is not None:  # actor weight-gradient GEMMs step by step behind the rollout (drm_rollout_grad.wgrad_stream)
+        g.wgrad_stream = wgrad_stream.cuda_stream
     _lib.check(lib.drm_rollout_bwd(C.byref(r), C.byref(g), _stream()), "drm_rollout_bwd")
     _count()
     return din, grssm, gactor

@@ -163,6 +163,11 @@ typedef struct drm_rollout_grad {
      * step_rows_done counters of the head kernels producing them on other streams, target = n). */
     int32_t g_wait_target;
     const int32_t* g_wait_flags;
+    /* bf16 POLICY path, phase RUN only, optional: a second CUDA stream for the actor weight-gradient GEMMs.  They then follow
+     * the rollout step by step (device counters in the workspace) instead of starting when it has finished.  The caller
+     * orders that stream after the PREPARE call, keeps the SMs the rollout does not use free for it (anything else queued on
+     * it runs first), and joins it afterwards. */
+    void* wgrad_stream;
 } drm_rollout_grad;
 
 /* Batched MLP over M rows; the input is the concatenation of two column segments

@@ -51,9 +51,12 @@ def test_graph_step_matches_eager(prec):
         assert rel_err(p.grad, r) < 1e-4, (p.shape, rel_err(p.grad, r))  # fp32 atomics reorder between runs
 
 
-def test_heads_beside_the_rollout_match_stream_order():
-    """The head MLPs gated by the rollout's per-step completion counters (side streams, capped grids) must give the
-    results of the plain stream-ordered launch sequence: same kernels, same data, only the schedule differs."""
+@pytest.mark.parametrize("use_pcont", [False, True])
+def test_kernels_beside_each_other_match_stream_order(use_pcont):
+    """Forward: head MLPs gated by the rollout's per-step completion counters.  Backward: weight packing issued beside the
+    forward pass, head data-gradient kernels beside the reverse-time rollout (tile hand-over between heads, per-step row
+    counters towards the rollout).  All on side streams with capped grids; they must give the results of the plain
+    stream-ordered launch sequence: same kernels, same data, only the schedule differs."""
     from dreamer_pytorch_b200 import algo, noise
     from dreamer_pytorch_b200.dropin.agent import AtariDreamerModel
     from dreamer_pytorch_b200.dropin.rnns import RSSMState
@@ -62,7 +65,7 @@ def test_heads_beside_the_rollout_match_stream_order():
     dev = torch.device("cuda:0")
     torch.manual_seed(3)
     A, N, H = 6, 1000, 15
-    model = AtariDreamerModel(action_shape=(A,), action_dist="tanh_normal").to(dev).train()
+    model = AtariDreamerModel(action_shape=(A,), action_dist="tanh_normal", use_pcont=use_pcont).to(dev).train()
     g = torch.Generator().manual_seed(4)
     stoch = torch.randn(N, 30, generator=g).to(dev)
     deter = torch.tanh(torch.randn(N, 200, generator=g)).to(dev)
@@ -70,22 +73,29 @@ def test_heads_beside_the_rollout_match_stream_order():
     nza = torch.randn(H, N, A, generator=g).to(dev)
     params = list(model.action_decoder.parameters()) + list(model.value_model.parameters())
     res = {}
-    old = algo._PIPELINE_HEADS
+    flags = ("_PIPELINE_HEADS", "_PREPARE_BACKWARD", "_PIPELINE_BACKWARD")
+    old = {k: getattr(algo, k) for k in flags}
     try:
-        for mode in (True, False):
-            algo._PIPELINE_HEADS = mode
+        # everything beside everything / plain stream order / each mechanism alone
+        for mode in ((True, True, True), (False, False, False), (True, False, False), (False, True, False),
+                     (False, False, True)):
+            for k, v in zip(flags, mode):
+                setattr(algo, k, v)
             for p in params:
                 p.grad = None
             with precision("bf16"), noise.injected(eps_prior=[eps], noise_act=[nza]):
-                al, vl, info = algo.imagination_losses(model, RSSMState(stoch, stoch, stoch, deter), H)
+                al, vl, info = algo.imagination_losses(model, RSSMState(stoch, stoch, stoch, deter), H,
+                                                       use_pcont=use_pcont)
                 al.backward(); vl.backward()
             torch.cuda.synchronize()
             res[mode] = (al.detach().clone(), vl.detach().clone(), info.reward.clone(), info.value.clone(),
                          [p.grad.clone() for p in params])
     finally:
-        algo._PIPELINE_HEADS = old
-    a, b = res[True], res[False]
-    assert torch.equal(a[2], b[2]) and torch.equal(a[3], b[3])          # head outputs: bit-identical
-    assert rel_err(a[0], b[0]) < 1e-6 and rel_err(a[1], b[1]) < 1e-6
-    for ga, gb in zip(a[4], b[4]):
-        assert rel_err(ga, gb) < 1e-4                                     # fp32 atomics reorder between runs
+        for k, v in old.items():
+            setattr(algo, k, v)
+    b = res[(False, False, False)]
+    for mode, a in res.items():
+        assert torch.equal(a[2], b[2]) and torch.equal(a[3], b[3]), mode      # head outputs: bit-identical
+        assert rel_err(a[0], b[0]) < 1e-6 and rel_err(a[1], b[1]) < 1e-6, mode
+        for ga, gb in zip(a[4], b[4]):
+            assert rel_err(ga, gb) < 1e-4, mode                                 # fp32 atomics reorder between runs
