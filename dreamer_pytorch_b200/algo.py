@@ -27,9 +27,26 @@ from .functional import (KLFn, RolloutCfg, _f32c, mlp_backward_raw, mlp_forward_
 _SIDE = {}
 
 
-_PIPELINE_HEADS = True  # heads beside the rollout when SMs are idle (see _ActorLossFn.forward)
-_PREPARE_BACKWARD = True  # weight packing / zero-filled sinks of the backward pass issued beside the forward pass
-_PIPELINE_BACKWARD = True  # head data-gradient kernels beside the reverse-time rollout (see _ActorLossFn.backward)
+# Scheduling switches (results do not depend on them, tests/test_graph_gpu.py).  DRM_B200_SCHEDULE=plain in the environment
+# turns all of them off: every kernel in stream order; a comma-separated subset of "heads,prepare,backward" keeps those.
+import os as _os
+
+_sched = _os.environ.get("DRM_B200_SCHEDULE", "heads,prepare,backward").split(",")
+_PIPELINE_HEADS = "heads" in _sched  # heads beside the rollout when SMs are idle (see _ActorLossFn.forward)
+_PREPARE_BACKWARD = "prepare" in _sched  # weight packing / zero-filled sinks of the backward pass beside the forward pass
+_PIPELINE_BACKWARD = "backward" in _sched  # head data-gradient kernels beside the reverse-time rollout (_ActorLossFn.backward)
+_FOLLOW_WGRAD = "nofollow" not in _sched  # actor weight gradients step by step behind the rollout backward
+
+
+# CUDA loads a kernel on its first launch (lazy module loading), and that load may have to wait for the device to go idle.
+# A kernel that spins on counters must therefore never be on the device while one of its producers is launched for the
+# first time: the first full forward + backward pass on a device runs in plain stream order (it loads every kernel of the
+# step), the overlapped schedule starts with the second.
+_WARM = {}
+
+
+def _overlap_ok(device, prec) -> bool:
+    return _WARM.get((device.type, device.index, prec), 0) >= 1
 
 
 def _side_stream(device, k: int = 0) -> "torch.cuda.Stream":
@@ -72,12 +89,14 @@ class _ActorLossFn(torch.autograd.Function):
         # step t overlap the rollout of step t+1 (drm_rollout.step_flags / drm_mlp_call.wait_flags).
         ctx.set_materialize_grads(False)  # 12 by-products: no zero tensors for their (unused) gradients
         flags = tiles = fork = None
-        if prec == "bf16" and (_PIPELINE_HEADS or _PREPARE_BACKWARD):
+        warm = _overlap_ok(stoch_dev(t), prec)
+        pipe_heads, prepare = _PIPELINE_HEADS and warm, _PREPARE_BACKWARD and warm
+        if prec == "bf16" and (pipe_heads or prepare):
             fork = torch.cuda.Event()
             fork.record(torch.cuda.current_stream())  # the side streams branch off BEFORE the rollout is enqueued
         if prec == "bf16":
             tiles = []
-        if prec == "bf16" and _PIPELINE_HEADS:
+        if prec == "bf16" and pipe_heads:
             flags = torch.zeros(H, dtype=torch.int32, device=stoch_dev(t))
         save = rollout_forward_raw(cfg, t, rssm, actor, training, step_flags=flags, tiles_out=tiles)
         x0 = t["prior_stoch"].view(H * N, S)
@@ -106,7 +125,7 @@ class _ActorLossFn(torch.autograd.Function):
         # sinks.  None of that depends on the forward results, so it is issued now, on its own stream, beside the rollout
         # (DRM_PHASE_PREPARE); backward() then only launches the compute kernels (DRM_PHASE_RUN).
         plans = None
-        if training and fork is not None and _PREPARE_BACKWARD:
+        if training and fork is not None and prepare:
             main = torch.cuda.current_stream()
             prep = _side_stream(x0.device, 0)
             prep.wait_event(fork)
@@ -166,7 +185,7 @@ class _ActorLossFn(torch.autograd.Function):
         # rollout kernel waits on (step_rows_done / g_wait_flags).  Grids are capped so that all of them are resident.
         free = (_sm_count(g_loss.device) - roll_tiles) // len(heads) if roll_tiles > 0 else 0
         g_wait = None
-        if prec == "bf16" and _PIPELINE_BACKWARD and free >= 16:
+        if prec == "bf16" and _PIPELINE_BACKWARD and free >= 16 and _overlap_ok(g_loss.device, prec):
             mlp_tiles = (H * N + 127) // 128
             cnt = torch.zeros(len(heads) * mlp_tiles + H, dtype=torch.int32, device=g_loss.device)
             steps_done = cnt[len(heads) * mlp_tiles:]
@@ -203,13 +222,15 @@ class _ActorLossFn(torch.autograd.Function):
                 g.record_stream(main)
             shared["value_grads"] = (vg, ev)
         # the actor's weight-gradient GEMMs follow the rollout step by step on the side stream (behind the value pass)
-        follow = side if (g_wait is not None and plans is not None) else None
+        follow = side if (g_wait is not None and plans is not None and _FOLLOW_WGRAD) else None
         _, _, gactor = rollout_backward_raw(cfg, t, rssm, actor, save, dict(g_prior_stoch=g_stoch, g_deter=g_deter),
                                             want_actor=True, phase=ph, plan=proll, g_wait=g_wait, wgrad_stream=follow)
         for hs in joins:
             main.wait_stream(hs)
         if follow is not None:
             main.wait_stream(side)
+        key = (g_loss.device.type, g_loss.device.index, prec)
+        _WARM[key] = _WARM.get(key, 0) + 1
         return (None, *gactor)
 
 
