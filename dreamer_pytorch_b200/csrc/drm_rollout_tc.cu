@@ -1259,7 +1259,10 @@ int rollout_tc_bwd(const drm_rollout* r, const drm_rollout_grad* g, cudaStream_t
     int* flags = d.bwd_flags;
     d.bwd_flags = nullptr;
     if (want_actor) pl.jobs.zero(reinterpret_cast<float*>(flags), (size_t)d.T);
-    if (want_actor && g->wgrad_stream && g->phase == DRM_PHASE_RUN && d.ntiles + 16 <= kNumSM) {  // both grids resident
+    // Both grids must be resident, and a waiting weight-gradient CTA (64-row images: 49 KB, 256 TMEM columns) must never share
+    // an SM with a rollout CTA, whose TMEM allocation it could block: the rollout's shared memory has to exclude that.
+    const bool excl = pl.smem_bytes + 50 * 1024 > (size_t)kMaxSmem;
+    if (want_actor && g->wgrad_stream && g->phase == DRM_PHASE_RUN && d.ntiles + 16 <= kNumSM && excl) {
         wg_stream = (cudaStream_t)g->wgrad_stream;
         d.bwd_flags = flags;
     }
