@@ -101,6 +101,7 @@ class drm_kl_call(C.Structure):
 class drm_clip_adam_call(C.Structure):
     _fields_ = ([("n_tensors", C.c_int32), ("pad_", C.c_int32)]
                 + [(k, C.c_float) for k in ("max_norm", "beta1", "beta2", "eps", "one_minus_beta1", "one_minus_beta2", "step_size", "bias2_sqrt")]
+                + [("lr", C.c_float), ("pad2_", C.c_int32), ("beta1_d", C.c_double), ("beta2_d", C.c_double), ("step_dev", P)]
                 + [(k, P * 64) for k in ("param", "grad", "exp_avg", "exp_avg_sq")]
                 + [("numel", C.c_int64 * 64), ("norm_out", P), ("workspace", P), ("workspace_bytes", C.c_size_t)])
 

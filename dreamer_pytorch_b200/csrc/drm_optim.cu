@@ -11,6 +11,7 @@ constexpr int kOptThreads = 256;
 // sum of squares of every gradient element of the group -> acc[0] (double)
 __global__ void __launch_bounds__(kOptThreads) grad_sumsq_kernel(const drm_clip_adam_call c, double* acc) {
     const int t = blockIdx.y;
+    if (c.step_dev && blockIdx.x == 0 && t == 0 && threadIdx.x == 0) atomicAdd(c.step_dev, 1);  // read by the update kernel
     const float* g = c.grad[t];
     const int64_t n = c.numel[t];
     float s = 0.f;
@@ -41,15 +42,21 @@ __global__ void __launch_bounds__(kOptThreads) clip_adam_kernel(const drm_clip_a
     float* v = c.exp_avg_sq[t];
     const int64_t n = c.numel[t];
     const float w1 = c.one_minus_beta1, w2 = c.one_minus_beta2;
+    float step_size = c.step_size, bias2_sqrt = c.bias2_sqrt;
+    if (c.step_dev) {  // bias corrections from the device-side step counter (adam.py: 1 - beta ** step), in double
+        const double st = (double)*c.step_dev;
+        step_size = (float)((double)c.lr / (1.0 - pow(c.beta1_d, st)));
+        bias2_sqrt = (float)sqrt(1.0 - pow(c.beta2_d, st));
+    }
     for (int64_t i = (int64_t)blockIdx.x * kOptThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kOptThreads) {
         const float gi = g[i] * coef;
         const float mi = m[i] + w1 * (gi - m[i]);         // exp_avg.lerp_(grad, 1 - beta1)
         const float vi = v[i] * c.beta2 + w2 * gi * gi;   // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, value=1 - beta2)
-        const float denom = sqrtf(vi) / c.bias2_sqrt + c.eps;
+        const float denom = sqrtf(vi) / bias2_sqrt + c.eps;
         g[i] = gi;
         m[i] = mi;
         v[i] = vi;
-        p[i] = p[i] - c.step_size * (mi / denom);         // param.addcdiv_(exp_avg, denom, value=-step_size)
+        p[i] = p[i] - step_size * (mi / denom);           // param.addcdiv_(exp_avg, denom, value=-step_size)
     }
 }
 

@@ -24,7 +24,12 @@ from .dropin.rnns import RSSMState
 
 class ImaginationGraph:
     def __init__(self, model, n_states: int, horizon: int, discount: float = 0.99, discount_lambda: float = 0.95,
-                 use_pcont: bool = False, warmup: int = 3):
+                 use_pcont: bool = False, warmup: int = 3, actor_opt=None, value_opt=None):
+        """actor_opt / value_opt: optional ``optim.ClipAdam(..., capturable=True)`` over the action decoder's / the value
+        model's parameters.  Their step() (clip_grad_norm_ + Adam, dreamer_algo.py:182-194) is then recorded behind the
+        backward pass, so that one replay is one whole actor + value update.  Parameters and optimizer state are restored
+        after the warm-up passes; single-process only (with several ranks the gradient all-reduce sits between the
+        backward pass and the optimizers: keep them outside the graph there)."""
         p0 = next(model.parameters())
         if not p0.is_cuda:
             raise RuntimeError("ImaginationGraph needs a CUDA model (there is no CPU fallback)")
@@ -36,6 +41,15 @@ class ImaginationGraph:
         self.actor_params = list(model.action_decoder.parameters())
         self.value_params = list(model.value_model.parameters())
         self.params = self.actor_params + self.value_params
+        self.opts = [(o, ps) for o, ps in ((actor_opt, self.actor_params), (value_opt, self.value_params)) if o is not None]
+        for o, ps in self.opts:
+            if getattr(o, "step_dev", None) is None:
+                raise ValueError("optimizers recorded into the graph must be ClipAdam(..., capturable=True)")
+            if [id(p) for p in o.params] != [id(p) for p in ps]:
+                raise ValueError("the optimizer must cover exactly the parameters of its module, in order")
+        keep = [(p, p.detach().clone()) for p in self.params] if self.opts else []
+        for o, _ in self.opts:  # warm-up passes step the optimizers: remember their state
+            keep += [(t, t.clone()) for st in o.state.values() for t in st.values()] + [(o.step_dev, o.step_dev.clone())]
         # eager warm-up on a side stream (lazy initialisation, allocator high-water mark), as capture requires
         cur = torch.cuda.current_stream(dev)
         s = torch.cuda.Stream(device=dev)
@@ -54,6 +68,9 @@ class ImaginationGraph:
         self.launches_per_replay = int(lib.drm_launch_count() - n0)  # kernels of this library inside the graph
         for p, g in zip(self.params, self.grads):
             p.grad = g  # static tensors from the graph's pool, refreshed by every replay
+        with torch.no_grad():
+            for t, saved in keep:
+                t.copy_(saved)
 
     def _eager(self):
         start = RSSMState(self.stoch, self.stoch, self.stoch, self.deter)  # mean / std of a start state are never read
@@ -62,7 +79,12 @@ class ImaginationGraph:
         # on, which breaks capture when the model has been used on the default stream before)
         ga = torch.autograd.grad(actor_loss, self.actor_params)
         gv = torch.autograd.grad(value_loss, self.value_params)
-        return actor_loss.detach(), value_loss.detach(), list(ga) + list(gv)
+        grads = list(ga) + list(gv)
+        if self.opts:
+            for p, g in zip(self.params, grads):
+                p.grad = g
+            self.grad_norms = [o.step() for o, _ in self.opts]  # device scalars (norm before clipping), static
+        return actor_loss.detach(), value_loss.detach(), grads
 
     def step(self, stoch: torch.Tensor, deter: torch.Tensor):
         """Copies the start states into the captured buffers (a host->device copy when they live in pinned host

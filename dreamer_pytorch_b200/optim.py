@@ -27,7 +27,9 @@ from . import _lib
 
 class ClipAdam:
     def __init__(self, params: Iterable[torch.nn.Parameter], lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
-                 grad_clip: Optional[float] = None):
+                 grad_clip: Optional[float] = None, capturable: bool = False):
+        """capturable: keep the step counter on the device (like torch.optim.Adam(capturable=True)) so that step() can be
+        recorded into a CUDA graph; ``step_count`` then costs a device read."""
         self.listed = list(params)                      # as given (duplicates kept: they count in the norm)
         seen, uniq = set(), []
         for p in self.listed:
@@ -41,11 +43,23 @@ class ClipAdam:
             if not p.is_cuda or p.dtype != torch.float32:
                 raise RuntimeError("ClipAdam needs fp32 CUDA parameters (there is no CPU fallback)")
         self.lr, self.betas, self.eps, self.grad_clip = float(lr), (float(betas[0]), float(betas[1])), float(eps), grad_clip
-        self.step_count = 0
+        self._steps = 0
         self.state = {p: dict(exp_avg=torch.zeros_like(p), exp_avg_sq=torch.zeros_like(p)) for p in self.params}
         dev = self.params[0].device
         self._ws = torch.zeros(4, dtype=torch.float32, device=dev)
         self.grad_norm = torch.zeros((), dtype=torch.float32, device=dev)
+        self.step_dev = torch.zeros(1, dtype=torch.int32, device=dev) if capturable else None
+
+    @property
+    def step_count(self) -> int:
+        return int(self.step_dev.item()) if self.step_dev is not None else self._steps
+
+    @step_count.setter
+    def step_count(self, v: int):
+        if self.step_dev is not None:
+            self.step_dev.fill_(int(v))
+        else:
+            self._steps = int(v)
 
     def zero_grad(self, set_to_none: bool = True):
         for p in self.params:
@@ -62,10 +76,12 @@ class ClipAdam:
         live = [p for p in self.params if p.grad is not None]
         if not live:
             return self.grad_norm.zero_()
-        self.step_count += 1
         b1, b2 = self.betas
-        step_size = self.lr / (1.0 - b1 ** self.step_count)
-        bias2_sqrt = math.sqrt(1.0 - b2 ** self.step_count)
+        step_size = bias2_sqrt = 0.0
+        if self.step_dev is None:
+            self._steps += 1
+            step_size = self.lr / (1.0 - b1 ** self._steps)
+            bias2_sqrt = math.sqrt(1.0 - b2 ** self._steps)
         counts = {}
         for p in self.listed:
             counts[id(p)] = counts.get(id(p), 0) + 1
@@ -78,6 +94,8 @@ class ClipAdam:
             c.max_norm = float(self.grad_clip) if self.grad_clip else 0.0
             c.beta1, c.beta2, c.eps = b1, b2, self.eps
             c.one_minus_beta1, c.one_minus_beta2 = 1.0 - b1, 1.0 - b2
+            if self.step_dev is not None:
+                c.lr, c.beta1_d, c.beta2_d, c.step_dev = self.lr, b1, b2, self.step_dev.data_ptr()
             c.step_size, c.bias2_sqrt = step_size, bias2_sqrt
             for i, p in enumerate(chunk):
                 g = p.grad

@@ -287,6 +287,13 @@ typedef struct drm_clip_adam_call {
     float beta1, beta2, eps;
     float one_minus_beta1, one_minus_beta2;  /* computed in double by the host (1 - 0.999f in fp32 is off by 5e-5) */
     float step_size, bias2_sqrt;
+    /* Device-side step counter (optional, for CUDA-graph capture where host scalars would be frozen): when step_dev is
+     * non-NULL the call increments *step_dev and derives step_size = lr / (1 - beta1^t) and bias2_sqrt = sqrt(1 - beta2^t)
+     * from it on the device (in double, from beta1_d / beta2_d); step_size / bias2_sqrt above are then ignored. */
+    float lr;
+    int32_t pad2_;
+    double beta1_d, beta2_d;
+    int32_t* step_dev;
     float* param[DRM_MAX_OPT_TENSORS];
     float* grad[DRM_MAX_OPT_TENSORS];
     float* exp_avg[DRM_MAX_OPT_TENSORS];

@@ -51,3 +51,64 @@ def test_clip_adam_rejects_cpu_and_duplicates():
     p.grad = torch.ones_like(p)
     with pytest.raises(NotImplementedError):
         ClipAdam([p, p], grad_clip=1.0).step()
+
+
+def test_whole_update_in_one_graph_matches_eager_updates():
+    """ImaginationGraph with recorded optimizers (one replay = losses, backward, clip + Adam for actor and value) against
+    the same fused losses stepped eagerly with torch's clip_grad_norm_ + Adam, on identical noise, over three updates."""
+    import copy
+
+    from dreamer_pytorch_b200 import noise
+    from dreamer_pytorch_b200.algo import imagination_losses
+    from dreamer_pytorch_b200.dropin.agent import AtariDreamerModel
+    from dreamer_pytorch_b200.dropin.rnns import RSSMState
+    from dreamer_pytorch_b200.graph import ImaginationGraph
+    from dreamer_pytorch_b200.optim import ClipAdam
+    from dreamer_pytorch_b200.precision import precision
+
+    dev = torch.device("cuda:0")
+    torch.manual_seed(0)
+    A, N, H, updates, warm = 6, 300, 5, 3, 2
+    model = AtariDreamerModel(action_shape=(A,), action_dist="tanh_normal").to(dev).train()
+    ref_model = copy.deepcopy(model)
+    g = torch.Generator().manual_seed(1)
+    stoch = torch.randn(N, 30, generator=g).to(dev)
+    deter = torch.tanh(torch.randn(N, 200, generator=g)).to(dev)
+    eps = [torch.randn(H, N, 30, generator=g).to(dev) for _ in range(updates)]
+    nza = [torch.randn(H, N, A, generator=g).to(dev) for _ in range(updates)]
+    lr, clip = 8e-5, 100.0
+    with precision("bf16"):
+        # eager reference: fused losses + torch optimizers
+        groups = [list(ref_model.action_decoder.parameters()), list(ref_model.value_model.parameters())]
+        opts = [torch.optim.Adam(ps, lr=lr) for ps in groups]
+        ref_norms = []
+        with noise.injected(eps_prior=eps, noise_act=nza):
+            for _ in range(updates):
+                for o in opts:
+                    o.zero_grad()
+                al, vl, _ = imagination_losses(ref_model, RSSMState(stoch, stoch, stoch, deter), H)
+                al.backward(); vl.backward()
+                ref_norms.append([torch.nn.utils.clip_grad_norm_(ps, clip).clone() for ps in groups])
+                for o in opts:
+                    o.step()
+        del al, vl
+        # one graph per update
+        a_opt = ClipAdam(model.action_decoder.parameters(), lr=lr, grad_clip=clip, capturable=True)
+        v_opt = ClipAdam(model.value_model.parameters(), lr=lr, grad_clip=clip, capturable=True)
+        eps_buf, nza_buf = eps[0].clone(), nza[0].clone()  # the graph records these buffers: refilled before every replay
+        with noise.injected(eps_prior=[eps_buf] * (warm + 1), noise_act=[nza_buf] * (warm + 1)):
+            graph = ImaginationGraph(model, N, H, warmup=warm, actor_opt=a_opt, value_opt=v_opt)
+        assert a_opt.step_count == 0 and v_opt.step_count == 0      # warm-up passes left no trace
+        norms = []
+        for k in range(updates):
+            eps_buf.copy_(eps[k]); nza_buf.copy_(nza[k])
+            graph.step(stoch, deter)
+            norms.append([n.clone() for n in graph.grad_norms])
+    torch.cuda.synchronize()
+    assert a_opt.step_count == updates and v_opt.step_count == updates
+    for p, r in zip(model.action_decoder.parameters(), ref_model.action_decoder.parameters()):
+        assert rel_err(p, r) < 1e-4
+    for p, r in zip(model.value_model.parameters(), ref_model.value_model.parameters()):
+        assert rel_err(p, r) < 1e-4
+    for a, b in zip(norms, ref_norms):
+        assert rel_err(a[0], b[0]) < 1e-3 and rel_err(a[1], b[1]) < 1e-3
