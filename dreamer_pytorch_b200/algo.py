@@ -288,11 +288,17 @@ def imagination_losses(model, start_state: RSSMState, horizon: int, discount: fl
     cfg = RolloutCfg(_lib.MODE_POLICY, horizon, N, model.transition.dims(), act_dist=model.action_dist,
                      mean_scale=float(dec.mean_scale), raw_init_std=float(dec.raw_init_std),
                      act_min_std=float(dec.min_std))
-    if model.action_dist == "tanh_normal":
-        noise_act = noise.normal("noise_act", (horizon, N, A), dev)
+    if model.action_dist == "tanh_normal" and not noise.is_injected("noise_act", "eps_prior") and (horizon * N * A) % 4 == 0:
+        # both N(0,1) blocks from one generator launch (two 16-byte aligned views of one buffer)
+        flat = torch.randn(horizon * N * (A + S), dtype=torch.float32, device=dev)
+        noise_act = flat[:horizon * N * A].view(horizon, N, A)
+        eps = flat[horizon * N * A:].view(horizon, N, S)
     else:
-        noise_act = noise.gumbel("noise_act", (horizon, N, A), dev)
-    eps = noise.normal("eps_prior", (horizon, N, S), dev)
+        if model.action_dist == "tanh_normal":
+            noise_act = noise.normal("noise_act", (horizon, N, A), dev)
+        else:
+            noise_act = noise.gumbel("noise_act", (horizon, N, A), dev)
+        eps = noise.normal("eps_prior", (horizon, N, S), dev)
     t = dict(start_stoch=stoch, start_deter=deter, eps_prior=eps, noise_act=noise_act)
     frozen = lambda ws: [_f32c(w.detach()) for w in ws]
     rssm = frozen(model.transition.weights()) + [None] * 4

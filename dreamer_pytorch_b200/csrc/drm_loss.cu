@@ -86,6 +86,92 @@ __global__ void __launch_bounds__(256) returns_loss_kernel(const drm_returns_los
     }
 }
 
+// Same computation with the trajectory held in registers (H <= MAXH): every global load of a column is issued up front
+// instead of one dependent load per step of the recursions (the generic kernel above spends ~H load latencies per pass).
+template <int MAXH>
+__global__ void __launch_bounds__(128) returns_loss_reg_kernel(const drm_returns_loss_call c) {
+    __shared__ float red[8];
+    const int N = c.N, H = c.H, L = c.H - 1;
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    const float lam = c.lambda_;
+    const float cmean = -1.f / ((float)L * (float)N);
+    float sum_actor = 0.f, sum_value = 0.f;
+    if (n < N) {
+        float V[MAXH], Rw[MAXH], D[MAXH], Ret[MAXH], Disc[MAXH], gP[MAXH];
+#pragma unroll
+        for (int h = 0; h < MAXH; ++h) {
+            V[h] = h < H ? c.value[(size_t)h * N + n] : 0.f;
+            Rw[h] = h < L ? c.reward[(size_t)h * N + n] : 0.f;
+            D[h] = c.pcont ? (h < L ? sigmoidf_(c.pcont[(size_t)h * N + n]) : 0.f) : c.discount;
+            Ret[h] = 0.f; Disc[h] = 0.f; gP[h] = 0.f;
+        }
+        // pass 1 (reverse): lambda-returns
+        float acc = 0.f;
+#pragma unroll
+        for (int h = MAXH - 1; h >= 0; --h) {
+            if (h == H - 1) acc = V[h];  // bootstrap
+            if (h < L) {
+                const float vnext = h + 1 < MAXH ? V[h + 1 < MAXH ? h + 1 : h] : 0.f;
+                const float target = Rw[h] + D[h] * vnext * (1.f - lam);
+                acc = target + D[h] * lam * acc;
+                Ret[h] = acc;
+                c.returns[(size_t)h * N + n] = acc;
+            }
+        }
+        // pass 2 (forward): cumulative discount, losses, adjoints of the return recursion
+        float disc = 1.f, gR = 0.f, dprev = 0.f;
+        c.d_value[n] = 0.f;
+#pragma unroll
+        for (int h = 0; h < MAXH; ++h) {
+            if (h < L) {
+                const float d = D[h];
+                if (h > 0) disc *= d;
+                const float Rh = Ret[h], v = V[h];
+                Disc[h] = disc;
+                c.disc[(size_t)h * N + n] = disc;
+                sum_actor += disc * Rh;
+                const float diff = Rh - v;
+                sum_value += disc * (-0.5f * diff * diff - 0.9189385332046727f);
+                c.d_value_pred[(size_t)h * N + n] = cmean * disc * diff;
+                gR = cmean * disc + gR * dprev * lam;
+                dprev = d;
+                const float vnext = V[h + 1 < MAXH ? h + 1 : h];
+                const float Rnext = (h + 1 < L) ? Ret[h + 1 < MAXH ? h + 1 : h] : vnext;
+                c.d_reward[(size_t)h * N + n] = gR;
+                float dv = gR * d * (1.f - lam);
+                if (h == L - 1) dv += gR * d * lam;
+                c.d_value[(size_t)(h + 1) * N + n] = dv;
+                gP[h] = gR * (lam * Rnext + (1.f - lam) * vnext);
+            }
+        }
+        c.d_reward[(size_t)L * N + n] = 0.f;
+        c.d_value_pred[(size_t)L * N + n] = 0.f;
+        if (c.d_pcont) {
+            c.d_pcont[(size_t)L * N + n] = 0.f;
+            float carry = 0.f;
+#pragma unroll
+            for (int h = MAXH - 1; h >= 0; --h) {
+                if (h < L) {
+                    const float d = D[h];
+                    float gd = gP[h];
+                    if (h >= 1) {
+                        const float gdisc = cmean * Ret[h] + carry;
+                        gd += gdisc * Disc[h >= 1 ? h - 1 : 0];
+                        carry = gdisc * d;
+                    }
+                    c.d_pcont[(size_t)h * N + n] = gd * d * (1.f - d);
+                }
+            }
+        }
+    }
+    const float sa = block_sum(sum_actor, red);
+    const float sv = block_sum(sum_value, red);
+    if (threadIdx.x == 0) {
+        atomicAdd(c.losses + 0, cmean * sa);
+        atomicAdd(c.losses + 1, cmean * sv);
+    }
+}
+
 __global__ void __launch_bounds__(256) kl_fwd_kernel(const drm_kl_call c) {
     __shared__ float red[8];
     const size_t total = (size_t)c.M * c.S;
@@ -138,9 +224,10 @@ int drm_returns_loss(const drm_returns_loss_call* c, void* stream_) {
                     c->d_value_pred, DRM_E_ARG, "null pointer");
     DRM_REQUIRE((c->pcont == nullptr) == (c->d_pcont == nullptr), DRM_E_ARG, "pcont and d_pcont must come together");
     int rc = check_device(); if (rc) return rc;
-    const int grid = (c->N + 255) / 256;
     ProfScope prof(PROF_LOSS, stream);
-    returns_loss_kernel<<<grid, 256, 0, stream>>>(*c);
+    if (c->H <= 16) returns_loss_reg_kernel<16><<<(c->N + 127) / 128, 128, 0, stream>>>(*c);
+    else if (c->H <= 32) returns_loss_reg_kernel<32><<<(c->N + 127) / 128, 128, 0, stream>>>(*c);
+    else returns_loss_kernel<<<(c->N + 255) / 256, 256, 0, stream>>>(*c);
     DRM_CUDA_OK(cudaGetLastError());
     return DRM_OK;
 }

@@ -32,6 +32,11 @@ def injected(**named):
         _queues = old
 
 
+def is_injected(*names) -> bool:
+    """True if a tensor is queued for any of the names."""
+    return any(_queues.get(n) for n in names)
+
+
 def _pop(name, shape, device):
     q = _queues.get(name)
     if not q:

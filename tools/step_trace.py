@@ -45,9 +45,9 @@ def main():
     ev = json.load(open(path))["traceEvents"]
     dev_ev = [e for e in ev if e.get("ph") == "X" and e.get("cat") in ("kernel", "gpu_memset", "gpu_memcpy")]
     dev_ev.sort(key=lambda e: e["ts"])
-    # the last step starts at its first noise kernel (two of them open every step)
+    # the last step starts at its noise kernel (one generator launch opens every step)
     firsts = [i for i, e in enumerate(dev_ev) if "distribution_elementwise" in e["name"]]
-    lo = firsts[-2] if len(firsts) >= 2 else 0
+    lo = firsts[-1] if firsts else 0
     last = dev_ev[lo:]
     t0 = last[0]["ts"]
     print(f"# {len(last)} device activities in the last step; span {last[-1]['ts'] + last[-1]['dur'] - t0:.1f} us")
