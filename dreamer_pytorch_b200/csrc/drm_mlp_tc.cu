@@ -262,8 +262,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_fwd_tc_kernel(const __gr
                     epi_for_chunks(tmem_base, 0, cbeg, cend, [&](int c, float (&v)[8]) {
                         float b[8];
                         lds8(bias + c * 8, b);
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) v[i] = elu_fast(v[i] + b[i]);
+                        elu_bias8(v, b);
                         const uint4 q = pack_bf16x8(v);
                         *reinterpret_cast<uint4*>(act_cur + ((size_t)c * kTileRows + row) * 16) = q;
                         if (sv) *reinterpret_cast<uint4*>(tcm_at(sv, p.ch, tile, c, row)) = q;

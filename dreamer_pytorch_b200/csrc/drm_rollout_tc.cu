@@ -168,8 +168,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                     epi_for_chunks(tmem_base, 0, a_beg, a_end, [&](int c, float (&v)[8]) {
                         float b[8];
                         lds8(bias + c * 8, b);
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) v[i] = elu_fast(v[i] + b[i]);
+                        elu_bias8(v, b);
                         st_chunk_bf16(hb + ((size_t)c * kTileRows + row) * 16, v);
                         if (sv) st_chunk_bf16(tcm_at(sv, p.cha, ts, c, row), v);
                     }, a_go);
@@ -302,8 +301,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                     epi_for_chunks(tmem_base, 0, h_beg, h_end, [&](int c, float (&v)[8]) {
                         float b[8];
                         lds8(bias + c * 8, b);
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) v[i] = elu_fast(v[i] + b[i]);
+                        elu_bias8(v, b);
                         st_chunk_bf16(hb + ((size_t)c * kTileRows + row) * 16, v);
                         if (sv) st_chunk_bf16(tcm_at(sv, p.chh, ts, c, row), v);
                     }, h_go);
@@ -424,8 +422,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                     epi_for_chunks(tmem_base, 0, h_beg, h_end, [&](int c, float (&v)[8]) {
                         float b[8];
                         lds8(bias + c * 8, b);
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) v[i] = elu_fast(v[i] + b[i]);
+                        elu_bias8(v, b);
                         st_chunk_bf16(hb + ((size_t)c * kTileRows + row) * 16, v);
                         if (sv) st_chunk_bf16(tcm_at(sv, p.chh, ts, c, row), v);
                     }, h_go);

@@ -125,7 +125,16 @@ __device__ __forceinline__ void chain_producer(const TcProgram& pg, ChainBars* b
                 const uint32_t bytes = (uint32_t)c * n * 16;
                 mbar_wait(&bars->empty[stage], phase ^ 1);
                 mbar_expect_tx(&bars->full[stage], bytes);
+#ifdef DRM_BULK_PIECES
+                {
+                    uint8_t* dstp = smem + pg.stage_off + (size_t)stage * pg.stage_bytes;
+                    const uint32_t piece = ((bytes / DRM_BULK_PIECES) + 15u) & ~15u;
+                    for (uint32_t o = 0; o < bytes; o += piece)
+                        bulk_g2s(dstp + o, src + o, min(piece, bytes - o), &bars->full[stage]);
+                }
+#else
                 bulk_g2s(smem + pg.stage_off + (size_t)stage * pg.stage_bytes, src, bytes, &bars->full[stage]);
+#endif
                 src += bytes;
                 chunks -= c;
                 if (++stage == pg.n_stages) { stage = 0; phase ^= 1; }
@@ -184,7 +193,9 @@ __device__ __forceinline__ void chain_mma(const TcProgram& pg, ChainBars* bars, 
             int c = 0;
             while (c < total) {
                 const int cnt = min(kc, total - c);
+                if ((threadIdx.x & 31) == 0) DRM_TL(3);
                 mbar_wait(&bars->full[stage], phase);
+                if ((threadIdx.x & 31) == 0) DRM_TL(3);
                 tc_fence_after_sync();
                 uint32_t b_lo = (((stage0 + (uint32_t)stage * stage_bytes) & 0x3FFFFu) >> 4) | b_flags;
 #pragma unroll 1
@@ -388,6 +399,33 @@ __device__ __forceinline__ void fill_bias(float* dst, const float* a, const floa
 // ---------------------------------------------------------------------------------------------- fast pointwise math
 // (bf16 path only: the operands of the next GEMM are rounded to 8 bits of mantissa anyway)
 __device__ __forceinline__ float elu_fast(float x) { return fmaxf(x, 0.f) + (__expf(fminf(x, 0.f)) - 1.f); }
+// ELU(v + b) over one 8-column chunk.  The epilogues are bound by instruction issue (4 warps per scheduler), so this is
+// written for instruction count: packed fp32 pairs (add / mul .f32x2), exp2 with flush-to-zero (no denormal fix-up code),
+// and ELU(x) = max(x, exp(min(x, 0)) - 1), which holds because exp(x) - 1 >= x everywhere.  About 5 issue slots per
+// element instead of 10.
+__device__ __forceinline__ void elu_bias8(float (&v)[8], const float (&b)[8]) {
+#pragma unroll
+    for (int i = 0; i < 8; i += 2) {
+        float x0, x1, t0, t1;
+        asm("{\n\t.reg .b64 a, c, x;\n\t"
+            "mov.b64 a, {%2, %3};\n\tmov.b64 c, {%4, %5};\n\t"
+            "add.rn.f32x2 x, a, c;\n\t"
+            "mov.b64 {%0, %1}, x;\n\t}"
+            : "=f"(x0), "=f"(x1) : "f"(v[i]), "f"(v[i + 1]), "f"(b[i]), "f"(b[i + 1]));
+        const float m0 = fminf(x0, 0.f), m1 = fminf(x1, 0.f);
+        asm("{\n\t.reg .b64 a, c, s;\n\t.reg .f32 s0, s1, e0, e1;\n\t"
+            "mov.b64 a, {%2, %3};\n\tmov.b64 c, {%4, %4};\n\t"
+            "mul.rn.f32x2 s, a, c;\n\t"
+            "mov.b64 {s0, s1}, s;\n\t"
+            "ex2.approx.ftz.f32 e0, s0;\n\tex2.approx.ftz.f32 e1, s1;\n\t"
+            "mov.b64 a, {e0, e1};\n\tmov.b64 c, {%5, %5};\n\t"
+            "add.rn.f32x2 s, a, c;\n\t"
+            "mov.b64 {%0, %1}, s;\n\t}"
+            : "=f"(t0), "=f"(t1) : "f"(m0), "f"(m1), "f"(1.4426950408889634f), "f"(-1.f));
+        v[i] = fmaxf(x0, t0);
+        v[i + 1] = fmaxf(x1, t1);
+    }
+}
 __device__ __forceinline__ float tanh_fast(float x) {
     float y;
     asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
