@@ -362,10 +362,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_bwd_tc_kernel(const __gr
                 epi_for_chunks_saved(es, tmem_base, 0, cbeg, cend,
                     [&](int c) { return *reinterpret_cast<const uint4*>(tcm_at(hs, p.ch, tile, c, row)); },
                     [&](int c, float (&v)[8], const uint4 hq) {
-                        float h[8];
-                        unpack_bf16x8(hq, h);
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) v[i] = live ? v[i] * (h[i] > 0.f ? 1.f : h[i] + 1.f) : 0.f;
+                        elu_bwd8(v, hq, live);
                         const uint4 q = pack_bf16x8(v);
                         *reinterpret_cast<uint4*>(act + ((size_t)c * kTileRows + row) * 16) = q;
                         if (dsv) *reinterpret_cast<uint4*>(tcm_at(dsv, p.ch, tile, c, row)) = q;

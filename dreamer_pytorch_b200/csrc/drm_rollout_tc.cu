@@ -667,10 +667,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                     epi_for_chunks_saved(es, tmem_base, 0, cbeg, cend,
                         [&](int c) { return *reinterpret_cast<const uint4*>(tcm_at(p.sv_hid, p.chh, ts, c, row)); },
                         [&](int c, float (&v)[8], const uint4 hq) {
-                            float h[8];
-                            unpack_bf16x8(hq, h);
-#pragma unroll
-                            for (int i = 0; i < 8; ++i) v[i] = live ? v[i] * (h[i] > 0.f ? 1.f : h[i] + 1.f) : 0.f;
+                            elu_bwd8(v, hq, live);
                             st_chunk_bf16(ga + ((size_t)c * kTileRows + row) * 16, v);
                         }, [] {}, go);
                 }
@@ -758,10 +755,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                     epi_for_chunks_saved(es, tmem_base, 0, cbeg, cend,
                         [&](int c) { return *reinterpret_cast<const uint4*>(tcm_at(p.sv_x, p.chh, ts, c, row)); },
                         [&](int c, float (&v)[8], const uint4 hq) {
-                            float h[8];
-                            unpack_bf16x8(hq, h);
-#pragma unroll
-                            for (int i = 0; i < 8; ++i) v[i] = live ? v[i] * (h[i] > 0.f ? 1.f : h[i] + 1.f) : 0.f;
+                            elu_bwd8(v, hq, live);
                             st_chunk_bf16(ga + ((size_t)c * kTileRows + row) * 16, v);
                         }, [] {}, go);
                     if (p.want_actor && tid == 0) l2_prefetch(tcm_at(p.sv_ah[last - 1], p.cha, ts, 0, 0), p.cha * chunk_img * 2);
@@ -850,10 +844,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                         epi_for_chunks_saved(es, tmem_base, 0, cbeg, cend,
                             [&](int c) { return *reinterpret_cast<const uint4*>(tcm_at(p.sv_ah[l - 1], p.cha, ts, c, row)); },
                             [&](int c, float (&v)[8], const uint4 hq) {
-                                float h[8];
-                                unpack_bf16x8(hq, h);
-#pragma unroll
-                                for (int i = 0; i < 8; ++i) v[i] = live ? v[i] * (h[i] > 0.f ? 1.f : h[i] + 1.f) : 0.f;
+                                elu_bwd8(v, hq, live);
                                 if (l > 1) st_chunk_bf16(ga + ((size_t)c * kTileRows + row) * 16, v);  // layer 0 gets no data gradient
                                 st_chunk_bf16(tcm_at(p.dys_a[l - 1], p.cha, ts, c, row), v);
                             },

@@ -426,6 +426,27 @@ __device__ __forceinline__ void elu_bias8(float (&v)[8], const float (&b)[8]) {
         v[i + 1] = fmaxf(x1, t1);
     }
 }
+// ELU backward over one chunk: v *= ELU'(pre) with the saved bf16 activation h = ELU(pre): ELU' = 1 for h > 0, h + 1
+// otherwise, i.e. min(h, 0) + 1 -- no compare / select; packed fp32 pairs; rows beyond the batch give zeros.
+__device__ __forceinline__ void elu_bwd8(float (&v)[8], const uint4 hq, bool live) {
+    if (!live) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] = 0.f;
+        return;
+    }
+    const uint32_t w[4] = {hq.x, hq.y, hq.z, hq.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float m0 = fminf(__uint_as_float(w[i] << 16), 0.f), m1 = fminf(__uint_as_float(w[i] & 0xFFFF0000u), 0.f);
+        asm("{\n\t.reg .b64 a, c, f, x;\n\t"
+            "mov.b64 a, {%2, %3};\n\tmov.b64 c, {%4, %4};\n\t"
+            "add.rn.f32x2 f, a, c;\n\t"
+            "mov.b64 x, {%0, %1};\n\t"
+            "mul.rn.f32x2 x, x, f;\n\t"
+            "mov.b64 {%0, %1}, x;\n\t}"
+            : "+f"(v[2 * i]), "+f"(v[2 * i + 1]) : "f"(m0), "f"(m1), "f"(1.f));
+    }
+}
 __device__ __forceinline__ float tanh_fast(float x) {
     float y;
     asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
