@@ -395,9 +395,9 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_bwd_tc_kernel(const __gr
                     else if (p.dx1) stg_row8(p.dx1 + (size_t)grow * p.ld1, (c - p.c0) * 8, p.k1, v, p.accumulate_dx != 0);
                 }
                 if (p.tile_done || p.step_rows_done) {
-                    __threadfence();  // this thread's dx stores before the signal
-                    named_bar<kEpiThreads, 1>();
+                    named_bar<kEpiThreads, 1>();  // every thread's dx stores ...
                     if (threadIdx.x == 0) {
+                        __threadfence();          // ... are released by one cumulative gpu-scope fence before the signal
                         if (p.tile_done) atomicExch(p.tile_done + tile, 1);
                         if (p.step_rows_done) {
                             const int r_end = min(p.M, row0 + kTileRows);

@@ -496,9 +496,10 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
                         p.prior_stoch[o0 + i] = sE[i];
                     }
                 }
-                if (p.step_flags) __threadfence();  // this thread's stores of step t (deter, action, prior) before the signal
                 named_bar<kEpiThreads, 1>();  // the hidden buffer is written again by the next epilogue
-                if (p.step_flags && tid == 0) atomicAdd(p.step_flags + t, 1);
+                // release: the barrier orders every epilogue thread's stores of step t (deter, action, prior) before this
+                // thread's gpu-scope fence, which is cumulative (the CUTLASS barrier pattern: sync, then one thread releases)
+                if (p.step_flags && tid == 0) { __threadfence(); atomicAdd(p.step_flags + t, 1); }
             }
         }
     }
@@ -630,9 +631,9 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
                 const size_t trow = (size_t)t * p.n + grow;
                 // ------------------------------------------------------------ prior head (pointwise) -> G2
                 cp_async_wait_all();
-                if (p.bwd_flags) __threadfence();  // this thread's dY image stores of step t + 1 before the signal below
                 named_bar<kEpiThreads, 1>();
-                if (p.bwd_flags && tid == 0 && t + 1 < p.T) atomicAdd(p.bwd_flags + t + 1, 1);
+                // the dY images of step t + 1 are complete: one thread releases them (barrier + cumulative gpu-scope fence)
+                if (p.bwd_flags && tid == 0 && t + 1 < p.T) { __threadfence(); atomicAdd(p.bwd_flags + t + 1, 1); }
                 pf_gru(t);
                 {
                     const int per = (p.cs + kEpiGroups - 1) / kEpiGroups;
@@ -863,9 +864,8 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
             }
             // the next tile's zero-fill of R_C / R_AS and its first release() come after these loads
             if (p.bwd_flags) {
-                __threadfence();
                 named_bar<kEpiThreads, 1>();
-                if (tid == 0) atomicAdd(p.bwd_flags, 1);
+                if (tid == 0) { __threadfence(); atomicAdd(p.bwd_flags, 1); }
             }
         }
     }
