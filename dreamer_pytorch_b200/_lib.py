@@ -112,6 +112,8 @@ STRUCTS = {s.__name__: s for s in (drm_clip_adam_call, drm_mlp, drm_mlp_grad, dr
 # every symbol include/dreamer_b200.h declares: name -> (restype, argtypes)
 SYMBOLS = {
     "drm_version": (C.c_int, []),
+    "drm_init": (C.c_int, []),
+    "drm_num_sms": (C.c_int, []),
     "drm_last_error": (C.c_char_p, []),
     "drm_sizeof": (C.c_size_t, [C.c_char_p]),
     "drm_launch_count": (C.c_ulonglong, []),
@@ -162,6 +164,20 @@ def load():
             raise RuntimeError(f"ABI mismatch for {name}: C says {got} bytes, ctypes says {C.sizeof(st)}")
     _lib = lib
     return lib
+
+
+_inited = set()
+
+
+def ensure_init():
+    """drm_init() once per device: architecture check + eager load of every kernel (a kernel that spins on the
+    counters of a producer must never be resident while another kernel is loaded lazily at its first launch)."""
+    import torch
+
+    dev = torch.cuda.current_device()
+    if dev not in _inited:
+        check(load().drm_init(), "drm_init")
+        _inited.add(dev)
 
 
 def check(rc: int, what: str):

@@ -31,22 +31,41 @@ _SIDE = {}
 # turns all of them off: every kernel in stream order; a comma-separated subset of "heads,prepare,backward" keeps those.
 import os as _os
 
-_sched = _os.environ.get("DRM_B200_SCHEDULE", "heads,prepare,backward").split(",")
-_PIPELINE_HEADS = "heads" in _sched  # heads beside the rollout when SMs are idle (see _ActorLossFn.forward)
-_PREPARE_BACKWARD = "prepare" in _sched  # weight packing / zero-filled sinks of the backward pass beside the forward pass
-_PIPELINE_BACKWARD = "backward" in _sched  # head data-gradient kernels beside the reverse-time rollout (_ActorLossFn.backward)
-_FOLLOW_WGRAD = "nofollow" not in _sched  # actor weight gradients step by step behind the rollout backward
+_PIPELINE_HEADS = _PREPARE_BACKWARD = _PIPELINE_BACKWARD = _FOLLOW_WGRAD = True
+
+
+def set_schedule(spec: str = "heads,prepare,backward") -> str:
+    """Selects which kernels run beside each other; returns the previous setting.  "plain": every kernel in stream
+    order (what bench.py uses to time the dominant kernel in isolation)."""
+    global _PIPELINE_HEADS, _PREPARE_BACKWARD, _PIPELINE_BACKWARD, _FOLLOW_WGRAD, _sched_spec
+    prev = _sched_spec
+    parts = spec.split(",")
+    _PIPELINE_HEADS = "heads" in parts  # heads beside the rollout when SMs are idle (see _ActorLossFn.forward)
+    _PREPARE_BACKWARD = "prepare" in parts  # weight packing / zero-filled sinks of the backward pass beside the forward pass
+    _PIPELINE_BACKWARD = "backward" in parts  # head data-gradient kernels beside the reverse-time rollout (_ActorLossFn.backward)
+    _FOLLOW_WGRAD = "nofollow" not in parts  # actor weight gradients step by step behind the rollout backward
+    _sched_spec = spec
+    return prev
+
+
+_sched_spec = ""
+set_schedule(_os.environ.get("DRM_B200_SCHEDULE", "heads,prepare,backward"))
 
 
 # CUDA loads a kernel on its first launch (lazy module loading), and that load may have to wait for the device to go idle.
-# A kernel that spins on counters must therefore never be on the device while one of its producers is launched for the
-# first time: the first full forward + backward pass on a device runs in plain stream order (it loads every kernel of the
-# step), the overlapped schedule starts with the second.
+# A kernel that spins on counters must therefore never be on the device while another kernel is launched for the first
+# time.  This library's own kernels are all loaded up front (drm_init, _lib.ensure_init); for everything else a step
+# launches (torch's fill / random / copy kernels) the first full forward + backward pass of every distinct configuration
+# on a device runs in plain stream order, the overlapped schedule starts with the second.
 _WARM = {}
 
 
-def _overlap_ok(device, prec) -> bool:
-    return _WARM.get((device.type, device.index, prec), 0) >= 1
+def _warm_key(device, prec, cfg, pcont) -> tuple:
+    return (device.type, device.index, prec, cfg.act_dist, cfg.dims, cfg.steps, bool(pcont), cfg.n >= 128 * _sm_count(device))
+
+
+def _overlap_ok(key) -> bool:
+    return _WARM.get(key, 0) >= 1
 
 
 def _side_stream(device, k: int = 0) -> "torch.cuda.Stream":
@@ -89,15 +108,18 @@ class _ActorLossFn(torch.autograd.Function):
         # step t overlap the rollout of step t+1 (drm_rollout.step_flags / drm_mlp_call.wait_flags).
         ctx.set_materialize_grads(False)  # 12 by-products: no zero tensors for their (unused) gradients
         flags = tiles = fork = None
-        warm = _overlap_ok(stoch_dev(t), prec)
+        wkey = _warm_key(stoch_dev(t), prec, cfg, pcont_w)
+        warm = _overlap_ok(wkey)
         pipe_heads, prepare = _PIPELINE_HEADS and warm, _PREPARE_BACKWARD and warm
+        if prec == "bf16" and pipe_heads:
+            # zero-filled on the main stream BEFORE the fork: the head kernels on the side streams poll these counters
+            # and must never see the previous pass' values (the block is reused across iterations / graph replays)
+            flags = torch.zeros(H, dtype=torch.int32, device=stoch_dev(t))
         if prec == "bf16" and (pipe_heads or prepare):
             fork = torch.cuda.Event()
             fork.record(torch.cuda.current_stream())  # the side streams branch off BEFORE the rollout is enqueued
         if prec == "bf16":
             tiles = []
-        if prec == "bf16" and pipe_heads:
-            flags = torch.zeros(H, dtype=torch.int32, device=stoch_dev(t))
         save = rollout_forward_raw(cfg, t, rssm, actor, training, step_flags=flags, tiles_out=tiles)
         x0 = t["prior_stoch"].view(H * N, S)
         x1 = t["deter"].view(H * N, D)
@@ -149,7 +171,7 @@ class _ActorLossFn(torch.autograd.Function):
         out = returns_loss_raw(reward.view(H, N), value.view(H, N), None if pc is None else pc.view(H, N), discount,
                                lambda_)
         ctx.pack = (cfg, t, rssm, actor, save, reward_w, value_w, pcont_w, rsave, vsave, psave, out, x0, x1, prec, shared,
-                    plans, tiles[0] if tiles else 0)
+                    plans, tiles[0] if tiles else 0, wkey)
         aux = (t["prior_mean"], t["prior_std"], t["prior_stoch"], t["deter"], t["action_out"], reward.view(H, N, 1),
                value.view(H, N, 1), out["returns"].view(H - 1, N, 1), out["disc"].view(H - 1, N, 1),
                out["losses"][1].clone(), out["d_value_pred"], vsave if vsave is not None else torch.empty(0))
@@ -159,7 +181,7 @@ class _ActorLossFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_loss, *_):
         (cfg, t, rssm, actor, save, reward_w, value_w, pcont_w, rsave, vsave, psave, out, x0, x1, prec, shared,
-         plans, roll_tiles) = ctx.pack
+         plans, roll_tiles, wkey) = ctx.pack
         ctx.pack = None
         if g_loss is None:
             return (None,) * (1 + len(actor))
@@ -185,7 +207,7 @@ class _ActorLossFn(torch.autograd.Function):
         # rollout kernel waits on (step_rows_done / g_wait_flags).  Grids are capped so that all of them are resident.
         free = (_sm_count(g_loss.device) - roll_tiles) // len(heads) if roll_tiles > 0 else 0
         g_wait = None
-        if prec == "bf16" and _PIPELINE_BACKWARD and free >= 16 and _overlap_ok(g_loss.device, prec):
+        if prec == "bf16" and _PIPELINE_BACKWARD and free >= 16 and _overlap_ok(wkey):
             mlp_tiles = (H * N + 127) // 128
             cnt = torch.zeros(len(heads) * mlp_tiles + H, dtype=torch.int32, device=g_loss.device)
             steps_done = cnt[len(heads) * mlp_tiles:]
@@ -229,8 +251,7 @@ class _ActorLossFn(torch.autograd.Function):
             main.wait_stream(hs)
         if follow is not None:
             main.wait_stream(side)
-        key = (g_loss.device.type, g_loss.device.index, prec)
-        _WARM[key] = _WARM.get(key, 0) + 1
+        _WARM[wkey] = _WARM.get(wkey, 0) + 1
         return (None, *gactor)
 
 

@@ -9,7 +9,7 @@ namespace drm {
 
 constexpr int kThreads = 256;          // 8 warps per CTA for the row-tile kernels
 constexpr int kWarps = kThreads / 32;
-constexpr int kNumSM = 148;            // B200
+int num_sms();                         // SMs of the current device (cudaDevAttrMultiProcessorCount, cached per device; 148 on B200)
 constexpr int kMaxSmem = 227 * 1024;   // usable dynamic shared memory per CTA
 
 __host__ __device__ inline int rup(int x, int m) { return (x + m - 1) / m * m; }
@@ -17,6 +17,16 @@ __host__ __device__ inline size_t rup_sz(size_t x, size_t m) { return (x + m - 1
 
 void set_error(const char* fmt, ...);
 int check_device();  // DRM_OK or DRM_E_ARCH / DRM_E_CUDA
+// Forces the CUDA module load of one kernel (lazy loading would otherwise do it at the first launch, which may have to
+// wait for the device to go idle -- something a kernel spinning on device counters never lets happen).
+template <class K>
+inline void warm_kernel(K kernel) {
+    cudaFuncAttributes a;
+    (void)cudaFuncGetAttributes(&a, kernel);
+}
+// per translation unit: load every kernel it defines (drm_init)
+void warm_util(); void warm_mlp(); void warm_mlp_tc(); void warm_wgrad_tc(); void warm_rollout_fwd(); void warm_rollout_bwd();
+void warm_rollout_tc(); void warm_loss(); void warm_optim();
 
 // Diagnostics (drm_launch_count / drm_prof_*): every kernel launch site bumps the counter and,
 // when profiling is on, is bracketed by a cudaEvent pair on the launching stream.
@@ -203,11 +213,12 @@ __device__ __forceinline__ void cta_linear_narrow(const float* __restrict__ W, i
         default: drm::set_error("bad tile height %d", Rv); return DRM_E_SHAPE; \
     }
 
-// Picks the tile height: the smallest supported R that covers ceil(n / kNumSM) rows (so one
+// Picks the tile height: the smallest supported R that covers ceil(n / num_sms()) rows (so one
 // wave of CTAs finishes the job), capped by what fits in shared memory.
 inline int pick_rows(int n, size_t smem_bytes_per_row, size_t smem_fixed) {
     static const int opts[] = {4, 8, 12, 16, 20, 24, 32};
-    int want = (n + kNumSM - 1) / kNumSM;
+    const int sms = num_sms();
+    int want = (n + sms - 1) / sms;
     int best = 0;
     for (int i = 0; i < 7; ++i) {
         int R = opts[i];

@@ -210,6 +210,8 @@ __global__ void __launch_bounds__(256) kl_bwd_kernel(const drm_kl_call c) {
     }
 }
 
+void warm_loss() { warm_kernel(returns_loss_kernel); warm_kernel(returns_loss_reg_kernel<16>); warm_kernel(returns_loss_reg_kernel<32>); warm_kernel(kl_fwd_kernel); warm_kernel(kl_finalize_kernel); warm_kernel(kl_bwd_kernel); }
+
 }  // namespace drm
 
 using namespace drm;
@@ -240,7 +242,7 @@ int drm_kl_fwd(const drm_kl_call* c, void* stream_) {
     int rc = check_device(); if (rc) return rc;
     const size_t total = (size_t)c->M * c->S;
     int grid = (int)((total + 255) / 256);
-    if (grid > 2 * kNumSM) grid = 2 * kNumSM;
+    if (grid > 2 * num_sms()) grid = 2 * num_sms();
     ProfScope prof(PROF_LOSS, stream);
     kl_fwd_kernel<<<grid, 256, 0, stream>>>(*c);
     kl_finalize_kernel<<<1, 1, 0, stream>>>(c->out, c->free_nats);
@@ -256,7 +258,7 @@ int drm_kl_bwd(const drm_kl_call* c, void* stream_) {
     int rc = check_device(); if (rc) return rc;
     const size_t total = (size_t)c->M * c->S;
     int grid = (int)((total + 255) / 256);
-    if (grid > 4 * kNumSM) grid = 4 * kNumSM;
+    if (grid > 4 * num_sms()) grid = 4 * num_sms();
     ProfScope prof(PROF_LOSS, stream);
     kl_bwd_kernel<<<grid, 256, 0, stream>>>(*c);
     DRM_CUDA_OK(cudaGetLastError());

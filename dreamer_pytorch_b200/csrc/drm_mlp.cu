@@ -215,7 +215,7 @@ int launch_wgrad(const float* dY, int64_t ldy, const float* X, int64_t ldx, int 
                  int ld_dw, int koff, float* db, cudaStream_t stream) {
     if (M <= 0 || Nout <= 0 || K <= 0) return DRM_OK;
     const int tn = (Nout + WG_T - 1) / WG_T, tk = (K + WG_T - 1) / WG_T;
-    int splits = (4 * kNumSM + tn * tk - 1) / (tn * tk);
+    int splits = (4 * num_sms() + tn * tk - 1) / (tn * tk);
     const int max_splits = (M + 4 * WG_M - 1) / (4 * WG_M);
     if (splits > max_splits) splits = max_splits;
     if (splits < 1) splits = 1;
@@ -296,7 +296,7 @@ static int launch_mlp_kernel(const MlpDev& p, bool backward, cudaStream_t stream
     DRM_REQUIRE(Rv > 0, DRM_E_SHAPE, "layer too wide for shared memory");
     const size_t smem = per_row * Rv;
     const int tiles = (p.M + Rv - 1) / Rv;
-    const int grid = tiles < 2 * kNumSM ? tiles : 2 * kNumSM;
+    const int grid = tiles < 2 * num_sms() ? tiles : 2 * num_sms();
     ProfScope prof(backward ? PROF_MLP_BWD : PROF_MLP_FWD, stream);
     if (!backward) {
         DRM_DISPATCH_R(Rv, {
@@ -343,6 +343,8 @@ int launch_linear_dx(const float* dy, int M, int nout, const float* W, int w_ld,
     return launch_mlp_kernel(p, true, stream);
 }
 
+void warm_mlp() { warm_kernel(mlp_fwd_kernel<4>); warm_kernel(mlp_fwd_kernel<8>); warm_kernel(mlp_fwd_kernel<12>); warm_kernel(mlp_fwd_kernel<16>); warm_kernel(mlp_fwd_kernel<20>); warm_kernel(mlp_fwd_kernel<24>); warm_kernel(mlp_fwd_kernel<32>); warm_kernel(mlp_bwd_kernel<4>); warm_kernel(mlp_bwd_kernel<8>); warm_kernel(mlp_bwd_kernel<12>); warm_kernel(mlp_bwd_kernel<16>); warm_kernel(mlp_bwd_kernel<20>); warm_kernel(mlp_bwd_kernel<24>); warm_kernel(mlp_bwd_kernel<32>); warm_kernel(wgrad_kernel); }
+
 }  // namespace drm
 
 using namespace drm;
@@ -369,15 +371,17 @@ size_t drm_mlp_workspace_bytes(const drm_mlp_call* c) {
 
 // fp32 path + producer gating: the FFMA kernels do not poll, so one thread waits for the LAST step's flag first
 __global__ void wait_flag_kernel(const int* flag, int target) {
-    unsigned spins = 0;
-    int v;
-    do {
+    unsigned long long t0 = 0;
+    for (;;) {
+        int v;
         asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
-        if (v < target) {
-            __nanosleep(500);
-            if (++spins > (1u << 24)) __trap();
-        }
-    } while (v < target);
+        if (v >= target) return;
+        __nanosleep(500);
+        unsigned long long now;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > 30000000000ull) __trap();  // 30 s: the producer is not running
+    }
 }
 
 int drm_mlp_fwd(const drm_mlp_call* c, void* stream_) {

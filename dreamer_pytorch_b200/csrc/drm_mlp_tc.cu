@@ -139,7 +139,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_fwd_tc_kernel(const __gr
                     int r, q;
                     sv4[u] = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (blk1(part, u, r, q) && row0 + r < p.M)
-                        sv4[u] = __ldg(reinterpret_cast<const float4*>(p.x1 + (size_t)(row0 + r) * p.ld1) + q);
+                        sv4[u] = ldcg4(reinterpret_cast<const float4*>(p.x1 + (size_t)(row0 + r) * p.ld1) + q);  // rows may come from a kernel running beside this one
                 }
             } else {
 #pragma unroll
@@ -147,7 +147,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_fwd_tc_kernel(const __gr
                     int r, q;
                     sv4[u] = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (blk0(u, r, q) && 2 * q < p.k0 && row0 + r < p.M) {
-                        const float2 w = __ldg(reinterpret_cast<const float2*>(p.x0 + (size_t)(row0 + r) * p.ld0) + q);
+                        const float2 w = ldcg2(reinterpret_cast<const float2*>(p.x0 + (size_t)(row0 + r) * p.ld0) + q);
                         sv4[u].x = w.x; sv4[u].y = w.y;
                     }
                 }
@@ -163,8 +163,8 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_fwd_tc_kernel(const __gr
 #pragma unroll
                     for (int i = 0; i < 8; ++i) v[i] = 0.f;
                     if (grow < p.M) {
-                        if (chunk < p.c0) ldg_row8(p.x0 + (size_t)grow * p.ld0, chunk * 8, p.k0, v);
-                        else if (chunk < p.c0 + p.c1) ldg_row8(p.x1 + (size_t)grow * p.ld1, (chunk - p.c0) * 8, p.k1, v);
+                        if (chunk < p.c0) ldcg_row8(p.x0 + (size_t)grow * p.ld0, chunk * 8, p.k0, v);
+                        else if (chunk < p.c0 + p.c1) ldcg_row8(p.x1 + (size_t)grow * p.ld1, (chunk - p.c0) * 8, p.k1, v);
                     }
                     st_chunk_bf16(dst + (size_t)idx * 16, v);
                     if (p.sx) st_chunk_bf16(p.sx + ((size_t)tile * p.cin * kTileRows + idx) * 8, v);
@@ -210,15 +210,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_fwd_tc_kernel(const __gr
                 const int last_row = min(p.M, (tile + 1) * kTileRows) - 1;
                 const int t_hi = min(p.wait_steps - 1, last_row / p.wait_rows);
                 const int* f = p.wait_flags + t_hi;
-                unsigned spins = 0;
-                int v;
-                do {
-                    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
-                    if (v < p.wait_target) {
-                        __nanosleep(200);
-                        if (++spins > (1u << 24)) __trap();  // ~ seconds: the producer is not running
-                    }
-                } while (v < p.wait_target);
+                wait_counter_ge(f, p.wait_target, 200);
             }
             __syncwarp();
             ready_tile = tile;
@@ -373,15 +365,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) mlp_bwd_tc_kernel(const __gr
                 es.wait_acc();
                 if (p.tile_wait) {  // the previous head's rows of this tile (we accumulate into them)
                     if ((threadIdx.x & 31) == 0) {
-                        unsigned spins = 0;
-                        int v;
-                        do {
-                            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p.tile_wait + tile) : "memory");
-                            if (v == 0) {
-                                __nanosleep(100);
-                                if (++spins > (1u << 24)) __trap();  // ~ seconds: the producer is not running
-                            }
-                        } while (v == 0);
+                        wait_counter_ge(p.tile_wait + tile, 1, 100);
                     }
                     __syncwarp();
                 }
@@ -604,7 +588,7 @@ int mlp_tc_fwd(const drm_mlp_call* c, cudaStream_t stream) {
         carve_save(c, pl, d);
     }
     rc = launch_pack_tc(pl.jobs, stream); if (rc) return rc;
-    int cap = kNumSM;
+    int cap = num_sms();
     if (c->max_ctas > 0 && c->max_ctas < cap) cap = c->max_ctas;
     const int grid = pl.tiles < cap ? pl.tiles : cap;
     d.wait_flags = c->wait_flags; d.wait_target = c->wait_target; d.wait_rows = c->wait_rows; d.wait_steps = c->wait_steps;
@@ -657,7 +641,7 @@ int mlp_tc_bwd(const drm_mlp_bwd_call* bc, cudaStream_t stream) {
         if (bc->phase == DRM_PHASE_PREPARE) return DRM_OK;
     }
     {
-        int grid = pl.tiles < kNumSM ? pl.tiles : kNumSM;
+        int grid = pl.tiles < num_sms() ? pl.tiles : num_sms();
         if (c->max_ctas > 0 && c->max_ctas < grid) grid = c->max_ctas;
         DRM_CUDA_OK(cudaFuncSetAttribute(mlp_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
         ProfScope prof(PROF_MLP_BWD, stream);
@@ -691,6 +675,8 @@ int mlp_tc_bwd(const drm_mlp_bwd_call* bc, cudaStream_t stream) {
 }
 
 }  // namespace tc
+void warm_mlp_tc() { warm_kernel(tc::pack_tc_kernel); warm_kernel(tc::mlp_fwd_tc_kernel); warm_kernel(tc::mlp_bwd_tc_kernel); }
+
 }  // namespace drm
 
 #ifdef DRM_TIMELINE

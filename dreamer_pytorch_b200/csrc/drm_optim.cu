@@ -60,6 +60,8 @@ __global__ void __launch_bounds__(kOptThreads) clip_adam_kernel(const drm_clip_a
     }
 }
 
+void warm_optim() { warm_kernel(grad_sumsq_kernel); warm_kernel(clip_adam_kernel); }
+
 }  // namespace drm
 
 extern "C" int drm_clip_adam(const drm_clip_adam_call* c, void* stream_) {

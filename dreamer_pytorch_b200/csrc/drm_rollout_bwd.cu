@@ -277,7 +277,7 @@ int launch_rollout_bwd(const RollDev& p, cudaStream_t stream) {
     DRM_REQUIRE(Rv > 0, DRM_E_SHAPE, "model too wide for shared memory");
     const size_t smem = per_row * Rv;
     const int tiles = (p.n + Rv - 1) / Rv;
-    const int grid = tiles < kNumSM ? tiles : kNumSM;
+    const int grid = tiles < num_sms() ? tiles : num_sms();
     ProfScope prof(PROF_ROLLOUT_BWD, stream);
     DRM_DISPATCH_R(Rv, {
         DRM_CUDA_OK(cudaFuncSetAttribute(rollout_bwd_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -286,5 +286,7 @@ int launch_rollout_bwd(const RollDev& p, cudaStream_t stream) {
     DRM_CUDA_OK(cudaGetLastError());
     return DRM_OK;
 }
+
+void warm_rollout_bwd() { warm_kernel(rollout_bwd_kernel<4>); warm_kernel(rollout_bwd_kernel<8>); warm_kernel(rollout_bwd_kernel<12>); warm_kernel(rollout_bwd_kernel<16>); warm_kernel(rollout_bwd_kernel<20>); warm_kernel(rollout_bwd_kernel<24>); warm_kernel(rollout_bwd_kernel<32>); }
 
 }  // namespace drm

@@ -272,7 +272,7 @@ int launch_rollout_fwd(const RollDev& p, cudaStream_t stream) {
     DRM_REQUIRE(Rv > 0, DRM_E_SHAPE, "model too wide for shared memory");
     const size_t smem = per_row * Rv;
     const int tiles = (p.n + Rv - 1) / Rv;
-    const int grid = tiles < kNumSM ? tiles : kNumSM;
+    const int grid = tiles < num_sms() ? tiles : num_sms();
     ProfScope prof(PROF_ROLLOUT_FWD, stream);
     DRM_DISPATCH_R(Rv, {
         DRM_CUDA_OK(cudaFuncSetAttribute(rollout_fwd_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -281,5 +281,7 @@ int launch_rollout_fwd(const RollDev& p, cudaStream_t stream) {
     DRM_CUDA_OK(cudaGetLastError());
     return DRM_OK;
 }
+
+void warm_rollout_fwd() { warm_kernel(rollout_fwd_kernel<4>); warm_kernel(rollout_fwd_kernel<8>); warm_kernel(rollout_fwd_kernel<12>); warm_kernel(rollout_fwd_kernel<16>); warm_kernel(rollout_fwd_kernel<20>); warm_kernel(rollout_fwd_kernel<24>); warm_kernel(rollout_fwd_kernel<32>); }
 
 }  // namespace drm

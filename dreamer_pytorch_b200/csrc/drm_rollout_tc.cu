@@ -580,15 +580,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_bwd_tc_kernel(const 
             auto fetch_prior = [&](int t2) {
                 if (p.g_wait_flags) {  // the head kernels producing g_* run beside this one (drm_rollout_grad.g_wait_flags)
                     if (lane == 0) {
-                        unsigned spins = 0;
-                        int v;
-                        do {
-                            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p.g_wait_flags + t2) : "memory");
-                            if (v < p.g_wait_target) {
-                                __nanosleep(100);
-                                if (++spins > (1u << 24)) __trap();  // ~ seconds: the producer is not running
-                            }
-                        } while (v < p.g_wait_target);
+                        wait_counter_ge(p.g_wait_flags + t2, p.g_wait_target, 100);
                     }
                     __syncwarp();
                 }
@@ -915,7 +907,7 @@ static int tile_rows_for(int n) {
     const int forced = e ? atoi(e) : 0;
     if (forced == 64 || forced == 128) return forced;
     const int t128 = (n + 127) / 128;
-    return t128 < kNumSM ? 64 : 128;
+    return t128 < num_sms() ? 64 : 128;
 }
 static size_t tcm_bytes_r(int tr, size_t tiles, int chunks) { return tiles * (size_t)chunks * tr * 16; }
 
@@ -1082,7 +1074,7 @@ int rollout_tc_fwd(const drm_rollout* r, cudaStream_t stream) {
     RollTcDev& d = pl.dev;
     fill_io_tc(r, d);
     d.wstream = ws;
-    const int grid = d.ntiles < kNumSM ? d.ntiles : kNumSM;
+    const int grid = d.ntiles < num_sms() ? d.ntiles : num_sms();
     if (r->training) {
         DRM_REQUIRE(r->save && r->save_bytes >= rollout_tc_save_bytes(r), DRM_E_WORKSPACE, "save buffer too small (bf16 rollout)");
         RollTcDev carved;
@@ -1191,7 +1183,7 @@ static size_t carve_bwd_ws(const RollTcDev& dd, size_t wbytes, uint8_t* base, Ro
     };
     RollTcDev tmp = dd;
     for (int l = 0; l < dd.an; ++l) tmp.dys_a[l] = (__nv_bfloat16*)take(tcm_bytes_r(dd.tr, TS, l == dd.an - 1 ? 2 : dd.cha));
-    const int grid = dd.ntiles < kNumSM ? dd.ntiles : kNumSM;
+    const int grid = dd.ntiles < num_sms() ? dd.ntiles : num_sms();
     tmp.stash = (__nv_bfloat16*)take((size_t)grid * 2 * dd.cdp * (dd.tr * 16));
     tmp.bwd_flags = (int*)take(sizeof(int) * dd.T);
     if (out) *out = tmp;
@@ -1250,7 +1242,7 @@ int rollout_tc_bwd(const drm_rollout* r, const drm_rollout_grad* g, cudaStream_t
     // Both grids must be resident, and a waiting weight-gradient CTA (64-row images: 49 KB, 256 TMEM columns) must never share
     // an SM with a rollout CTA, whose TMEM allocation it could block: the rollout's shared memory has to exclude that.
     const bool excl = pl.smem_bytes + 50 * 1024 > (size_t)kMaxSmem;
-    if (want_actor && g->wgrad_stream && g->phase == DRM_PHASE_RUN && d.ntiles + 16 <= kNumSM && excl) {
+    if (want_actor && g->wgrad_stream && g->phase == DRM_PHASE_RUN && d.ntiles + 16 <= num_sms() && excl) {
         wg_stream = (cudaStream_t)g->wgrad_stream;
         d.bwd_flags = flags;
     }
@@ -1259,7 +1251,7 @@ int rollout_tc_bwd(const drm_rollout* r, const drm_rollout_grad* g, cudaStream_t
         if (g->phase == DRM_PHASE_PREPARE) return DRM_OK;
     }
     {
-        const int grid = d.ntiles < kNumSM ? d.ntiles : kNumSM;
+        const int grid = d.ntiles < num_sms() ? d.ntiles : num_sms();
         ProfScope prof(PROF_ROLLOUT_BWD, stream);
         if (d.tr == 64) {
             DRM_CUDA_OK(cudaFuncSetAttribute(rollout_bwd_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
@@ -1297,7 +1289,7 @@ int rollout_tc_bwd(const drm_rollout* r, const drm_rollout_grad* g, cudaStream_t
             // row tiles in reverse time order, each gated by its step's counter; the grid must be resident BESIDE the rollout
             wg.wait_flags = d.bwd_flags; wg.wait_target = d.ntiles;
             wg.tiles_per_step = d.ntiles; wg.reverse = 1;
-            slots = (kNumSM - d.ntiles) * (d.tr == 64 ? 2 : 1);
+            slots = (num_sms() - d.ntiles) * (d.tr == 64 ? 2 : 1);
         }
         wgrad_tc_plan(wg, slots);
         rc = launch_wgrad_tc(wg, wg_stream); if (rc) return rc;
@@ -1313,11 +1305,16 @@ int rollout_tc_tiles(const drm_rollout* r) {
 size_t rollout_tc_fwd_workspace_bytes(const drm_rollout* r) {
     RollTcPlan pl;
     if (!rollout_tc_supported(r) || plan_fwd(r, nullptr, pl) != DRM_OK) return 0;
-    const int grid = pl.dev.ntiles < kNumSM ? pl.dev.ntiles : kNumSM;
-    return rup_sz(pl.wbytes, 256) + tcm_bytes_r(pl.dev.tr, (size_t)kNumSM, pl.dev.cdp) + 1024;
+    const int grid = pl.dev.ntiles < num_sms() ? pl.dev.ntiles : num_sms();
+    return rup_sz(pl.wbytes, 256) + tcm_bytes_r(pl.dev.tr, (size_t)num_sms(), pl.dev.cdp) + 1024;
 }
 
 }  // namespace tc
+void warm_rollout_tc() {
+    warm_kernel(tc::rollout_fwd_tc_kernel<64>); warm_kernel(tc::rollout_fwd_tc_kernel<128>);
+    warm_kernel(tc::rollout_bwd_tc_kernel<64>); warm_kernel(tc::rollout_bwd_tc_kernel<128>);
+}
+
 }  // namespace drm
 
 #ifdef DRM_TIMELINE

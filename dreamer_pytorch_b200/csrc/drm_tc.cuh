@@ -60,6 +60,23 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     }
 }
 
+// Spin until a device counter written by ANOTHER kernel (running beside this one) reaches `target`.  Acquire load +
+// back-off; bounded by TIME (30 s of %globaltimer), not by a poll count: a producer that is merely slow (time-slicing,
+// a profiler, a debugger) must not poison the context, a producer that is not running at all must not hang the GPU.
+__device__ __forceinline__ void wait_counter_ge(const int* flag, int target, unsigned backoff_ns) {
+    unsigned long long t0 = 0;
+    for (;;) {
+        int v;
+        asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+        if (v >= target) return;
+        __nanosleep(backoff_ns);
+        unsigned long long now;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > 30000000000ull) __trap();
+    }
+}
+
 // ---------------------------------------------------------------------------------------------- proxies / fences
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before_sync() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }

@@ -360,6 +360,40 @@ __device__ __forceinline__ void ldg_row8(const float* __restrict__ row, int k, i
     for (int i = 0; i < 8; ++i) v[i] = (k + i < kvalid) ? __ldg(src + i) : 0.f;
 }
 
+// Coherent (L2) loads for rows that ANOTHER kernel running beside this one may still be writing when this kernel
+// starts (producer / consumer gating through device counters): `ld.global.nc` (__ldg) requires the data to be read-only
+// for the whole lifetime of the kernel, which does not hold there.  .cg caches in L2 only, the point of coherence.
+__device__ __forceinline__ float4 ldcg4(const float4* p) {
+    float4 v;
+    asm volatile("ld.global.cg.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ float2 ldcg2(const float2* p) {
+    float2 v;
+    asm volatile("ld.global.cg.v2.f32 {%0,%1}, [%2];" : "=f"(v.x), "=f"(v.y) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ float ldcg1(const float* p) {
+    float v;
+    asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+    return v;
+}
+// ldg_row8 with coherent loads
+__device__ __forceinline__ void ldcg_row8(const float* row, int k, int kvalid, float (&v)[8]) {
+    const float* src = row + k;
+    if (k + 8 <= kvalid) {
+        const uintptr_t a = reinterpret_cast<uintptr_t>(src);
+        if ((a & 15) == 0) {
+            const float4 lo = ldcg4(reinterpret_cast<const float4*>(src));
+            const float4 hi = ldcg4(reinterpret_cast<const float4*>(src) + 1);
+            v[0] = lo.x; v[1] = lo.y; v[2] = lo.z; v[3] = lo.w; v[4] = hi.x; v[5] = hi.y; v[6] = hi.z; v[7] = hi.w;
+            return;
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] = (k + i < kvalid) ? ldcg1(src + i) : 0.f;
+}
+
 // row[k .. k+8) (=|+=) v[0..8) for the columns below kvalid, widest aligned accesses possible.
 __device__ __forceinline__ void stg_row8(float* row, int k, int kvalid, const float (&v)[8], bool accumulate) {
     float* dst = row + k;

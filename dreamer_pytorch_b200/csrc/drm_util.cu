@@ -32,6 +32,18 @@ int check_device() {
     return DRM_OK;
 }
 
+int num_sms() {
+    static int cached_dev = -1, cached = 148;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return cached;
+    if (dev != cached_dev) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0) cached = n;
+        cached_dev = dev;
+    }
+    return cached;
+}
+
 // ---------------------------------------------------------------------------------------------
 // launch counter + optional per-kernel CUDA-event timing
 // ---------------------------------------------------------------------------------------------
@@ -83,11 +95,27 @@ int launch_pack(const PackJobs& jobs, cudaStream_t stream) {
     return DRM_OK;
 }
 
+void warm_util() { warm_kernel(pack_kernel); }
+
 }  // namespace drm
 
 extern "C" {
 
 int drm_version(void) { return DRM_ABI_VERSION; }
+
+int drm_init(void) {
+    int rc = drm::check_device(); if (rc) return rc;
+    static int done_dev = -1;
+    int dev = 0;
+    DRM_CUDA_OK(cudaGetDevice(&dev));
+    if (dev == done_dev) return DRM_OK;
+    drm::warm_util(); drm::warm_mlp(); drm::warm_mlp_tc(); drm::warm_wgrad_tc(); drm::warm_rollout_fwd();
+    drm::warm_rollout_bwd(); drm::warm_rollout_tc(); drm::warm_loss(); drm::warm_optim();
+    DRM_CUDA_OK(cudaGetLastError());
+    done_dev = dev;
+    return DRM_OK;
+}
+int drm_num_sms(void) { return drm::num_sms(); }
 const char* drm_last_error(void) { return drm::g_err; }
 
 unsigned long long drm_launch_count(void) { return drm::g_launches; }

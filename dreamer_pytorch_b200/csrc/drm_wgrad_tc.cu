@@ -103,15 +103,7 @@ __global__ void __launch_bounds__(kWgThreads, 2) wgrad_tc_kernel(const __grid_co
                 const int tile = w.reverse ? w.row_tiles - 1 - tile_i : tile_i;
                 if (w.wait_flags) {  // the producer of the images runs beside this kernel
                     const int* f = w.wait_flags + tile / w.tiles_per_step;
-                    unsigned spins = 0;
-                    int v;
-                    do {
-                        asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
-                        if (v < w.wait_target) {
-                            __nanosleep(200);
-                            if (++spins > (1u << 24)) __trap();  // ~ seconds: the producer is not running
-                        }
-                    } while (v < w.wait_target);
+                    wait_counter_ge(f, w.wait_target, 200);
                     asm volatile("fence.proxy.async;" ::: "memory");  // generic-proxy writes of the producer -> bulk copies
                 }
                 uint8_t* A = smem + 1024 + stage * stage_bytes;
@@ -198,7 +190,7 @@ void wgrad_tc_plan(WgParams& w, int slots) {
     // row-tile splits: at most two CTAs per SM in total (one wave of co-resident pairs with 64-row tiles, two full waves
     // with 128-row tiles -- never a third, nearly empty one), but keep >= 4 row tiles per CTA
     // (measured at 2 500 x 15: flat between one and two CTAs per SM, slower outside)
-    if (slots <= 0) slots = 2 * kNumSM;
+    if (slots <= 0) slots = 2 * num_sms();
     int splits = base > 0 ? slots / base : 1;
     const int max_splits = (w.row_tiles + 3) / 4;
     if (splits > max_splits) splits = max_splits;
@@ -225,4 +217,6 @@ int launch_wgrad_tc(const WgParams& w, cudaStream_t stream) {
 }
 
 }  // namespace tc
+void warm_wgrad_tc() { warm_kernel(tc::wgrad_tc_kernel); }
+
 }  // namespace drm

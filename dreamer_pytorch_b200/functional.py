@@ -24,6 +24,7 @@ RAW_INIT_STD = math.log(math.exp(5.0) - 1.0)
 
 
 def _stream():
+    _lib.ensure_init()
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
@@ -39,6 +40,18 @@ def _f32c(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
     if t.dtype != torch.float32:
         t = t.float()
     return t.contiguous()
+
+
+def flat_like(tensors: Sequence[torch.Tensor]) -> List[torch.Tensor]:
+    """Fresh fp32 tensors shaped like `tensors`, carved as 16-byte aligned views out of ONE flat buffer (``out[0]._base``):
+    the gradient bucket of an optimizer group.  The <= 3 padding floats between pieces are never read."""
+    sizes = [(w.numel() + 3) // 4 * 4 for w in tensors]
+    flat = torch.empty(sum(sizes), dtype=torch.float32, device=tensors[0].device)
+    out, o = [], 0
+    for w, n in zip(tensors, sizes):
+        out.append(flat[o:o + w.numel()].view(w.shape))
+        o += n
+    return out
 
 
 def _prec(mode):
@@ -205,7 +218,7 @@ def rollout_backward_raw(cfg: RolloutCfg, t: dict, rssm, actor, save, gouts: dic
         g.want_actor_grad = 1 if want_actor else 0
         gactor = None
         if want_actor:
-            gactor = [torch.empty_like(w) for w in actor]
+            gactor = flat_like(actor)  # views of ONE flat bucket (gactor[0]._base): a single collective averages them
             for l in range(len(actor) // 2):
                 g.actor.dW[l], g.actor.db[l] = gactor[2 * l].data_ptr(), gactor[2 * l + 1].data_ptr()
         if plan is not None:
@@ -343,13 +356,8 @@ def mlp_backward_raw(x0, x1, weights, save, dy, dy_scale=None, dx0=None, dx1=Non
         b.want_wgrad = 1 if want_wgrad else 0
         grads = None
         if want_wgrad:
-            # views of one flat buffer (16-byte aligned pieces): a caller can rescale all of them with one kernel
-            sizes = [(w.numel() + 3) // 4 * 4 for w in weights]
-            flat = torch.empty(sum(sizes), dtype=torch.float32, device=x0.device)
-            grads, o = [], 0
-            for w, n in zip(weights, sizes):
-                grads.append(flat[o:o + w.numel()].view(w.shape))
-                o += n
+            # views of one flat buffer (16-byte aligned pieces): a caller can rescale / all-reduce all of them at once
+            grads = flat_like(weights)
             for l in range(len(weights) // 2):
                 b.grad.dW[l], b.grad.db[l] = grads[2 * l].data_ptr(), grads[2 * l + 1].data_ptr()
         if plan is not None:

@@ -24,12 +24,17 @@ from .dropin.rnns import RSSMState
 
 class ImaginationGraph:
     def __init__(self, model, n_states: int, horizon: int, discount: float = 0.99, discount_lambda: float = 0.95,
-                 use_pcont: bool = False, warmup: int = 3, actor_opt=None, value_opt=None):
+                 use_pcont: bool = False, warmup: int = 3, actor_opt=None, value_opt=None, allreduce: bool = False):
         """actor_opt / value_opt: optional ``optim.ClipAdam(..., capturable=True)`` over the action decoder's / the value
         model's parameters.  Their step() (clip_grad_norm_ + Adam, dreamer_algo.py:182-194) is then recorded behind the
         backward pass, so that one replay is one whole actor + value update.  Parameters and optimizer state are restored
         after the warm-up passes; single-process only (with several ranks the gradient all-reduce sits between the
-        backward pass and the optimizers: keep them outside the graph there)."""
+        backward pass and the optimizers).
+        allreduce: with torch.distributed initialised, average the two gradient buckets (actor, value: one flat fp32 buffer
+        each, the tensors the backward kernels write into) over all ranks INSIDE the graph -- two NCCL all-reduces recorded
+        behind the backward pass, no Python between the backward kernels and the collective; the optimizers, when given,
+        are recorded behind them, so one replay is one whole data-parallel update.  ``allreduce_in_graph`` tells whether the
+        collectives were captured (False: capture of NCCL failed on this build, the caller all-reduces after ``step``)."""
         p0 = next(model.parameters())
         if not p0.is_cuda:
             raise RuntimeError("ImaginationGraph needs a CUDA model (there is no CPU fallback)")
@@ -41,6 +46,10 @@ class ImaginationGraph:
         self.actor_params = list(model.action_decoder.parameters())
         self.value_params = list(model.value_model.parameters())
         self.params = self.actor_params + self.value_params
+        import torch.distributed as dist
+
+        self._dist = dist if (allreduce and dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1) else None
+        self.allreduce_in_graph = self._dist is not None
         self.opts = [(o, ps) for o, ps in ((actor_opt, self.actor_params), (value_opt, self.value_params)) if o is not None]
         for o, ps in self.opts:
             if getattr(o, "step_dev", None) is None:
@@ -59,18 +68,29 @@ class ImaginationGraph:
                 self._eager()
         cur.wait_stream(s)
         torch.cuda.synchronize(dev)
-        self.graph = torch.cuda.CUDAGraph()
         lib = _lib.load()
-        n0 = lib.drm_launch_count()
-        with torch.cuda.graph(self.graph):
-            self.actor_loss, self.value_loss, self.grads = self._eager()
-            self.losses = torch.stack([self.actor_loss, self.value_loss])  # [2], one device->host read per step
-        self.launches_per_replay = int(lib.drm_launch_count() - n0)  # kernels of this library inside the graph
+        try:
+            self._capture(lib)
+        except Exception:
+            if self._dist is None:
+                raise
+            # this torch / NCCL build cannot record the collective: capture the step without it
+            self._dist, self.allreduce_in_graph = None, False
+            torch.cuda.synchronize(dev)
+            self._capture(lib)
         for p, g in zip(self.params, self.grads):
             p.grad = g  # static tensors from the graph's pool, refreshed by every replay
         with torch.no_grad():
             for t, saved in keep:
                 t.copy_(saved)
+
+    def _capture(self, lib):
+        self.graph = torch.cuda.CUDAGraph()
+        n0 = lib.drm_launch_count()
+        with torch.cuda.graph(self.graph):
+            self.actor_loss, self.value_loss, self.grads = self._eager()
+            self.losses = torch.stack([self.actor_loss, self.value_loss])  # [2], one device->host read per step
+        self.launches_per_replay = int(lib.drm_launch_count() - n0)  # kernels of this library inside the graph
 
     def _eager(self):
         start = RSSMState(self.stoch, self.stoch, self.stoch, self.deter)  # mean / std of a start state are never read
@@ -80,6 +100,16 @@ class ImaginationGraph:
         ga = torch.autograd.grad(actor_loss, self.actor_params)
         gv = torch.autograd.grad(value_loss, self.value_params)
         grads = list(ga) + list(gv)
+        if self._dist is not None:
+            # equal shards: the mean of the shard means is the global mean.  Each group's gradients are
+            # views of one flat bucket written by the backward kernels themselves (functional.flat_like).
+            for group in (ga, gv):
+                base = group[0]._base
+                if base is not None and all(g._base is base for g in group):
+                    self._dist.all_reduce(base, op=self._dist.ReduceOp.AVG)
+                else:
+                    for g in group:
+                        self._dist.all_reduce(g, op=self._dist.ReduceOp.AVG)
         if self.opts:
             for p, g in zip(self.params, grads):
                 p.grad = g

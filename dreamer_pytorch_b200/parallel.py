@@ -67,10 +67,22 @@ def allreduce_grads(groups: Iterable[Sequence[torch.Tensor]], weight: float = 1.
         return []
     world = dist.get_world_size()
     groups = [[p for p in params] for params in groups]
-    if fuse:
+    if fuse and not all(_shared_bucket(params) is not None for params in groups):
         groups = [[p for params in groups for p in params]]
     pending = []
     for params in groups:
+        base = _shared_bucket(params)
+        if base is not None and weight == 1.0:
+            # the backward kernels wrote these gradients into ONE flat bucket (functional.flat_like): average it in place
+            work = dist.all_reduce(base, op=dist.ReduceOp.AVG if dist.get_backend() == "nccl" else dist.ReduceOp.SUM,
+                                   async_op=async_op)
+            if dist.get_backend() != "nccl":
+                if work is not None:
+                    work.wait()
+                    work = None
+                base.div_(world)
+            pending.append((work, None, params))
+            continue
         flat = flatten_grads(params)
         flat.mul_(weight / world)
         work = dist.all_reduce(flat, op=dist.ReduceOp.SUM, async_op=async_op)
@@ -81,8 +93,23 @@ def allreduce_grads(groups: Iterable[Sequence[torch.Tensor]], weight: float = 1.
     return pending
 
 
+def _shared_bucket(params: Sequence[torch.Tensor]):
+    """The flat buffer all gradients of `params` are views of, or None."""
+    base = None
+    for p in params:
+        g = p.grad
+        if g is None or g._base is None or g.dtype != torch.float32:
+            return None
+        if base is None:
+            base = g._base
+        elif g._base is not base:
+            return None
+    return base
+
+
 def finish_allreduce(pending) -> None:
     for work, flat, params in pending:
         if work is not None:
             work.wait()
-        unflatten_into_grads(flat, params)
+        if flat is not None:
+            unflatten_into_grads(flat, params)

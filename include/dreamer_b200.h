@@ -129,7 +129,9 @@ typedef struct drm_rollout {
     size_t save_bytes;
     void* workspace;    /* drm_rollout_workspace_bytes(); contents undefined after the call */
     size_t workspace_bytes;
-    /* optional (POLICY, may be NULL): int32 [steps], zeroed by the caller.  The forward adds 1 to step_flags[t]
+    /* optional (POLICY, may be NULL): int32 [steps], zeroed by the caller -- and the zero-fill must be stream-ordered
+       BEFORE the launch of every consumer that polls the flags (a consumer on another stream waits on an event
+       recorded after the fill), or it can see the previous pass' counts.  The forward adds 1 to step_flags[t]
        (device-scope release) whenever one row tile has stored every output of step t, so that a consumer kernel
        running BESIDE the rollout (drm_mlp_call.wait_flags) can start on step t while step t+1 is computed.
        drm_rollout_tiles() is the count each flag reaches. */
@@ -242,6 +244,12 @@ typedef struct drm_kl_call {
 } drm_kl_call;
 
 int drm_version(void);
+/* Once per device, before the first compute call (the ctypes binding does it at load time): checks the architecture and
+ * loads every kernel of the library (CUDA would otherwise load a kernel lazily at its first launch, and that load may
+ * wait for the device to go idle -- which a kernel spinning on the counters of a producer never lets happen). */
+int drm_init(void);
+/* SMs of the current device: the co-residency budget of kernels that run beside each other (max_ctas, wgrad_stream). */
+int drm_num_sms(void);
 const char* drm_last_error(void);
 size_t drm_sizeof(const char* struct_name); /* ABI self-check for FFI bindings */
 

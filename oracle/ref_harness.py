@@ -1,8 +1,12 @@
-"""Drives the UNMODIFIED reference (imported from /root/reference) -- TEST INFRASTRUCTURE ONLY.
+"""Drives the UNMODIFIED reference -- TEST / BASELINE INFRASTRUCTURE ONLY.
 
-Used in the build container to (a) validate ``oracle/dreamer_oracle.py`` and (b) generate the golden
-fixtures under ``tests/golden/`` (``oracle/make_golden.py``).  ``/root/reference`` does not exist on
-the GPU box; nothing that runs there imports this module.
+The reference is imported from ``/root/reference`` (build container) or, where that does not exist (the
+GPU box), from the git-ignored copy ``oracle/_ref/`` that ``oracle/fetch_ref.py`` makes and that travels
+with the tree.  Used to (a) validate ``oracle/dreamer_oracle.py``, (b) generate the golden fixtures under
+``tests/golden/`` (``oracle/make_golden.py``), (c) time the reference itself on the host cores and on
+CUDA eager (``bench.py``: ``--impl reference``, ``cpu_baseline``, ``reference_cuda``) and (d) run the
+reference's own ``Dreamer.loss`` on the drop-in modules (``tests/test_reference_algo_gpu.py``).
+The product never imports this module.
 
 Noise injection follows SURVEY.md section 8(c): ``torch.distributions.normal._standard_normal`` is
 patched to pop pre-generated tensors in the reference's own draw order; the categorical samplers
@@ -17,7 +21,19 @@ import types
 
 import torch
 
-REF_ROOT = os.environ.get("DREAMER_REFERENCE_ROOT", "/root/reference")
+_LOCAL_COPY = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+
+
+def _find_root() -> str:
+    env = os.environ.get("DREAMER_REFERENCE_ROOT")
+    if env:
+        return env
+    if os.path.isdir("/root/reference/dreamer"):
+        return "/root/reference"
+    return _LOCAL_COPY
+
+
+REF_ROOT = _find_root()
 
 
 def reference_available() -> bool:
@@ -169,3 +185,108 @@ def reference_rollouts(model, obs_embed, action, noise, horizon, dist, use_pcont
     with injected_noise(nq, gq):
         imag, actions = model.rollout.rollout_policy(horizon, model.policy, flat)
     return prior, post, imag, actions
+
+
+# ------------------------------------------------------------------------------------------------
+# timing harnesses (bench.py): the reference's own modules, on the host cores or on CUDA eager
+# ------------------------------------------------------------------------------------------------
+def set_as_shipped(on: bool):
+    """as shipped: autograd anomaly mode on (dreamer_algo.py:16) and distribution argument validation on (torch
+    default); best case: both off."""
+    torch.autograd.set_detect_anomaly(bool(on))
+    torch.distributions.Distribution.set_default_validate_args(bool(on))
+
+
+def default_reference_model(A, dist, use_pcont=False, device="cpu", seed=0, **model_kwargs):
+    """Reference ``AtariDreamerModel`` with its own default init (SURVEY 8(d) config recipes)."""
+    agent, _ = import_reference()
+    torch.manual_seed(seed)
+    model = agent.AtariDreamerModel(action_shape=(A,), action_dist=dist, use_pcont=use_pcont, **model_kwargs)
+    return model.to(device).train()
+
+
+def reference_algo(model, B, T, horizon, use_pcont=False, device="cpu", **algo_kwargs):
+    """A reference ``Dreamer`` wired to ``model`` without sampler / runner."""
+    _, algo_mod = import_reference()
+    algo = algo_mod.Dreamer(batch_size=B, batch_length=T, horizon=horizon, use_pcont=use_pcont, log_video=False,
+                            **algo_kwargs)
+    algo.agent = types.SimpleNamespace(model=model, device=torch.device(device))
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        algo.optim_initialize()
+    torch.autograd.set_detect_anomaly(False)
+    return algo
+
+
+def imagination_step_fn(model, algo, flat_post):
+    """The actor / value block of ``Dreamer.loss`` (dreamer_algo.py:283-337) on the reference's OWN modules, then
+    ``actor_loss.backward()`` and ``value_loss.backward()`` (dreamer_algo.py:176-180) -- the metric's "step".
+    flat_post: reference RSSMState [N, .] (detached start states)."""
+    import_reference()
+    from dreamer.models.rnns import get_feat
+    from dreamer.utils.module import FreezeParameters
+
+    params = list(model.action_decoder.parameters()) + list(model.value_model.parameters())
+
+    def step():
+        for p in params:
+            p.grad = None
+        with FreezeParameters(algo.model_modules):  # :293-296
+            imag_dist, _ = model.rollout.rollout_policy(algo.horizon, model.policy, flat_post)
+        imag_feat = get_feat(imag_dist)  # :299
+        with FreezeParameters(algo.model_modules + algo.value_modules):  # :305-307
+            imag_reward = model.reward_model(imag_feat).mean
+            value = model.value_model(imag_feat).mean
+        if algo.use_pcont:  # :309-313
+            with FreezeParameters([model.pcont]):
+                discount_arr = model.pcont(imag_feat).mean
+        else:
+            discount_arr = algo.discount * torch.ones_like(imag_reward)
+        returns = algo.compute_return(imag_reward[:-1], value[:-1], discount_arr[:-1], bootstrap=value[-1],
+                                      lambda_=algo.discount_lambda)  # :314-320
+        discount_arr = torch.cat([torch.ones_like(discount_arr[:1]), discount_arr[1:]])  # :322
+        discount = torch.cumprod(discount_arr[:-1], 0)
+        actor_loss = -torch.mean(discount * returns)  # :324
+        with torch.no_grad():  # :331-334
+            value_feat = imag_feat[:-1].detach()
+            value_discount = discount.detach()
+            value_target = returns.detach()
+        value_pred = model.value_model(value_feat)
+        log_prob = value_pred.log_prob(value_target)
+        value_loss = -torch.mean(value_discount * log_prob.unsqueeze(2))  # :337
+        actor_loss.backward()
+        value_loss.backward()
+        return actor_loss.detach(), value_loss.detach()
+
+    return step
+
+
+def synthetic_samples(A, dist, B, T, device="cpu", seed=1):
+    """SamplesFromReplay of SURVEY 8(d) config 2 / 3 shapes."""
+    import_reference()
+    from rlpyt.replays.sequence.n_step import SamplesFromReplay
+
+    g = torch.Generator().manual_seed(seed)
+    obs = torch.randint(0, 256, (T + 1, B, 3, 64, 64), generator=g, dtype=torch.uint8)
+    if dist == "tanh_normal":
+        act = torch.rand(T + 1, B, A, generator=g) * 2 - 1
+    else:
+        act = torch.nn.functional.one_hot(torch.randint(0, A, (T + 1, B), generator=g), A).float()
+    rew = torch.randn(T + 1, B, generator=g)
+    done = torch.rand(T, B, generator=g) < 0.01
+    return SamplesFromReplay(all_observation=obs.to(device), all_action=act.to(device), all_reward=rew.to(device),
+                             return_=None, done=done.to(device), done_n=None, init_rnn_state=None)
+
+
+def full_loss_step_fn(model, algo, samples):
+    """The reference's whole ``Dreamer.loss`` + the three backwards of ``optimize_agent`` (dreamer_algo.py:174-180)."""
+    def step():
+        model.zero_grad(set_to_none=True)
+        model_loss, actor_loss, value_loss, _ = algo.loss(samples, 0, 0)
+        model_loss.backward()
+        actor_loss.backward()
+        value_loss.backward()
+        return model_loss.detach(), actor_loss.detach(), value_loss.detach()
+
+    return step

@@ -75,7 +75,7 @@ def test_kernels_beside_each_other_match_stream_order(use_pcont):
     with precision("bf16"):  # the first pass on a device always runs in plain stream order (algo._WARM): get it out of the way
         al, vl, _ = algo.imagination_losses(model, RSSMState(stoch, stoch, stoch, deter), H, use_pcont=use_pcont)
         al.backward(); vl.backward()
-    assert algo._overlap_ok(dev, "bf16")
+    assert any(k[:3] == ("cuda", 0, "bf16") and algo._overlap_ok(k) for k in algo._WARM)
     res = {}
     flags = ("_PIPELINE_HEADS", "_PREPARE_BACKWARD", "_PIPELINE_BACKWARD")
     old = {k: getattr(algo, k) for k in flags}
