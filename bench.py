@@ -360,14 +360,20 @@ def time_full_paths(w, dev, precision, reps=10):
     rew = torch.randn(T, B, 1, generator=g).to(dev)
     done = (torch.rand(T, B, 1, generator=g) < 0.01).to(dev)
     out = {}
-    for key, kw in (("t_full", dict(observation=None, obs_embed=embed)), ("full_update", dict(observation=obs))):
+    from dreamer_pytorch_b200.precision import conv_mode, get_conv_mode
+
+    cases = [("t_full", dict(observation=None, obs_embed=embed), get_conv_mode()),
+             ("full_update", dict(observation=obs), get_conv_mode())]
+    if precision == "bf16":
+        cases.append(("full_update_conv_bf16", dict(observation=obs), "bf16"))
+    for key, kw, cmode in cases:
         def run():
             model.zero_grad(set_to_none=True)
             ml, al, vl, _ = dreamer_loss(model, kw["observation"], act, rew, done, horizon=H, use_pcont=w["use_pcont"],
                                          obs_embed=kw.get("obs_embed"))
             ml.backward(); al.backward(); vl.backward()
         ts = []
-        with prec_ctx(precision):
+        with prec_ctx(precision), conv_mode(cmode):
             for i in range(reps + 3):
                 torch.cuda.synchronize()
                 a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -378,6 +384,7 @@ def time_full_paths(w, dev, precision, reps=10):
         ms = statistics.median(ts)
         n_imag = ((T - 1) * B if w["use_pcont"] else T * B) * H
         out[key] = dict(ms=ms, imagined_states_per_s=n_imag / (ms * 1e-3), observed_states=T * B, launch="eager",
+                        conv=cmode if key != "t_full" else None,
                         what=("rollout_representation + KL + reward loss + imagination, 3 backwards; conv excluded (synthetic "
                               "obs_embed)") if key == "t_full" else
                              "whole Dreamer.loss incl. conv encoder/decoder + image log-prob, 3 backwards")

@@ -103,10 +103,27 @@ class drm_clip_adam_call(C.Structure):
                 + [(k, C.c_float) for k in ("max_norm", "beta1", "beta2", "eps", "one_minus_beta1", "one_minus_beta2", "step_size", "bias2_sqrt")]
                 + [("lr", C.c_float), ("pad2_", C.c_int32), ("beta1_d", C.c_double), ("beta2_d", C.c_double), ("step_dev", P)]
                 + [(k, P * 64) for k in ("param", "grad", "exp_avg", "exp_avg_sq")]
-                + [("numel", C.c_int64 * 64), ("norm_out", P), ("workspace", P), ("workspace_bytes", C.c_size_t)])
+                + [("numel", C.c_int64 * 64), ("norm_out", P), ("workspace", P), ("workspace_bytes", C.c_size_t)]
+                + [("mult", C.c_int32 * 64), ("update", C.c_int32), ("pad3_", C.c_int32)])
 
 
-STRUCTS = {s.__name__: s for s in (drm_clip_adam_call, drm_mlp, drm_mlp_grad, drm_rssm, drm_rssm_grad, drm_rollout, drm_rollout_grad,
+class drm_image_logprob_call(C.Structure):
+    _fields_ = [("rows", C.c_int64), ("D", C.c_int32), ("mean_bf16", C.c_int32), ("mean", P), ("obs", P), ("logp", P),
+                ("g", P), ("dmean", P)]
+
+
+class drm_policy_mode_call(C.Structure):
+    _fields_ = [("n", C.c_int32), ("A", C.c_int32), ("samples", C.c_int32), ("mean_scale", C.c_float),
+                ("raw_init_std", C.c_float), ("min_std", C.c_float), ("raw", P), ("noise", P), ("action", P), ("logp", P),
+                ("index", P)]
+
+
+class drm_replay_gather_call(C.Structure):
+    _fields_ = [("T_cap", C.c_int64), ("B_env", C.c_int32), ("T_seq", C.c_int32), ("batch", C.c_int32),
+                ("t_offset", C.c_int32), ("row_bytes", C.c_int64), ("src", P), ("dst", P), ("t0", P), ("b", P)]
+
+
+STRUCTS = {s.__name__: s for s in (drm_replay_gather_call, drm_policy_mode_call, drm_image_logprob_call, drm_clip_adam_call, drm_mlp, drm_mlp_grad, drm_rssm, drm_rssm_grad, drm_rollout, drm_rollout_grad,
                                    drm_mlp_call, drm_mlp_bwd_call, drm_returns_loss_call, drm_kl_call)}
 
 # every symbol include/dreamer_b200.h declares: name -> (restype, argtypes)
@@ -130,6 +147,10 @@ SYMBOLS = {
     "drm_mlp_bwd": (C.c_int, [C.POINTER(drm_mlp_bwd_call), P]),
     "drm_returns_loss": (C.c_int, [C.POINTER(drm_returns_loss_call), P]),
     "drm_clip_adam": (C.c_int, [C.POINTER(drm_clip_adam_call), P]),
+    "drm_image_logprob_fwd": (C.c_int, [C.POINTER(drm_image_logprob_call), P]),
+    "drm_image_logprob_bwd": (C.c_int, [C.POINTER(drm_image_logprob_call), P]),
+    "drm_policy_mode": (C.c_int, [C.POINTER(drm_policy_mode_call), P]),
+    "drm_replay_gather": (C.c_int, [C.POINTER(drm_replay_gather_call), P]),
     "drm_kl_fwd": (C.c_int, [C.POINTER(drm_kl_call), P]),
     "drm_kl_bwd": (C.c_int, [C.POINTER(drm_kl_call), P]),
 }

@@ -1,5 +1,6 @@
 // Loss-section kernels: lambda-returns + actor/value losses with their analytic gradients
 // (dreamer_algo.py:314-337,398-422) and KL / free-nats / entropies (dreamer_algo.py:270-273,342-343).
+#include <cuda_bf16.h>
 #include "drm_common.cuh"
 
 namespace drm {
@@ -210,7 +211,64 @@ __global__ void __launch_bounds__(256) kl_bwd_kernel(const drm_kl_call c) {
     }
 }
 
-void warm_loss() { warm_kernel(returns_loss_kernel); warm_kernel(returns_loss_reg_kernel<16>); warm_kernel(returns_loss_reg_kernel<32>); warm_kernel(kl_fwd_kernel); warm_kernel(kl_finalize_kernel); warm_kernel(kl_bwd_kernel); }
+
+// ------------------------------------------------------------------------------------------------
+// Image log-likelihood of the observation decoder: Independent(Normal(mean, 1), 3).log_prob(obs)
+// (dreamer/models/observation.py:117, dreamer_algo.py:264) as ONE reduction per image instead of a chain of ATen
+// pointwise kernels over [T*B, 3*64*64]:  logp[row] = -0.5 * sum_i (obs - mean)^2 - D * 0.5 ln(2 pi).
+// HBM-bound: 2 reads per element forward, 2 reads + 1 write backward.  `mean` is fp32 or bf16 (autocast decoder).
+// ------------------------------------------------------------------------------------------------
+template <bool kBf16>
+__device__ __forceinline__ float4 ld_mean4(const void* mean, size_t i4) {
+    if (kBf16) {
+        const uint2 q = __ldg(reinterpret_cast<const uint2*>(mean) + i4);
+        return make_float4(__uint_as_float(q.x << 16), __uint_as_float(q.x & 0xFFFF0000u), __uint_as_float(q.y << 16),
+                           __uint_as_float(q.y & 0xFFFF0000u));
+    }
+    return __ldg(reinterpret_cast<const float4*>(mean) + i4);
+}
+
+template <bool kBf16>
+__global__ void __launch_bounds__(256) image_logprob_fwd_kernel(const drm_image_logprob_call c) {
+    __shared__ float red[8];
+    const size_t row = blockIdx.x;
+    const int D4 = c.D >> 2;
+    const size_t base4 = row * (size_t)D4;
+    float acc = 0.f;
+    for (int i = threadIdx.x; i < D4; i += 256) {
+        const float4 m = ld_mean4<kBf16>(c.mean, base4 + i);
+        const float4 x = __ldg(reinterpret_cast<const float4*>(c.obs) + base4 + i);
+        const float a = x.x - m.x, b = x.y - m.y, d = x.z - m.z, e = x.w - m.w;
+        acc += (a * a + b * b) + (d * d + e * e);
+    }
+    const float s = block_sum(acc, red);
+    if (threadIdx.x == 0) c.logp[row] = -0.5f * s - (float)c.D * 0.9189385332046727f;
+}
+
+template <bool kBf16>
+__global__ void __launch_bounds__(256) image_logprob_bwd_kernel(const drm_image_logprob_call c) {
+    const size_t row = blockIdx.x;
+    const int D4 = c.D >> 2;
+    const size_t base4 = row * (size_t)D4;
+    const float g = __ldg(c.g + row);
+    for (int i = threadIdx.x; i < D4; i += 256) {
+        const float4 m = ld_mean4<kBf16>(c.mean, base4 + i);
+        const float4 x = __ldg(reinterpret_cast<const float4*>(c.obs) + base4 + i);
+        const float4 d = make_float4(g * (x.x - m.x), g * (x.y - m.y), g * (x.z - m.z), g * (x.w - m.w));
+        if (kBf16) {
+            __nv_bfloat162 lo = __floats2bfloat162_rn(d.x, d.y), hi = __floats2bfloat162_rn(d.z, d.w);
+            uint2 q;
+            q.x = *reinterpret_cast<uint32_t*>(&lo); q.y = *reinterpret_cast<uint32_t*>(&hi);
+            reinterpret_cast<uint2*>(c.dmean)[base4 + i] = q;
+        } else {
+            reinterpret_cast<float4*>(c.dmean)[base4 + i] = d;
+        }
+    }
+}
+
+void warm_loss() { warm_kernel(returns_loss_kernel); warm_kernel(returns_loss_reg_kernel<16>); warm_kernel(returns_loss_reg_kernel<32>); warm_kernel(kl_fwd_kernel); warm_kernel(kl_finalize_kernel); warm_kernel(kl_bwd_kernel);
+    warm_kernel(image_logprob_fwd_kernel<false>); warm_kernel(image_logprob_fwd_kernel<true>);
+    warm_kernel(image_logprob_bwd_kernel<false>); warm_kernel(image_logprob_bwd_kernel<true>); }
 
 }  // namespace drm
 
@@ -261,6 +319,36 @@ int drm_kl_bwd(const drm_kl_call* c, void* stream_) {
     if (grid > 4 * num_sms()) grid = 4 * num_sms();
     ProfScope prof(PROF_LOSS, stream);
     kl_bwd_kernel<<<grid, 256, 0, stream>>>(*c);
+    DRM_CUDA_OK(cudaGetLastError());
+    return DRM_OK;
+}
+
+static int image_logprob_check(const drm_image_logprob_call* c, bool bwd) {
+    DRM_REQUIRE(c != nullptr, DRM_E_ARG, "null call");
+    DRM_REQUIRE(c->rows >= 1 && c->rows < (1ll << 31) && c->D >= 4 && (c->D & 3) == 0, DRM_E_SHAPE, "need rows >= 1 and D % 4 == 0");
+    DRM_REQUIRE(c->mean && c->obs, DRM_E_ARG, "null pointer");
+    DRM_REQUIRE(((uintptr_t)c->mean & 15) == 0 && ((uintptr_t)c->obs & 15) == 0, DRM_E_ALIGN, "mean / obs must be 16-byte aligned");
+    if (bwd) DRM_REQUIRE(c->g && c->dmean && ((uintptr_t)c->dmean & 15) == 0, DRM_E_ARG, "backward needs g and an aligned dmean");
+    else DRM_REQUIRE(c->logp != nullptr, DRM_E_ARG, "null logp");
+    return check_device();
+}
+
+int drm_image_logprob_fwd(const drm_image_logprob_call* c, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    int rc = image_logprob_check(c, false); if (rc) return rc;
+    ProfScope prof(PROF_LOSS, stream);
+    if (c->mean_bf16) image_logprob_fwd_kernel<true><<<(unsigned)c->rows, 256, 0, stream>>>(*c);
+    else image_logprob_fwd_kernel<false><<<(unsigned)c->rows, 256, 0, stream>>>(*c);
+    DRM_CUDA_OK(cudaGetLastError());
+    return DRM_OK;
+}
+
+int drm_image_logprob_bwd(const drm_image_logprob_call* c, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    int rc = image_logprob_check(c, true); if (rc) return rc;
+    ProfScope prof(PROF_LOSS, stream);
+    if (c->mean_bf16) image_logprob_bwd_kernel<true><<<(unsigned)c->rows, 256, 0, stream>>>(*c);
+    else image_logprob_bwd_kernel<false><<<(unsigned)c->rows, 256, 0, stream>>>(*c);
     DRM_CUDA_OK(cudaGetLastError());
     return DRM_OK;
 }

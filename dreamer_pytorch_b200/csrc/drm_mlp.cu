@@ -349,10 +349,15 @@ void warm_mlp() { warm_kernel(mlp_fwd_kernel<4>); warm_kernel(mlp_fwd_kernel<8>)
 
 using namespace drm;
 
+// bf16 requests run on the tcgen05 kernels when they cover the shape (every layer and the input at most 512 wide: the
+// reference's heads are 200-300 wide on 230 features); wider MLPs (BASELINE configs[4]: 660 input features) run on the
+// fp32 kernels of this library -- still CUDA, more accurate, slower.
+static bool use_tc(const drm_mlp_call* c) { return c->precision == DRM_BF16 && tc::mlp_tc_supported(c); }
+
 extern "C" {
 
 size_t drm_mlp_save_bytes(const drm_mlp_call* c) {
-    if (c && c->precision == DRM_BF16) return tc::mlp_tc_save_bytes(c) + 256;
+    if (c && use_tc(c)) return tc::mlp_tc_save_bytes(c) + 256;
     if (!c || c->mlp.n_linear < 2) return 16;
     return rup_sz((size_t)(c->mlp.n_linear - 1) * c->M * c->mlp.hidden * sizeof(float), 16) + 16;
 }
@@ -362,7 +367,7 @@ size_t drm_mlp_workspace_bytes(const drm_mlp_call* c) {
     size_t f = fwd_pack_floats(c);
     size_t b = bwd_pack_floats(c) + dysave_floats(c);
     size_t bytes = (f > b ? f : b) * sizeof(float) + 256;
-    if (c->precision == DRM_BF16) {
+    if (use_tc(c)) {
         const size_t t = tc::mlp_tc_workspace_bytes(c) + 256;
         if (t > bytes) bytes = t;
     }
@@ -392,7 +397,7 @@ int drm_mlp_fwd(const drm_mlp_call* c, void* stream_) {
     const drm_mlp& m = c->mlp;
     DRM_REQUIRE(c->x0 && c->y && (c->k1 == 0 || c->x1), DRM_E_ARG, "null io pointer");
     DRM_REQUIRE(c->workspace && c->workspace_bytes >= drm_mlp_workspace_bytes(c), DRM_E_WORKSPACE, "workspace too small");
-    if (c->precision == DRM_BF16) return tc::mlp_tc_fwd(c, stream);
+    if (use_tc(c)) return tc::mlp_tc_fwd(c, stream);
     if (c->wait_flags) {
         DRM_REQUIRE(c->wait_steps > 0, DRM_E_ARG, "wait_flags need wait_steps");
         wait_flag_kernel<<<1, 1, 0, stream>>>(c->wait_flags + c->wait_steps - 1, c->wait_target);
@@ -426,7 +431,7 @@ int drm_mlp_bwd(const drm_mlp_bwd_call* bc, void* stream_) {
     rc = check_device(); if (rc) return rc;
     const drm_mlp& m = c->mlp;
     DRM_REQUIRE(bc->phase >= DRM_PHASE_ALL && bc->phase <= DRM_PHASE_RUN, DRM_E_ARG, "bad phase");
-    const bool tc_path = c->precision == DRM_BF16;
+    const bool tc_path = use_tc(c);
     DRM_REQUIRE(tc_path || !(bc->tile_done || bc->tile_wait || bc->step_rows_done), DRM_E_ARG,
                 "tile_done / tile_wait / step_rows_done are honoured by the bf16 kernels only");
     if (bc->phase == DRM_PHASE_PREPARE && !tc_path) return DRM_OK;  // fp32: everything happens in RUN

@@ -20,6 +20,7 @@ int launch_linear_dx(const float* dy, int M, int nout, const float* W, int w_ld,
 
 // bf16 tensor-core path (drm_mlp_tc.cu)
 namespace tc {
+int mlp_tc_supported(const drm_mlp_call* c);  // every layer and the input at most 512 wide
 size_t mlp_tc_workspace_bytes(const drm_mlp_call* c);
 size_t mlp_tc_save_bytes(const drm_mlp_call* c);
 int mlp_tc_fwd(const drm_mlp_call* c, cudaStream_t stream);

@@ -417,6 +417,13 @@ struct MlpTcPlan {
     int tiles;
 };
 
+int mlp_tc_supported(const drm_mlp_call* c) {
+    const drm_mlp& m = c->mlp;
+    const int cin = rup((c->k0 + 7) / 8 + (c->k1 + 7) / 8, 2);
+    const int ch = rup(((m.n_linear > 1 ? m.hidden : 0) + 7) / 8, 2);
+    return ch * 8 <= 512 && rup(m.out_dim, 16) <= 512 && cin * 8 <= 512;
+}
+
 static int plan_dims(const drm_mlp_call* c, MlpTcPlan& pl) {
     const drm_mlp& m = c->mlp;
     MlpTcDev& d = pl.dev;

@@ -19,6 +19,7 @@ __global__ void __launch_bounds__(kOptThreads) grad_sumsq_kernel(const drm_clip_
         const float v = g[i];
         s = fmaf(v, v, s);
     }
+    if (c.mult[t] > 1) s *= (float)c.mult[t];  // a gradient listed k times counts k times in clip_grad_norm_
     s = warp_sum(s);
     __shared__ float part[kOptThreads / 32];
     if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = s;
@@ -47,6 +48,26 @@ __global__ void __launch_bounds__(kOptThreads) clip_adam_kernel(const drm_clip_a
         const double st = (double)*c.step_dev;
         step_size = (float)((double)c.lr / (1.0 - pow(c.beta1_d, st)));
         bias2_sqrt = (float)sqrt(1.0 - pow(c.beta2_d, st));
+    }
+    const int k = c.mult[t];
+    if (k > 1) {
+        // parameter listed k times (see drm_clip_adam_call.mult): gradient scaled k times, k sequential Adam updates
+        const double upd = (double)(c.step_dev ? *c.step_dev : c.update);
+        for (int64_t i = (int64_t)blockIdx.x * kOptThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kOptThreads) {
+            float gi = g[i];
+            for (int r = 0; r < k; ++r) gi *= coef;
+            float mi = m[i], vi = v[i], pi = p[i];
+            for (int r = 1; r <= k; ++r) {
+                const double st = (upd - 1.0) * k + r;
+                const float ss = (float)((double)c.lr / (1.0 - pow(c.beta1_d, st)));
+                const float b2 = (float)sqrt(1.0 - pow(c.beta2_d, st));
+                mi = mi + w1 * (gi - mi);
+                vi = vi * c.beta2 + w2 * gi * gi;
+                pi = pi - ss * (mi / (sqrtf(vi) / b2 + c.eps));
+            }
+            g[i] = gi; m[i] = mi; v[i] = vi; p[i] = pi;
+        }
+        return;
     }
     for (int64_t i = (int64_t)blockIdx.x * kOptThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kOptThreads) {
         const float gi = g[i] * coef;

@@ -116,7 +116,11 @@ __global__ void __launch_bounds__(kChainThreads, 1) rollout_fwd_tc_kernel(const 
         const int row = geo.row, grp = epi_group();
         const bool lead = geo.half == 0;  // half tiles: lanes 16..31 duplicate the rows of lanes 0..15
         const int cfeat = p.cs + p.cdp;
+#ifdef DRM_NO_SAVE  // timing experiment only: the backward pass then reads garbage
+        const bool save = false;
+#else
         const bool save = p.training != 0;
+#endif
         const size_t lo_stride = (size_t)p.cdp * kTileRows * 8;
         const int tid = threadIdx.x, lane = threadIdx.x & 31;
         float* hbf = reinterpret_cast<float*>(hb);

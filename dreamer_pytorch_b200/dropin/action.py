@@ -58,12 +58,14 @@ class ActionDecoder(nn.Module):
             mean, std = torch.chunk(x, 2, -1)
             mean = self.mean_scale * torch.tanh(mean / self.mean_scale)
             std = F.softplus(std + self.raw_init_std) + self.min_std
-            dist = torch.distributions.Normal(mean, std)
-            dist = torch.distributions.TransformedDistribution(dist, TanhBijector())
-            dist = torch.distributions.Independent(dist, 1)
-            return SampleDist(dist)
+            # validate_args=False: torch's argument validation is a host synchronisation per distribution (SURVEY 8(b):
+            # "no host sync inside"), and it cannot run under CUDA-graph capture (agent_step.EnvStepGraph)
+            dist = torch.distributions.Normal(mean, std, validate_args=False)
+            dist = torch.distributions.TransformedDistribution(dist, TanhBijector(), validate_args=False)
+            dist = torch.distributions.Independent(dist, 1, validate_args=False)
+            return SampleDist(dist, raw=x, params=(float(self.mean_scale), float(self.raw_init_std), float(self.min_std)))
         if self.dist == "one_hot":
-            return torch.distributions.OneHotCategorical(logits=x)
+            return torch.distributions.OneHotCategorical(logits=x, validate_args=False)
         if self.dist == "relaxed_one_hot":
-            return torch.distributions.RelaxedOneHotCategorical(0.1, logits=x)
+            return torch.distributions.RelaxedOneHotCategorical(0.1, logits=x, validate_args=False)
         return None

@@ -9,9 +9,13 @@ import torch
 
 
 class SampleDist:
-    def __init__(self, dist: torch.distributions.Distribution, samples=100):
+    def __init__(self, dist: torch.distributions.Distribution, samples=100, raw=None, params=None):
+        """raw / params (optional, set by ActionDecoder): the actor MLP's output [..., 2A] and (mean_scale, raw_init_std,
+        min_std) the distribution was built from.  With them ``mode()`` on CUDA tensors outside autograd is ONE fused
+        kernel (drm_policy_mode: draws, log-probs, arg-max, gather) instead of ~15 torch.distributions launches."""
         self._dist = dist
         self._samples = samples
+        self._raw, self._params = raw, params
 
     @property
     def name(self):
@@ -29,6 +33,11 @@ class SampleDist:
         return sample.mean(0)
 
     def mode(self):
+        raw = self._raw
+        if raw is not None and raw.is_cuda and not (torch.is_grad_enabled() and raw.requires_grad):
+            from ..functional import policy_mode
+
+            return policy_mode(raw.detach(), self._samples, *self._params)
         wide, sample = self._draw()
         logprob = wide.log_prob(sample)  # [samples, batch]
         best = logprob.argmax(dim=0)     # [batch]

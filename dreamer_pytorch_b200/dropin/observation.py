@@ -1,12 +1,52 @@
 """Conv encoder / decoder with the reference's parameter names and shapes
-(``dreamer/models/observation.py:7-136``).  OUT OF SCOPE as kernels:
-dense convolutions stay library (cuDNN) calls; they only feed ``obs_embed`` into the RSSM path and
-consume ``get_feat(post)``.  Present so that ``AgentModel`` is self-contained on a box without the
-reference checkout."""
+(``dreamer/models/observation.py:7-136``), SURVEY.md 8(f) N2.
+
+The dense convolutions stay library (cuDNN) calls -- plain library GEMM-class work -- but are laid out for the B200
+(``precision.get_conv_mode``): under ``precision("bf16")`` they run on channels-last tensors (tensor-core implicit
+GEMMs, no NCHW<->NHWC conversion kernels around every layer), optionally under bf16 autocast (``conv_mode("bf16")``);
+under ``precision("fp32")`` they are the reference's fp32 NCHW calls, bit for bit.  The decoder's distribution is ``Independent(Normal(mean, 1), 3)`` as in the reference, with ``log_prob`` routed to
+ONE fused reduction kernel per call (``drm_image_logprob_fwd/bwd``) instead of ATen's chain of pointwise kernels over
+[T*B, 3, 64, 64] (dreamer_algo.py:264)."""
 import numpy as np
 import torch
 import torch.distributions as td
 import torch.nn as nn
+
+import contextlib
+
+from ..precision import get_conv_mode
+
+
+def _mode(x: torch.Tensor) -> str:
+    return get_conv_mode() if x.is_cuda else "nchw"
+
+
+def _cast(mode: str):
+    return torch.autocast("cuda", dtype=torch.bfloat16) if mode == "bf16" else contextlib.nullcontext()
+
+
+class ImageNormal(td.Independent):
+    """``td.Independent(td.Normal(mean, 1), k)`` (observation.py:117) whose ``log_prob`` on CUDA tensors is the fused
+    reduction kernel.  ``mean`` may be bf16 (autocast decoder): ``.mean`` widens it."""
+
+    def __init__(self, mean: torch.Tensor, event_dims: int):
+        super().__init__(td.Normal(mean, 1, validate_args=False), event_dims, validate_args=False)
+        self._loc, self._k = mean, event_dims
+
+    @property
+    def mean(self):
+        return self._loc.float()
+
+    def log_prob(self, value):
+        loc = self._loc
+        if loc.is_cuda and value.is_cuda and value.shape == loc.shape and loc.dim() > self._k:
+            from ..functional import ImageLogProbFn
+
+            lead = loc.shape[:loc.dim() - self._k]
+            D = int(np.prod(loc.shape[loc.dim() - self._k:]))
+            if D % 4 == 0:
+                return ImageLogProbFn.apply(loc.reshape(-1, D), value.reshape(-1, D)).reshape(lead)
+        return super().log_prob(value)
 
 
 def conv_out(h_in, padding, kernel_size, stride):
@@ -37,7 +77,16 @@ class ObservationEncoder(nn.Module):
 
     def forward(self, obs):
         lead = obs.shape[:-3]
-        x = self.convolutions(obs.reshape(-1, *obs.shape[-3:]))
+        x = obs.reshape(-1, *obs.shape[-3:])
+        mode = _mode(x)
+        if mode != "nchw":
+            if not getattr(self, "_cl", False):
+                self.convolutions.to(memory_format=torch.channels_last)  # in place: same Parameter objects
+                self._cl = True
+            with _cast(mode):
+                x = self.convolutions(x.contiguous(memory_format=torch.channels_last))
+            return x.float().reshape(*lead, -1)  # logical NCHW order, like the reference's flatten
+        x = self.convolutions(x)
         return x.reshape(*lead, -1)
 
     @property
@@ -73,6 +122,16 @@ class ObservationDecoder(nn.Module):
     def forward(self, x):
         lead = x.shape[:-1]
         flat = x.reshape(int(np.prod(lead)), x.shape[-1])
-        y = self.linear(flat).reshape(flat.shape[0], *self.conv_shape)
-        mean = self.decoder(y).reshape(*lead, *self.shape)
-        return td.Independent(td.Normal(mean, 1), len(self.shape))
+        mode = _mode(flat)
+        if mode != "nchw":
+            if not getattr(self, "_cl", False):
+                self.decoder.to(memory_format=torch.channels_last)
+                self._cl = True
+            with _cast(mode):
+                y = self.linear(flat).reshape(flat.shape[0], *self.conv_shape)
+                mean = self.decoder(y.contiguous(memory_format=torch.channels_last))
+            mean = mean.contiguous().reshape(*lead, *self.shape)  # NCHW order (bf16 or fp32): what the log-prob kernel reads
+        else:
+            y = self.linear(flat).reshape(flat.shape[0], *self.conv_shape)
+            mean = self.decoder(y).reshape(*lead, *self.shape)
+        return ImageNormal(mean, len(self.shape))

@@ -483,3 +483,77 @@ def returns_loss_raw(reward, value, pcont, discount, lambda_):
     _lib.check(lib.drm_returns_loss(C.byref(c), _stream()), "drm_returns_loss")
     _count()
     return out
+
+
+# ------------------------------------------------------------------------------------------------
+# image log-likelihood of the observation decoder
+# ------------------------------------------------------------------------------------------------
+class ImageLogProbFn(torch.autograd.Function):
+    """logp [rows] = Independent(Normal(mean, 1), k).log_prob(obs) for mean / obs of shape [rows, D]: one fused
+    reduction launch (drm_image_logprob_fwd) instead of a chain of pointwise kernels; mean may be fp32 or bf16."""
+
+    @staticmethod
+    def forward(ctx, mean, obs):
+        lib = _lib.load()
+        if not (mean.is_cuda and obs.is_cuda):
+            raise RuntimeError("dreamer_pytorch_b200 ops need CUDA tensors (there is no CPU fallback)")
+        if mean.dtype not in (torch.float32, torch.bfloat16):
+            mean = mean.float()
+        mean = mean.contiguous()
+        obs = obs.float().contiguous()
+        rows, D = mean.shape
+        c = _lib.drm_image_logprob_call()
+        c.rows, c.D, c.mean_bf16 = rows, D, 1 if mean.dtype == torch.bfloat16 else 0
+        logp = torch.empty(rows, dtype=torch.float32, device=mean.device)
+        c.mean, c.obs, c.logp = mean.data_ptr(), obs.data_ptr(), logp.data_ptr()
+        _lib.check(lib.drm_image_logprob_fwd(C.byref(c), _stream()), "drm_image_logprob_fwd")
+        _count()
+        ctx.save_for_backward(mean, obs)
+        return logp
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g):
+        lib = _lib.load()
+        mean, obs = ctx.saved_tensors
+        if ctx.needs_input_grad[1]:
+            raise RuntimeError("the fused image log-prob is differentiable w.r.t. the decoder mean only")
+        g = _f32c(g)
+        c = _lib.drm_image_logprob_call()
+        c.rows, c.D, c.mean_bf16 = mean.shape[0], mean.shape[1], 1 if mean.dtype == torch.bfloat16 else 0
+        dmean = torch.empty_like(mean)
+        c.mean, c.obs, c.g, c.dmean = mean.data_ptr(), obs.data_ptr(), g.data_ptr(), dmean.data_ptr()
+        _lib.check(lib.drm_image_logprob_bwd(C.byref(c), _stream()), "drm_image_logprob_bwd")
+        _count()
+        return dmean, None
+
+
+# ------------------------------------------------------------------------------------------------
+# environment-time policy head (SURVEY 8(f) N4)
+# ------------------------------------------------------------------------------------------------
+def policy_mode(raw: torch.Tensor, samples: int, mean_scale: float, raw_init_std: float, min_std: float,
+                return_logp: bool = False):
+    """SampleDist.mode() of the tanh-Normal action distribution (distribution.py:24-35) from the actor MLP's output
+    ``raw`` [..., 2A]: ``samples`` draws, their log-probabilities, arg-max, gather -- one launch (drm_policy_mode).
+    No gradient (the reference only calls it under ``torch.no_grad`` at environment-step time)."""
+    from . import noise
+
+    lib = _lib.load()
+    lead = raw.shape[:-1]
+    A = raw.shape[-1] // 2
+    flat = _f32c(raw.reshape(-1, 2 * A))
+    n = flat.shape[0]
+    eps = noise.normal("mode_noise", (samples, n, A), flat.device)
+    action = torch.empty(n, A, dtype=torch.float32, device=flat.device)
+    c = _lib.drm_policy_mode_call()
+    c.n, c.A, c.samples = n, A, int(samples)
+    c.mean_scale, c.raw_init_std, c.min_std = float(mean_scale), float(raw_init_std), float(min_std)
+    c.raw, c.noise, c.action = flat.data_ptr(), eps.data_ptr(), action.data_ptr()
+    logp = None
+    if return_logp:
+        logp = torch.empty(samples, n, dtype=torch.float32, device=flat.device)
+        c.logp = logp.data_ptr()
+    _lib.check(lib.drm_policy_mode(C.byref(c), _stream()), "drm_policy_mode")
+    _count()
+    action = action.reshape(*lead, A)
+    return (action, logp) if return_logp else action

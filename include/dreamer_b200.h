@@ -243,6 +243,52 @@ typedef struct drm_kl_call {
     float *d_post_mean, *d_post_std, *d_prior_mean, *d_prior_std;
 } drm_kl_call;
 
+/* Image log-likelihood of the observation decoder: Independent(Normal(mean, 1), 3).log_prob(obs)
+ * (dreamer/models/observation.py:117 as consumed by dreamer_algo.py:264), one fused reduction per image:
+ *     logp[row] = -0.5 * sum_i (obs[row,i] - mean[row,i])^2 - D * 0.5 ln(2 pi)
+ * and its gradient  dmean[row,i] = g[row] * (obs[row,i] - mean[row,i]).  HBM-bound. */
+typedef struct drm_image_logprob_call {
+    int64_t rows;          /* images (T*B) */
+    int32_t D;             /* elements per image (C*H*W), multiple of 4 */
+    int32_t mean_bf16;     /* 1: mean / dmean are bf16 (an autocast decoder), 0: fp32 */
+    const void* mean;      /* [rows, D] */
+    const float* obs;      /* [rows, D] fp32, already normalised */
+    float* logp;           /* [rows]   (fwd) */
+    const float* g;        /* [rows]   upstream gradient of logp (bwd) */
+    void* dmean;           /* [rows, D] same dtype as mean (bwd) */
+} drm_image_logprob_call;
+int drm_image_logprob_fwd(const drm_image_logprob_call* c, void* stream);
+int drm_image_logprob_bwd(const drm_image_logprob_call* c, void* stream);
+
+/* Environment-time policy head: SampleDist.mode() of the tanh-Normal action distribution
+ * (dreamer/models/distribution.py:24-35 over dreamer/models/action.py:54-61), one launch. */
+typedef struct drm_policy_mode_call {
+    int32_t n, A, samples;    /* rows, action dims, Monte-Carlo draws (the reference uses 100) */
+    float mean_scale, raw_init_std, min_std; /* 5, ln(e^5 - 1), 1e-4 (action.py:20-22,35) */
+    const float* raw;    /* [n, 2A] output of the actor MLP (mean | std pre-activations) */
+    const float* noise;  /* [samples, n, A] N(0,1) */
+    float* action;       /* [n, A] the draw with the highest log-probability */
+    float* logp;         /* [samples, n] or NULL */
+    int32_t* index;      /* [n] winning draw, or NULL */
+} drm_policy_mode_call;
+int drm_policy_mode(const drm_policy_mode_call* c, void* stream);
+
+/* Replay -> device: sequence gather on a ring buffer resident in HBM (rlpyt/replays/sequence/n_step.py:68-106,
+ * rlpyt/utils/misc.py:38-56), dst[j, i, :] = src[(t0[i] + t_offset + j) mod T_cap, b[i], :]. */
+typedef struct drm_replay_gather_call {
+    int64_t T_cap;       /* time length of the ring */
+    int32_t B_env;       /* environments (second ring dimension) */
+    int32_t T_seq;       /* sequence length to extract */
+    int32_t batch;       /* sequences */
+    int32_t t_offset;    /* 0, or -1 for "previous" fields (all_action, all_reward) */
+    int64_t row_bytes;   /* bytes of one [t, b] entry */
+    const void* src;     /* [T_cap, B_env, row_bytes] */
+    void* dst;           /* [T_seq, batch, row_bytes] */
+    const int64_t* t0;   /* [batch] start times (device) */
+    const int64_t* b;    /* [batch] environment indices (device) */
+} drm_replay_gather_call;
+int drm_replay_gather(const drm_replay_gather_call* c, void* stream);
+
 int drm_version(void);
 /* Once per device, before the first compute call (the ctypes binding does it at load time): checks the architecture and
  * loads every kernel of the library (CUDA would otherwise load a kernel lazily at its first launch, and that load may
@@ -310,6 +356,16 @@ typedef struct drm_clip_adam_call {
     float* norm_out;   /* device scalar */
     void* workspace;   /* >= 16 bytes: sum-of-squares accumulator */
     size_t workspace_bytes;
+    /* Duplicated parameters.  The reference's world-model group lists the transition parameters TWICE (the transition
+     * module is also a sub-module of the representation module, dreamer_algo.py:112-118 / agent.py:57-68; torch warns).
+     * torch then -- in its sequential semantics (CPU, foreach=False) -- counts such a gradient twice in the norm, scales
+     * it by the clip coefficient twice, and runs two Adam updates on it per step, its per-parameter step count advancing
+     * by two.  mult[i] (0 or 1: listed once) is the number of listings of tensor i; for mult > 1 the bias corrections
+     * are derived on the device in double from the update count (*step_dev, or `update` when step_dev is NULL):
+     * steps (update - 1) * mult + 1 .. update * mult. */
+    int32_t mult[DRM_MAX_OPT_TENSORS];
+    int32_t update;    /* 1-based count of this optimizer step (host side), used when step_dev is NULL */
+    int32_t pad3_;
 } drm_clip_adam_call;
 int drm_clip_adam(const drm_clip_adam_call* c, void* stream);
 int drm_kl_fwd(const drm_kl_call* c, void* stream);
