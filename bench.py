@@ -424,7 +424,12 @@ def run_b200(args):
     launches0 = lib.drm_launch_count()
     ms_dev, t_wall = run.timed_device(steps)
     launches = int(lib.drm_launch_count() - launches0) if run.graph is None else run.graph.launches_per_replay * steps
-    # sustained block: the same step for >= 1.5 s, so that the clock record has > 10 samples under load
+    # sustained block: the same step for >= 1.5 s, so that the clock record has > 10 samples under load.  Every rank must
+    # replay the same number of steps (each replay holds the gradient all-reduce): agree on the slowest rank's time first.
+    if world > 1:
+        t0 = torch.tensor([ms_dev], dtype=torch.float64, device=dev)
+        dist.all_reduce(t0, op=dist.ReduceOp.MAX)
+        ms_dev = float(t0[0])
     sus_steps = max(steps, int(1.5e3 / max(ms_dev / steps, 1e-3)) + 1) if args.sustained else 0
     sus_steps = min(sus_steps, 20000)
     ms_sus = run.timed_device(sus_steps)[0] if sus_steps else 0.0
@@ -464,8 +469,7 @@ def run_b200(args):
         torch.cuda.synchronize()
         dist.barrier()
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
+        _finish(world, dist)
         return
 
     states = N * H * world * steps
@@ -522,8 +526,21 @@ def run_b200(args):
         if not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(w, args.cpu_seconds)
     print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    _finish(world, dist)
+
+
+def _finish(world, dist):
+    """Multi-rank exit: meet once more, then leave without tearing NCCL down -- destroying a communicator whose collectives
+    are referenced by captured CUDA graphs can block forever (seen: a 2-GPU run that had printed its line hung in
+    destroy_process_group until the box's time limit)."""
+    if world <= 1:
+        return
+    sys.stdout.flush()
+    sys.stderr.flush()
+    try:
+        dist.barrier()
+    finally:
+        os._exit(0)
 
 
 # ------------------------------------------------------------------------------------------------
