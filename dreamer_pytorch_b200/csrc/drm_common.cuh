@@ -166,8 +166,66 @@ __device__ __forceinline__ void seg_accumulate(float (&acc)[R], const Seg& s, in
 }
 
 // epi(r, col, value) is called for every r < R and col < nout.
+// Few rows per CTA (R <= 8; the observation rollout has 50 rows in all, 4 per CTA): the FMAs are nothing, the kernel is bound
+// by the latency of its weight loads, and 8 warps (2 per scheduler) cannot hide it (ncu: 24 % issue slots used, 3.3 warps
+// stalled on the long scoreboard per issue).  Such CTAs are launched with kWideThreads threads and split K over the warps
+// that would otherwise idle: warp = (K part, column block); partial sums meet in a shared-memory scratch
+// [warp][R][32] and are reduced, bias / activation applied, by all threads.  Same epi(r, col, value) contract.
+constexpr int kWideThreads = 1024;
 template <int R, class Epi>
-__device__ __forceinline__ void cta_linear(const Seg& s0, const Seg& s1, int ldw, int nout, Epi epi) {
+__device__ __forceinline__ void cta_linear_splitk(const Seg& s0, const Seg& s1, int ldw, int nout, Epi epi, float* scratch) {
+    const int nwarps = blockDim.x >> 5;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int CB = (nout + 31) >> 5;                       // column blocks of 32
+    const int ksplit = CB >= nwarps ? 1 : nwarps / CB;     // K parts
+    __syncthreads();                                       // scratch may still be read by the previous call's reduction
+    for (int slot = warp; slot < CB * ksplit; slot += nwarps) {
+        const int cb = slot % CB, ks = slot / CB;
+        const int col = cb * 32 + lane;
+        float acc[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) acc[r] = 0.f;
+        const int Ktot = s0.K4 + s1.K4;
+        int kbeg = (int)(((long long)Ktot * ks / ksplit) & ~3LL), kend = (int)(((long long)Ktot * (ks + 1) / ksplit) & ~3LL);
+        if (ks == ksplit - 1) kend = Ktot;
+        // [kbeg, kend) over the concatenation of the two segments
+        if (kbeg < s0.K4) {
+            Seg p = s0;
+            const int e = kend < s0.K4 ? kend : s0.K4;
+            p.W = s0.W + (size_t)kbeg * ldw; p.X = s0.X + kbeg; p.K4 = e - kbeg;
+            seg_accumulate<R>(acc, p, ldw, col);
+        }
+        if (kend > s0.K4 && s1.K4 > 0) {
+            Seg p = s1;
+            const int b = kbeg > s0.K4 ? kbeg - s0.K4 : 0;
+            p.W = s1.W + (size_t)b * ldw; p.X = s1.X + b; p.K4 = kend - s0.K4 - b;
+            seg_accumulate<R>(acc, p, ldw, col);
+        }
+        float* dst = scratch + (size_t)slot * R * 32 + lane;
+#pragma unroll
+        for (int r = 0; r < R; ++r) dst[r * 32] = acc[r];
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < R * CB * 32; idx += blockDim.x) {
+        const int r = idx / (CB * 32), c = idx - r * (CB * 32);
+        if (c >= nout) continue;
+        const int cb = c >> 5, ln = c & 31;
+        float v = 0.f;
+        for (int ks = 0; ks < ksplit; ++ks) v += scratch[((size_t)(ks * CB + cb) * R + r) * 32 + ln];
+        epi(r, c, v);
+    }
+}
+// floats of scratch a wide CTA needs: one [R][32] block per (K part, column block) slot, at most 2 x warps slots
+__host__ __device__ inline int splitk_scratch_floats(int R) { return 2 * (kWideThreads / 32) * R * 32; }
+
+template <int R, class Epi>
+__device__ __forceinline__ void cta_linear(const Seg& s0, const Seg& s1, int ldw, int nout, Epi epi, float* scratch = nullptr) {
+    if constexpr (R <= 8) {
+        if (scratch != nullptr && blockDim.x > kThreads) {
+            cta_linear_splitk<R>(s0, s1, ldw, nout, epi, scratch);
+            return;
+        }
+    }
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int c0 = warp * 32; c0 < nout; c0 += kWarps * 32) {
         const int col = c0 + lane;  // < ldw always (ldw is nout rounded up to 32)
@@ -189,7 +247,7 @@ template <class Epi>
 __device__ __forceinline__ void cta_linear_narrow(const float* __restrict__ W, int w_ld, int K,
                                                   const float* X, int ldx, int nrows, int nout, Epi epi) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int idx = warp; idx < nrows * nout; idx += kWarps) {
+    for (int idx = warp; idx < nrows * nout; idx += (int)(blockDim.x >> 5)) {
         const int r = idx / nout, c = idx - r * nout;
         const float* wr = W + (size_t)c * w_ld;
         const float* xr = X + r * ldx;

@@ -8,7 +8,7 @@
 namespace drm {
 
 template <int R>
-__global__ void __launch_bounds__(kThreads) rollout_bwd_kernel(const RollDev p) {
+__global__ void __launch_bounds__(R <= 8 ? kWideThreads : kThreads) rollout_bwd_kernel(const RollDev p) {
     extern __shared__ __align__(16) float smem[];
     const int S = p.S, D = p.D, Hd = p.Hd, A = p.A, U = p.U;
     float* cS = smem;                 // [R][S4]   carried d stoch
@@ -24,17 +24,19 @@ __global__ void __launch_bounds__(kThreads) rollout_bwd_kernel(const RollDev p) 
     const bool repr = p.mode == DRM_MODE_REPRESENTATION;
     const Seg none{nullptr, nullptr, 0, 0};
 
+    // wide CTAs (few rows): split-K scratch behind the row buffers, see cta_linear_splitk
+    float* ksc = (R <= 8 && blockDim.x > kThreads) ? smem + R * bwd_smem_floats_per_row(p) : nullptr;
     for (int tile = blockIdx.x; tile * R < p.n; tile += gridDim.x) {
         const int row0 = tile * R;
         const int total = R * bwd_smem_floats_per_row(p);
-        for (int i = threadIdx.x; i < total; i += kThreads) smem[i] = 0.f;
+        for (int i = threadIdx.x; i < total; i += blockDim.x) smem[i] = 0.f;
         __syncthreads();
 
         for (int t = p.T - 1; t >= 0; --t) {
             const size_t trow0 = (size_t)t * n + row0;
             // ------------------------------------------------------------ posterior head (REPRESENTATION)
             if (repr) {
-                for (int i = threadIdx.x; i < R * S; i += kThreads) {
+                for (int i = threadIdx.x; i < R * S; i += blockDim.x) {
                     const int r = i / S, c = i - r * S;
                     float dm = 0.f, ds = 0.f;
                     if (row0 + r < p.n) {
@@ -62,18 +64,18 @@ __global__ void __launch_bounds__(kThreads) rollout_bwd_kernel(const RollDev p) 
                         sV[r * Hd + col] = g;
                     };
                     Seg s0{p.Wq2, sMS, p.MS4, p.MS4};
-                    cta_linear<R>(s0, none, p.ld_q2, Hd, epi);
+                    cta_linear<R>(s0, none, p.ld_q2, Hd, epi, ksc);
                 }
                 __syncthreads();
                 {
                     auto epi = [&](int r, int col, float v) { sDH[r * D + col] = v; };
                     Seg s0{p.Wq1, sV, Hd, Hd};
-                    cta_linear<R>(s0, none, p.ld_q1, D, epi);
+                    cta_linear<R>(s0, none, p.ld_q1, D, epi, ksc);
                 }
                 __syncthreads();
             }
             // ------------------------------------------------------------ prior head
-            for (int i = threadIdx.x; i < R * S; i += kThreads) {
+            for (int i = threadIdx.x; i < R * S; i += blockDim.x) {
                 const int r = i / S, c = i - r * S;
                 float dm = 0.f, ds = 0.f;
                 if (row0 + r < p.n) {
@@ -101,7 +103,7 @@ __global__ void __launch_bounds__(kThreads) rollout_bwd_kernel(const RollDev p) 
                     sV[r * Hd + col] = g;
                 };
                 Seg s0{p.Wp2, sMS, p.MS4, p.MS4};
-                cta_linear<R>(s0, none, p.ld_p2, Hd, epi);
+                cta_linear<R>(s0, none, p.ld_p2, Hd, epi, ksc);
             }
             __syncthreads();
             {
@@ -111,11 +113,11 @@ __global__ void __launch_bounds__(kThreads) rollout_bwd_kernel(const RollDev p) 
                     sDH[r * D + col] = tot;
                 };
                 Seg s0{p.Wp1, sV, Hd, Hd};
-                cta_linear<R>(s0, none, p.ld_p1, D, epi);
+                cta_linear<R>(s0, none, p.ld_p1, D, epi, ksc);
             }
             __syncthreads();
             // ------------------------------------------------------------ GRU cell
-            for (int i = threadIdx.x; i < R * D; i += kThreads) {
+            for (int i = threadIdx.x; i < R * D; i += blockDim.x) {
                 const int r = i / D, c = i - r * D;
                 float dpr = 0.f, dpz = 0.f, din = 0.f, dhn = 0.f, carry = 0.f;
                 if (row0 + r < p.n) {
@@ -151,25 +153,25 @@ __global__ void __launch_bounds__(kThreads) rollout_bwd_kernel(const RollDev p) 
                     sV[r * Hd + col] = g;
                 };
                 Seg s0{p.Wih, sU, 3 * D, U};
-                cta_linear<R>(s0, none, p.ld_ih, Hd, epi_x);
+                cta_linear<R>(s0, none, p.ld_ih, Hd, epi_x, ksc);
                 auto epi_h = [&](int r, int col, float v) { cD[r * D + col] += v; };
                 Seg s1{p.Whh, sU, 2 * D, U};
                 Seg s2{p.Whh + (size_t)2 * D * p.ld_hh, sU + 3 * D, D, U};
-                cta_linear<R>(s1, s2, p.ld_hh, D, epi_h);
+                cta_linear<R>(s1, s2, p.ld_hh, D, epi_h, ksc);
             }
             __syncthreads();
             {
                 auto epi = [&](int r, int col, float v) { sAS[r * p.AS4 + col] = v; };
                 Seg s0{p.Win, sV, Hd, Hd};
-                cta_linear<R>(s0, none, p.ld_in, A + S, epi);
+                cta_linear<R>(s0, none, p.ld_in, A + S, epi, ksc);
             }
             __syncthreads();
-            for (int i = threadIdx.x; i < R * S; i += kThreads) {
+            for (int i = threadIdx.x; i < R * S; i += blockDim.x) {
                 const int r = i / S, c = i - r * S;
                 cS[r * p.S4 + c] = sAS[r * p.AS4 + A + c];
             }
             if (p.d_action_in) {
-                for (int i = threadIdx.x; i < R * A; i += kThreads) {
+                for (int i = threadIdx.x; i < R * A; i += blockDim.x) {
                     const int r = i / A, j = i - r * A;
                     if (row0 + r < p.n) p.d_action_in[(trow0 + r) * A + j] = sAS[r * p.AS4 + j];
                 }
@@ -178,7 +180,7 @@ __global__ void __launch_bounds__(kThreads) rollout_bwd_kernel(const RollDev p) 
             if (policy && p.want_actor_dy) {
                 const int ah = p.ah, last = p.an - 1;
                 if (p.act_dist == DRM_DIST_TANH_NORMAL) {
-                    for (int i = threadIdx.x; i < R * A; i += kThreads) {
+                    for (int i = threadIdx.x; i < R * A; i += blockDim.x) {
                         const int r = i / A, j = i - r * A;
                         float dm = 0.f, ds = 0.f;
                         if (row0 + r < p.n) {
@@ -198,7 +200,7 @@ __global__ void __launch_bounds__(kThreads) rollout_bwd_kernel(const RollDev p) 
                         sRaw[r * p.Aout4 + A + j] = ds;
                     }
                 } else {
-                    for (int r = threadIdx.x; r < R; r += kThreads) {
+                    for (int r = threadIdx.x; r < R; r += blockDim.x) {
                         const bool ok = row0 + r < p.n;
                         if (!ok) { for (int j = 0; j < A; ++j) sRaw[r * p.Aout4 + j] = 0.f; continue; }
                         const float* lg = p.sv.raw + (trow0 + r) * p.Aout;
@@ -246,7 +248,7 @@ __global__ void __launch_bounds__(kThreads) rollout_bwd_kernel(const RollDev p) 
                         dst[r * U + col] = g;
                     };
                     Seg s0{p.Wa[l], cur, curK4, curLd};
-                    cta_linear<R>(s0, none, p.ld_a[l], ah, epi);
+                    cta_linear<R>(s0, none, p.ld_a[l], ah, epi, ksc);
                     __syncthreads();
                     cur = dst; curK4 = ah; curLd = U;
                     off = off ? 0 : ah;
@@ -256,13 +258,13 @@ __global__ void __launch_bounds__(kThreads) rollout_bwd_kernel(const RollDev p) 
         }
         // gradient w.r.t. the start state
         if (p.d_start_stoch) {
-            for (int i = threadIdx.x; i < R * S; i += kThreads) {
+            for (int i = threadIdx.x; i < R * S; i += blockDim.x) {
                 const int r = i / S, c = i - r * S;
                 if (row0 + r < p.n) p.d_start_stoch[(size_t)(row0 + r) * S + c] = cS[r * p.S4 + c];
             }
         }
         if (p.d_start_deter) {
-            for (int i = threadIdx.x; i < R * D; i += kThreads) {
+            for (int i = threadIdx.x; i < R * D; i += blockDim.x) {
                 const int r = i / D, c = i - r * D;
                 if (row0 + r < p.n) p.d_start_deter[(size_t)(row0 + r) * D + c] = cD[r * D + c];
             }
@@ -275,13 +277,15 @@ int launch_rollout_bwd(const RollDev& p, cudaStream_t stream) {
     const size_t per_row = (size_t)bwd_smem_floats_per_row(p) * sizeof(float);
     const int Rv = pick_rows(p.n, per_row, 0);
     DRM_REQUIRE(Rv > 0, DRM_E_SHAPE, "model too wide for shared memory");
-    const size_t smem = per_row * Rv;
+    const bool wide = Rv <= 8;
+    const size_t smem = per_row * Rv + (wide ? (size_t)splitk_scratch_floats(Rv) * sizeof(float) : 0);
+    const int nthreads = wide ? kWideThreads : kThreads;
     const int tiles = (p.n + Rv - 1) / Rv;
     const int grid = tiles < num_sms() ? tiles : num_sms();
     ProfScope prof(PROF_ROLLOUT_BWD, stream);
     DRM_DISPATCH_R(Rv, {
         DRM_CUDA_OK(cudaFuncSetAttribute(rollout_bwd_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        rollout_bwd_kernel<R><<<grid, kThreads, smem, stream>>>(p);
+        rollout_bwd_kernel<R><<<grid, nthreads, smem, stream>>>(p);
     });
     DRM_CUDA_OK(cudaGetLastError());
     return DRM_OK;

@@ -9,7 +9,7 @@
 namespace drm {
 
 template <int R>
-__global__ void __launch_bounds__(kThreads) rollout_fwd_kernel(const RollDev p) {
+__global__ void __launch_bounds__(R <= 8 ? kWideThreads : kThreads) rollout_fwd_kernel(const RollDev p) {
     extern __shared__ __align__(16) float smem[];
     const int S = p.S, D = p.D, Hd = p.Hd, A = p.A;
     const int ldXH = Hd + D;
@@ -26,16 +26,18 @@ __global__ void __launch_bounds__(kThreads) rollout_fwd_kernel(const RollDev p) 
     const bool save = p.training != 0;
     const Seg none{nullptr, nullptr, 0, 0};
 
+    // wide CTAs (few rows): split-K scratch behind the row buffers, see cta_linear_splitk
+    float* ksc = (R <= 8 && blockDim.x > kThreads) ? smem + R * fwd_smem_floats_per_row(p) : nullptr;
     for (int tile = blockIdx.x; tile * R < p.n; tile += gridDim.x) {
         const int row0 = tile * R;
         const int total = R * fwd_smem_floats_per_row(p);
-        for (int i = threadIdx.x; i < total; i += kThreads) smem[i] = 0.f;
+        for (int i = threadIdx.x; i < total; i += blockDim.x) smem[i] = 0.f;
         __syncthreads();
-        for (int i = threadIdx.x; i < R * S; i += kThreads) {
+        for (int i = threadIdx.x; i < R * S; i += blockDim.x) {
             const int r = i / S, c = i - r * S;
             if (row0 + r < p.n) sS[r * p.S4 + c] = p.start_stoch[(size_t)(row0 + r) * S + c];
         }
-        for (int i = threadIdx.x; i < R * D; i += kThreads) {
+        for (int i = threadIdx.x; i < R * D; i += blockDim.x) {
             const int r = i / D, c = i - r * D;
             if (row0 + r < p.n) sXH[r * ldXH + Hd + c] = p.start_deter[(size_t)(row0 + r) * D + c];
         }
@@ -57,7 +59,7 @@ __global__ void __launch_bounds__(kThreads) rollout_fwd_kernel(const RollDev p) 
                     };
                     Seg s0{p.Wa[0], sS, p.S4, p.S4};
                     Seg s1{p.Wa[0] + (size_t)p.S4 * p.ld_a[0], sXH + Hd, D, ldXH};
-                    cta_linear<R>(s0, s1, p.ld_a[0], ah, epi);
+                    cta_linear<R>(s0, s1, p.ld_a[0], ah, epi, ksc);
                 }
                 __syncthreads();
                 int cur = 0;  // offset of the current hidden buffer inside sU (0 or ah)
@@ -71,7 +73,7 @@ __global__ void __launch_bounds__(kThreads) rollout_fwd_kernel(const RollDev p) 
                         if (svh && row0 + r < p.n) svh[(trow0 + r) * ah + col] = v;
                     };
                     Seg s0{p.Wa[l], sU + cur, ah, U};
-                    cta_linear<R>(s0, none, p.ld_a[l], ah, epi);
+                    cta_linear<R>(s0, none, p.ld_a[l], ah, epi, ksc);
                     __syncthreads();
                     cur = nxt;
                 }
@@ -83,13 +85,13 @@ __global__ void __launch_bounds__(kThreads) rollout_fwd_kernel(const RollDev p) 
                         cta_linear_narrow(p.Wa_last, ah, ah, sU + cur, U, R, p.Aout, epi);
                     } else {
                         Seg s0{p.Wa[l], sU + cur, ah, U};
-                        cta_linear<R>(s0, none, p.ld_a[l], p.Aout, epi);
+                        cta_linear<R>(s0, none, p.ld_a[l], p.Aout, epi, ksc);
                     }
                 }
                 __syncthreads();
                 // sample the action (agent.py:101-117)
                 if (p.act_dist == DRM_DIST_TANH_NORMAL) {
-                    for (int i = threadIdx.x; i < R * A; i += kThreads) {
+                    for (int i = threadIdx.x; i < R * A; i += blockDim.x) {
                         const int r = i / A, j = i - r * A;
                         const bool ok = row0 + r < p.n;
                         const float rm = sRaw[r * p.Aout4 + j], rs = sRaw[r * p.Aout4 + A + j];
@@ -108,7 +110,7 @@ __global__ void __launch_bounds__(kThreads) rollout_fwd_kernel(const RollDev p) 
                     }
                 } else {
                     // categorical variants: one thread per row (A is small)
-                    for (int r = threadIdx.x; r < R; r += kThreads) {
+                    for (int r = threadIdx.x; r < R; r += blockDim.x) {
                         const bool ok = row0 + r < p.n;
                         const float* lg = sRaw + r * p.Aout4;
                         const float* gz = p.noise_act + (trow0 + r) * A;
@@ -149,7 +151,7 @@ __global__ void __launch_bounds__(kThreads) rollout_fwd_kernel(const RollDev p) 
                     }
                 }
             } else {
-                for (int i = threadIdx.x; i < R * A; i += kThreads) {
+                for (int i = threadIdx.x; i < R * A; i += blockDim.x) {
                     const int r = i / A, j = i - r * A;
                     sAct[r * p.A4 + j] = (row0 + r < p.n) ? p.action_in[(trow0 + r) * A + j] : 0.f;
                 }
@@ -165,7 +167,7 @@ __global__ void __launch_bounds__(kThreads) rollout_fwd_kernel(const RollDev p) 
                 };
                 Seg s0{p.Win, sAct, p.A4, p.A4};
                 Seg s1{p.Win + (size_t)p.A4 * p.ld_in, sS, p.S4, p.S4};
-                cta_linear<R>(s0, s1, p.ld_in, Hd, epi);
+                cta_linear<R>(s0, s1, p.ld_in, Hd, epi, ksc);
             }
             __syncthreads();
             // ------------------------------------------------------------------ GRU gates (torch GRUCell)
@@ -173,16 +175,16 @@ __global__ void __launch_bounds__(kThreads) rollout_fwd_kernel(const RollDev p) 
                 auto epi_rz = [&](int r, int col, float v) { sU[r * U + col] = sigmoidf_(v + p.b_ih[col] + p.b_hh[col]); };
                 Seg s0{p.Wrz, sXH, Hd, ldXH};
                 Seg s1{p.Wrz + (size_t)Hd * p.ld_rz, sXH + Hd, D, ldXH};
-                cta_linear<R>(s0, s1, p.ld_rz, 2 * D, epi_rz);
+                cta_linear<R>(s0, s1, p.ld_rz, 2 * D, epi_rz, ksc);
                 auto epi_in = [&](int r, int col, float v) { sU[r * U + 2 * D + col] = v + p.b_ih[2 * D + col]; };
                 Seg s2{p.Wni, sXH, Hd, ldXH};
-                cta_linear<R>(s2, none, p.ld_n, D, epi_in);
+                cta_linear<R>(s2, none, p.ld_n, D, epi_in, ksc);
                 auto epi_hn = [&](int r, int col, float v) { sU[r * U + 3 * D + col] = v + p.b_hh[2 * D + col]; };
                 Seg s3{p.Wnh, sXH + Hd, D, ldXH};
-                cta_linear<R>(s3, none, p.ld_n, D, epi_hn);
+                cta_linear<R>(s3, none, p.ld_n, D, epi_hn, ksc);
             }
             __syncthreads();
-            for (int i = threadIdx.x; i < R * D; i += kThreads) {
+            for (int i = threadIdx.x; i < R * D; i += blockDim.x) {
                 const int r = i / D, c = i - r * D;
                 const float rr = sU[r * U + c], zz = sU[r * U + D + c];
                 const float in_ = sU[r * U + 2 * D + c], hn = sU[r * U + 3 * D + c];
@@ -206,16 +208,16 @@ __global__ void __launch_bounds__(kThreads) rollout_fwd_kernel(const RollDev p) 
                     if (svh && row0 + r < p.n) svh[(trow0 + r) * Hd + col] = v;
                 };
                 Seg s0{p.Wp1, sXH + Hd, D, ldXH};
-                cta_linear<R>(s0, none, p.ld_p1, Hd, epi);
+                cta_linear<R>(s0, none, p.ld_p1, Hd, epi, ksc);
             }
             __syncthreads();
             {
                 auto epi = [&](int r, int col, float v) { sMS[r * p.MS4 + col] = v + p.b_p2[col]; };
                 Seg s0{p.Wp2, sU, Hd, U};
-                cta_linear<R>(s0, none, p.ld_p2, 2 * S, epi);
+                cta_linear<R>(s0, none, p.ld_p2, 2 * S, epi, ksc);
             }
             __syncthreads();
-            for (int i = threadIdx.x; i < R * S; i += kThreads) {
+            for (int i = threadIdx.x; i < R * S; i += blockDim.x) {
                 const int r = i / S, c = i - r * S;
                 const bool ok = row0 + r < p.n;
                 const float mean = sMS[r * p.MS4 + c];
@@ -239,16 +241,16 @@ __global__ void __launch_bounds__(kThreads) rollout_fwd_kernel(const RollDev p) 
                         if (svh && ok) svh[(trow0 + r) * Hd + col] = v;
                     };
                     Seg s0{p.Wq1, sXH + Hd, D, ldXH};
-                    cta_linear<R>(s0, none, p.ld_q1, Hd, epi);
+                    cta_linear<R>(s0, none, p.ld_q1, Hd, epi, ksc);
                 }
                 __syncthreads();
                 {
                     auto epi = [&](int r, int col, float v) { sMS[r * p.MS4 + col] = v + p.b_q2[col]; };
                     Seg s0{p.Wq2, sU, Hd, U};
-                    cta_linear<R>(s0, none, p.ld_q2, 2 * S, epi);
+                    cta_linear<R>(s0, none, p.ld_q2, 2 * S, epi, ksc);
                 }
                 __syncthreads();
-                for (int i = threadIdx.x; i < R * S; i += kThreads) {
+                for (int i = threadIdx.x; i < R * S; i += blockDim.x) {
                     const int r = i / S, c = i - r * S;
                     const bool ok = row0 + r < p.n;
                     const float mean = sMS[r * p.MS4 + c];
@@ -270,13 +272,15 @@ int launch_rollout_fwd(const RollDev& p, cudaStream_t stream) {
     const size_t per_row = (size_t)fwd_smem_floats_per_row(p) * sizeof(float);
     const int Rv = pick_rows(p.n, per_row, 0);
     DRM_REQUIRE(Rv > 0, DRM_E_SHAPE, "model too wide for shared memory");
-    const size_t smem = per_row * Rv;
+    const bool wide = Rv <= 8;
+    const size_t smem = per_row * Rv + (wide ? (size_t)splitk_scratch_floats(Rv) * sizeof(float) : 0);
+    const int nthreads = wide ? kWideThreads : kThreads;
     const int tiles = (p.n + Rv - 1) / Rv;
     const int grid = tiles < num_sms() ? tiles : num_sms();
     ProfScope prof(PROF_ROLLOUT_FWD, stream);
     DRM_DISPATCH_R(Rv, {
         DRM_CUDA_OK(cudaFuncSetAttribute(rollout_fwd_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        rollout_fwd_kernel<R><<<grid, kThreads, smem, stream>>>(p);
+        rollout_fwd_kernel<R><<<grid, nthreads, smem, stream>>>(p);
     });
     DRM_CUDA_OK(cudaGetLastError());
     return DRM_OK;
