@@ -388,6 +388,44 @@ def time_full_paths(w, dev, precision, reps=10):
                         what=("rollout_representation + KL + reward loss + imagination, 3 backwards; conv excluded (synthetic "
                               "obs_embed)") if key == "t_full" else
                              "whole Dreamer.loss incl. conv encoder/decoder + image log-prob, 3 backwards")
+    # the whole update -- loss, 3 backwards, clip + Adam of the three groups -- as ONE graph replay (graph.UpdateGraph),
+    # fed from the device-resident replay (replay.DeviceSequenceReplay): what one iteration of the training loop costs
+    try:
+        from collections import namedtuple
+
+        import numpy as np
+
+        from dreamer_pytorch_b200.graph import UpdateGraph
+        from dreamer_pytorch_b200.replay import DeviceSequenceReplay
+
+        Ex = namedtuple("Ex", ["observation", "action", "reward", "done"])
+        rep = DeviceSequenceReplay(Ex(np.zeros((3, 64, 64), np.uint8), np.zeros(A, np.float32), np.float32(0),
+                                      np.bool_(False)), size=20000, B=10, device=dev)
+        gfill = torch.Generator().manual_seed(6)
+        for _ in range(4):
+            rep.append_samples(Ex(torch.randint(0, 256, (500, 10, 3, 64, 64), generator=gfill, dtype=torch.uint8),
+                                  torch.rand(500, 10, A, generator=gfill) * 2 - 1, torch.randn(500, 10, generator=gfill),
+                                  torch.rand(500, 10, generator=gfill) < 0.01))
+        with prec_ctx(precision):
+            ug = UpdateGraph(model, B, T, horizon=H, use_pcont=w["use_pcont"])
+            ts, ts_s = [], []
+            for i in range(reps + 3):
+                torch.cuda.synchronize()
+                a, m, b = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+                a.record()
+                batch = rep.sample_batch(B, T)
+                m.record()
+                ug.step(batch)
+                b.record()
+                torch.cuda.synchronize()
+                if i >= 3:
+                    ts.append(a.elapsed_time(b)); ts_s.append(a.elapsed_time(m))
+        out["full_update_graph"] = dict(
+            ms=statistics.median(ts), replay_sample_ms=statistics.median(ts_s), launch="one CUDA graph replay",
+            what="replay sample on the device (gather kernels) + whole Dreamer.loss + 3 backwards + clip_grad_norm_ + Adam "
+                 "of the world-model / actor / value groups", conv=get_conv_mode())
+    except Exception as e:
+        out["full_update_graph"] = dict(error=f"{type(e).__name__}: {e}"[:300])
     return out
 
 
@@ -706,6 +744,14 @@ def reference_cuda(w, dev, our_value, line):
             out["full_update"] = dict(ms=med3 * 1e3, passes=len(ts3),
                                       speedup=med3 * 1e3 / line["full_update"]["ms"],
                                       what="reference Dreamer.loss + 3 backwards, eager CUDA, best case")
+            if "ms" in line.get("full_update_graph", {}):
+                full_opt = RH.full_loss_step_fn(model, algo, samples, optimize=True)
+                ts4 = _timed_calls(full_opt, 60.0, 10, warm=2, sync=sync)
+                med4 = statistics.median(ts4)
+                out["full_update_with_optimizers"] = dict(
+                    ms=med4 * 1e3, passes=len(ts4), speedup=med4 * 1e3 / line["full_update_graph"]["ms"],
+                    what="reference training-loop iteration (loss, 3 backwards, 3 x clip_grad_norm_ + Adam.step, 13 .item() "
+                         "reads; batch already on the device), eager CUDA, best case; speedup vs full_update_graph")
     except Exception as e:
         out["error"] = f"{type(e).__name__}: {e}"[:300]
     return out

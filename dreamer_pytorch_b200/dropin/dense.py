@@ -48,7 +48,10 @@ class DenseModel(nn.Module):
         dist_inputs = MlpFn.apply(flat, None, *mlp_weights(self.model))
         reshaped = dist_inputs.reshape(lead + tuple(self._output_shape))
         if self._dist == "normal":
-            return td.independent.Independent(td.Normal(reshaped, 1), len(self._output_shape))
+            # scale as a 0-dim device tensor: a Python scalar would be turned into a tensor through a host->device copy,
+            # which cannot be captured into a CUDA graph (graph.UpdateGraph)
+            return td.independent.Independent(td.Normal(reshaped, reshaped.new_ones(()), validate_args=False),
+                                              len(self._output_shape), validate_args=False)
         if self._dist == "binary":
             # validate_args=False: the reference feeds the soft target discount*(1-done) to log_prob
             # (dreamer_algo.py:266-269), which torch >= 1.8 rejects under argument validation

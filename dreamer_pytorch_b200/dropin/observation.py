@@ -30,7 +30,7 @@ class ImageNormal(td.Independent):
     reduction kernel.  ``mean`` may be bf16 (autocast decoder): ``.mean`` widens it."""
 
     def __init__(self, mean: torch.Tensor, event_dims: int):
-        super().__init__(td.Normal(mean, 1, validate_args=False), event_dims, validate_args=False)
+        super().__init__(td.Normal(mean, mean.new_ones(()), validate_args=False), event_dims, validate_args=False)
         self._loc, self._k = mean, event_dims
 
     @property

@@ -130,3 +130,99 @@ class ImaginationGraph:
                 p.grad = g  # an optimizer's zero_grad(set_to_none=True) dropped it; the graph writes into g
         self.graph.replay()
         return self.actor_loss, self.value_loss
+
+
+class UpdateGraph:
+    """One whole Dreamer update -- ``Dreamer.loss`` + the three backwards + clip_grad_norm_ + Adam for the three optimizer
+    groups (dreamer_algo.py:174-194,213-371) -- as ONE CUDA graph replay.
+
+        g = UpdateGraph(model, batch_size=50, batch_length=50, horizon=15)
+        model_loss, actor_loss, value_loss = g.step(samples)   # SamplesFromReplay-like: all_observation u8 [T+1,B,C,H,W],
+                                                               # all_action [T+1,B,A], all_reward [T+1,B], done [T,B]
+
+    The batch is copied into static buffers (device tensors from ``replay.DeviceSequenceReplay`` cost a device copy, pinned
+    host tensors an asynchronous H2D copy), the graph is replayed, parameters are updated in place.  The frame
+    normalisation (uint8 -> float / 255 - 0.5, dreamer_algo.py:241), the conv encoder / decoder (cuDNN), every fused kernel
+    of this library, the noise generation and the optimizers are inside the graph; nothing synchronises with the host.
+    Optimizers: ``optim.ClipAdam(capturable=True)`` with the reference's hyper-parameters (dreamer_algo.py:28-30,111-131:
+    model 6e-4, actor / value 8e-5, grad_clip 100), created here unless passed in.
+    """
+
+    def __init__(self, model, batch_size: int, batch_length: int, horizon: int = 15, discount: float = 0.99,
+                 discount_lambda: float = 0.95, free_nats: float = 3.0, kl_scale: float = 1.0, use_pcont: bool = False,
+                 pcont_scale: float = 10.0, model_lr: float = 6e-4, actor_lr: float = 8e-5, value_lr: float = 8e-5,
+                 grad_clip: float = 100.0, optimizers=None, warmup: int = 3):
+        from .algo import dreamer_loss
+        from .dropin.module import get_parameters
+        from .optim import ClipAdam
+
+        p0 = next(model.parameters())
+        if not p0.is_cuda:
+            raise RuntimeError("UpdateGraph needs a CUDA model (there is no CPU fallback)")
+        dev = p0.device
+        self.model, self._loss_fn = model, dreamer_loss
+        T, B, A = int(batch_length), int(batch_size), int(model.action_size)
+        self._kw = dict(horizon=horizon, discount=discount, discount_lambda=discount_lambda, free_nats=free_nats,
+                        kl_scale=kl_scale, use_pcont=use_pcont, pcont_scale=pcont_scale)
+        shape = tuple(model.observation_encoder.shape)
+        self.all_observation = torch.zeros(T + 1, B, *shape, dtype=torch.uint8, device=dev)
+        self.all_action = torch.zeros(T + 1, B, A, device=dev)
+        self.all_reward = torch.zeros(T + 1, B, device=dev)
+        self.done = torch.zeros(T, B, dtype=torch.bool, device=dev)
+        # the reference's three groups (dreamer_algo.py:111-122); the world-model list keeps its duplicated transition tensors
+        model_modules = [model.observation_encoder, model.observation_decoder, model.reward_model, model.representation,
+                         model.transition] + ([model.pcont] if use_pcont else [])
+        listed = get_parameters(model_modules)
+        self.model_params = list({id(p): p for p in listed}.values())
+        self.actor_params = list(model.action_decoder.parameters())
+        self.value_params = list(model.value_model.parameters())
+        if optimizers is None:
+            optimizers = (ClipAdam(listed, lr=model_lr, grad_clip=grad_clip, capturable=True),
+                          ClipAdam(self.actor_params, lr=actor_lr, grad_clip=grad_clip, capturable=True),
+                          ClipAdam(self.value_params, lr=value_lr, grad_clip=grad_clip, capturable=True))
+        self.model_opt, self.actor_opt, self.value_opt = optimizers
+        for o in optimizers:
+            if getattr(o, "step_dev", None) is None:
+                raise ValueError("optimizers recorded into the graph must be ClipAdam(..., capturable=True)")
+        params = self.model_params + self.actor_params + self.value_params
+        keep = [(p, p.detach().clone()) for p in params]
+        for o in optimizers:
+            keep += [(t, t.clone()) for st in o.state.values() for t in st.values()] + [(o.step_dev, o.step_dev.clone())]
+        cur = torch.cuda.current_stream(dev)
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            for _ in range(max(1, warmup)):
+                self._eager()
+        cur.wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.losses, self.grad_norms = self._eager()
+        with torch.no_grad():  # the warm-up passes stepped the optimizers: restore parameters and optimizer state
+            for t, saved in keep:
+                t.copy_(saved)
+
+    def _eager(self):
+        observation = self.all_observation[:-1].float() / 255.0 - 0.5  # dreamer_algo.py:225-241
+        ml, al, vl, info = self._loss_fn(self.model, observation, self.all_action[1:], self.all_reward[1:].unsqueeze(2),
+                                         self.done.unsqueeze(2), **self._kw)
+        # autograd.grad rather than .backward(): no AccumulateGrad nodes (they pin the stream they were created on)
+        gm = torch.autograd.grad(ml, self.model_params, allow_unused=True)
+        ga = torch.autograd.grad(al, self.actor_params)
+        gv = torch.autograd.grad(vl, self.value_params)
+        for ps, gs in ((self.model_params, gm), (self.actor_params, ga), (self.value_params, gv)):
+            for p, g in zip(ps, gs):
+                p.grad = g
+        norms = [o.step() for o in (self.model_opt, self.actor_opt, self.value_opt)]
+        return torch.stack([ml.detach(), al.detach(), vl.detach()]), torch.stack([n.detach() for n in norms])
+
+    def step(self, samples):
+        """samples: any object with all_observation / all_action / all_reward / done (rlpyt's SamplesFromReplay or
+        replay.SamplesFromReplay).  Returns the static tensor [model_loss, actor_loss, value_loss]."""
+        self.all_observation.copy_(samples.all_observation, non_blocking=True)
+        self.all_action.copy_(samples.all_action, non_blocking=True)
+        self.all_reward.copy_(samples.all_reward, non_blocking=True)
+        self.done.copy_(samples.done, non_blocking=True)
+        self.graph.replay()
+        return self.losses

@@ -105,8 +105,19 @@ class ClipAdam:
         if not live:
             return self.grad_norm.zero_()
         for p, _ in live:  # validate before touching any state
-            if not p.grad.is_contiguous() or p.grad.dtype != torch.float32:
-                raise RuntimeError("ClipAdam needs contiguous fp32 gradients")
+            g = p.grad
+            if g.dtype != torch.float32:
+                raise RuntimeError("ClipAdam needs fp32 gradients")
+            # the kernel walks raw storage: parameter, gradient and both moments must share one dense layout (contiguous,
+            # or channels-last for the conv weights of precision.conv_mode "channels_last" / "bf16")
+            if g.stride() != p.stride():
+                p.grad = torch.empty_like(p).copy_(g)
+            if not (p.is_contiguous() or (p.dim() == 4 and p.is_contiguous(memory_format=torch.channels_last))):
+                raise RuntimeError("ClipAdam needs dense (contiguous or channels-last) parameters")
+            st = self.state[p]
+            if st["exp_avg"].stride() != p.stride():  # the parameter changed its memory format after construction
+                st["exp_avg"] = torch.empty_like(p).copy_(st["exp_avg"])
+                st["exp_avg_sq"] = torch.empty_like(p).copy_(st["exp_avg_sq"])
         b1, b2 = self.betas
         c = _lib.drm_clip_adam_call()
         c.n_tensors = len(live)

@@ -279,14 +279,32 @@ def synthetic_samples(A, dist, B, T, device="cpu", seed=1):
                              return_=None, done=done.to(device), done_n=None, init_rnn_state=None)
 
 
-def full_loss_step_fn(model, algo, samples):
-    """The reference's whole ``Dreamer.loss`` + the three backwards of ``optimize_agent`` (dreamer_algo.py:174-180)."""
+def full_loss_step_fn(model, algo, samples, optimize=False):
+    """The reference's whole ``Dreamer.loss`` + the three backwards of ``optimize_agent`` (dreamer_algo.py:174-180);
+    with ``optimize`` also its clip_grad_norm_ x 3 + Adam.step x 3 + the 13 ``.item()`` read-backs (dreamer_algo.py:182-209),
+    i.e. the body of one iteration of the reference's training loop."""
+    import_reference()
+    from dreamer.utils.module import get_parameters
+
     def step():
-        model.zero_grad(set_to_none=True)
-        model_loss, actor_loss, value_loss, _ = algo.loss(samples, 0, 0)
+        if optimize:
+            algo.model_optimizer.zero_grad(); algo.actor_optimizer.zero_grad(); algo.value_optimizer.zero_grad()
+        else:
+            model.zero_grad(set_to_none=True)
+        model_loss, actor_loss, value_loss, info = algo.loss(samples, 0, 0)
         model_loss.backward()
         actor_loss.backward()
         value_loss.backward()
+        if optimize:
+            import warnings
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore")
+                norms = [torch.nn.utils.clip_grad_norm_(get_parameters(ms), algo.grad_clip)
+                         for ms in (algo.model_modules, algo.actor_modules, algo.value_modules)]
+            algo.model_optimizer.step(); algo.actor_optimizer.step(); algo.value_optimizer.step()
+            out = [(model_loss + actor_loss + value_loss).item()] + [n.item() for n in norms]
+            out += [getattr(info, f).item() for f in info._fields]
+            return out
         return model_loss.detach(), actor_loss.detach(), value_loss.detach()
 
     return step

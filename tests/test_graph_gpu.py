@@ -103,3 +103,75 @@ def test_kernels_beside_each_other_match_stream_order(use_pcont):
         assert rel_err(a[0], b[0]) < 1e-6 and rel_err(a[1], b[1]) < 1e-6, mode
         for ga, gb in zip(a[4], b[4]):
             assert rel_err(ga, gb) < 1e-4, mode                                 # fp32 atomics reorder between runs
+
+
+@pytest.mark.parametrize("use_pcont", [False, True])
+def test_whole_update_graph_matches_eager_update(use_pcont):
+    """UpdateGraph (Dreamer.loss + 3 backwards + clip + Adam of the three groups, conv stack included, one replay) against the
+    same update done eagerly -- dreamer_loss, .backward() x 3, ClipAdam.step() x 3 -- on identical noise, over two updates."""
+    import copy
+
+    from dreamer_pytorch_b200 import noise
+    from dreamer_pytorch_b200.algo import dreamer_loss
+    from dreamer_pytorch_b200.dropin.agent import AtariDreamerModel
+    from dreamer_pytorch_b200.dropin.module import get_parameters
+    from dreamer_pytorch_b200.graph import UpdateGraph
+    from dreamer_pytorch_b200.optim import ClipAdam
+    from dreamer_pytorch_b200.precision import precision
+    from dreamer_pytorch_b200.replay import SamplesFromReplay
+
+    dev = torch.device("cuda:0")
+    torch.manual_seed(11)
+    A, T, B, H, S = 6, 6, 8, 5, 30
+    dist = "one_hot" if use_pcont else "tanh_normal"
+    m_graph = AtariDreamerModel(action_shape=(A,), action_dist=dist, use_pcont=use_pcont).to(dev).train()
+    m_eager = copy.deepcopy(m_graph)
+    g = torch.Generator().manual_seed(12)
+    obs = torch.randint(0, 256, (T + 1, B, 3, 64, 64), generator=g, dtype=torch.uint8).to(dev)
+    if use_pcont:
+        act = torch.nn.functional.one_hot(torch.randint(0, A, (T + 1, B), generator=g), A).float().to(dev)
+    else:
+        act = (torch.rand(T + 1, B, A, generator=g) * 2 - 1).to(dev)
+    rew = torch.randn(T + 1, B, generator=g).to(dev)
+    done = (torch.rand(T, B, generator=g) < 0.1).to(dev)
+    N = (T - 1) * B if use_pcont else T * B
+    eo, eq = torch.randn(T, B, S, generator=g).to(dev), torch.randn(T, B, S, generator=g).to(dev)
+    ei = torch.randn(H, N, S, generator=g).to(dev)
+    na = torch.randn(H, N, A, generator=g).to(dev)
+    if use_pcont:
+        na = -torch.log(-torch.log(torch.rand(H, N, A, generator=g).clamp(1e-6, 1 - 1e-6))).to(dev)
+
+    def inj(k):
+        return dict(eps_prior=[eo, ei] * k, eps_post=[eq] * k, noise_act=[na] * k)
+
+    samples = SamplesFromReplay(obs, act, rew, None, done, None, None)
+    with precision("fp32"):
+        with noise.injected(**inj(4)):  # 3 warm-up passes + capture: the injected tensors become the graph's noise
+            graph = UpdateGraph(m_graph, B, T, horizon=H, use_pcont=use_pcont)
+        losses_g = [graph.step(samples).clone() for _ in range(2)]
+
+        def modules(m):
+            return [m.observation_encoder, m.observation_decoder, m.reward_model, m.representation, m.transition] + (
+                [m.pcont] if use_pcont else [])
+
+        opts = (ClipAdam(get_parameters(modules(m_eager)), lr=6e-4, grad_clip=100.0),
+                ClipAdam(list(m_eager.action_decoder.parameters()), lr=8e-5, grad_clip=100.0),
+                ClipAdam(list(m_eager.value_model.parameters()), lr=8e-5, grad_clip=100.0))
+        losses_e = []
+        for _ in range(2):
+            m_eager.zero_grad(set_to_none=True)
+            with noise.injected(**inj(1)):
+                ml, al, vl, _ = dreamer_loss(m_eager, obs[:-1].float() / 255.0 - 0.5, act[1:], rew[1:].unsqueeze(2),
+                                             done.unsqueeze(2), horizon=H, use_pcont=use_pcont)
+            ml.backward(); al.backward(); vl.backward()
+            for o in opts:
+                o.step()
+            losses_e.append(torch.stack([ml.detach(), al.detach(), vl.detach()]))
+    torch.cuda.synchronize()
+    for a, b in zip(losses_g, losses_e):
+        assert rel_err(a, b) < 1e-5, (a, b)
+    assert rel_err(losses_g[0], losses_g[1]) > 1e-7  # the second update saw the first one's parameters
+    for (k, pg), (_, pe) in zip(m_graph.named_parameters(), m_eager.named_parameters()):
+        # the first Adam steps move every weight by ~lr * sign(g): fp32-atomic reordering of a near-zero gradient shows up
+        # as a few 1e-5 of the largest weight
+        assert rel_err(pg, pe) < 1e-4, k

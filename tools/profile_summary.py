@@ -53,11 +53,12 @@ for r in rr[2:]:
         v, u = float(r[h.index(k)].replace(",", "")), rr[1][h.index(k)]
         return v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[u]
 
-    key = "rollout_fwd" if "fwd" in name else "rollout_bwd"
-    traffic[f"walker:2500:bf16:{key}"] = by("dram__bytes_read.sum") + by("dram__bytes_write.sum")
+    if "_tc_" in name:  # the tcgen05 imagination rollouts (the fp32 observation rollouts are listed in the table only)
+        key = "rollout_fwd" if "fwd" in name else "rollout_bwd"
+        traffic[f"walker:2500:bf16:{key}"] = by("dram__bytes_read.sum") + by("dram__bytes_write.sum")
 with open(os.path.join(ROOT, "profiles", f"{tag}_kernels.md"), "w") as f:
     f.write(f"# {tag}: launch list ({os.path.basename(launch_csv)}) and ncu --set full of the rollout kernels "
-            f"(tools/prof_tc.py, 2 500 start states x 15)\n\n" + "\n".join(lines) + "\n" + "\n".join(full) + "\n")
+            f"(tools/prof_r2.py: one whole RSSM update, 50 x 50 observed + 2 500 x 15 imagined states)\n\n" + "\n".join(lines) + "\n" + "\n".join(full) + "\n")
 with open(os.path.join(ROOT, "profiles", "ncu_traffic.json"), "w") as f:
     json.dump(traffic, f, indent=1)
 print("\n".join(lines[:12]))
