@@ -905,13 +905,20 @@ int rollout_tc_supported(const drm_rollout* r) {
     return 1;
 }
 
-// Rows per CTA: 64-row half tiles (see chain_mma) while they put more CTAs on the 148 SMs than 128-row tiles would.
+// Rows per CTA.  64-row half tiles (see chain_mma) put more CTAs on the SMs than 128-row tiles while the batch is small.
+// One window goes back to 128 rows: when the 64-row tiles would fill the machine in a single wave they leave no SMs for
+// the head kernels that run BESIDE the rollout (algo.py), and half as many 128-row tiles plus overlapped heads win
+// (8 192 start states = one GPU's shard of BASELINE configs[3] at 8 GPUs: 1.89 -> 1.71 ms per step; 4 096: 64 rows stay
+// 1.11 vs 1.45; 12 288: 64 rows stay 3.15 vs 3.42 -- profiles/r2_experiments.md).
 static int tile_rows_for(int n) {
-    const char* e = getenv("DRM_ROLLOUT_TR");  // developer / test override (64 or 128), read on every call
-    const int forced = e ? atoi(e) : 0;
+    static int forced = -1;  // developer / test override DRM_ROLLOUT_TR = 64 | 128, read once
+    if (forced < 0) { const char* e = getenv("DRM_ROLLOUT_TR"); forced = e ? atoi(e) : 0; }
     if (forced == 64 || forced == 128) return forced;
-    const int t128 = (n + 127) / 128;
-    return t128 < num_sms() ? 64 : 128;
+    const int sms = num_sms();
+    const int t64 = (n + 63) / 64, t128 = (n + 127) / 128;
+    if (t128 >= sms) return 128;
+    if (t64 > sms - 32 && t64 <= sms) return 128;
+    return 64;
 }
 static size_t tcm_bytes_r(int tr, size_t tiles, int chunks) { return tiles * (size_t)chunks * tr * 16; }
 

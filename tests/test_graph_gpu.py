@@ -174,4 +174,5 @@ def test_whole_update_graph_matches_eager_update(use_pcont):
     for (k, pg), (_, pe) in zip(m_graph.named_parameters(), m_eager.named_parameters()):
         # the first Adam steps move every weight by ~lr * sign(g): fp32-atomic reordering of a near-zero gradient shows up
         # as a few 1e-5 of the largest weight
-        assert rel_err(pg, pe) < 1e-4, k
+        # (conv weights: cuDNN's weight-gradient kernels reduce with atomics too, a few 1e-4)
+        assert rel_err(pg, pe) < (1e-3 if k.startswith("observation_") else 1e-4), k

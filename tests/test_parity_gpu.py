@@ -364,3 +364,45 @@ def test_full_size_loss_section_vs_oracle(cuda):
             continue
         assert k in cg, k
         assert rel_err(cg[k], gr) < FP32_TOL, (k, rel_err(cg[k], gr))
+
+
+@pytest.mark.parametrize("prec,tol", [("fp32", FP32_TOL), ("bf16", 1e-2)])
+def test_scaled_rssm_config_vs_oracle(cuda, prec, tol):
+    """BASELINE.json configs[4]: stoch 60 / deter 600 / hidden 600 (GRU weights alone 2.16 M parameters: beyond what the
+    tcgen05 rollout keeps per CTA, and 660 input features beyond the tcgen05 MLP's 512), heads at the reference defaults.
+    Both precisions run the fp32 kernels there; the whole loss section against the fp64 oracle."""
+    from dreamer_pytorch_b200 import noise
+    from dreamer_pytorch_b200.algo import dreamer_loss
+    from dreamer_pytorch_b200.dropin.agent import AtariDreamerModel
+    from dreamer_pytorch_b200.precision import precision
+
+    A, S, D, Hd, T, B, H = 6, 60, 600, 600, 4, 5, 6
+    w = O.make_weights(O.weight_shapes(A, S=S, D=D, Hd=Hd, conv=True), 21)
+    g = torch.Generator().manual_seed(22)
+    embed = torch.randn(T, B, 1024, generator=g)
+    action = torch.rand(T, B, A, generator=g) * 2 - 1
+    reward = torch.randn(T, B, 1, generator=g)
+    nz = O.make_noise(T, B, T * B, H, S, A, 23)
+    wl = {k: v.double().requires_grad_(True) for k, v in w.items()}
+    nz64 = {k: v.double() for k, v in nz.items()}
+    ref = O.dreamer_loss(wl, None, torch.cat([action[:1], action]).double(),
+                         torch.cat([reward[:1, :, 0], reward[:, :, 0]]).double(), None, nz64, horizon=H,
+                         obs_embed=embed.double())
+    names = [k for k in wl if not k.startswith("observation_")]
+    rgrads = dict(zip(names, torch.autograd.grad(ref["model_loss"] + ref["actor_loss"] + ref["value_loss"],
+                                                 [wl[k] for k in names], allow_unused=True)))
+    model = AtariDreamerModel(action_shape=(A,), action_dist="tanh_normal", stochastic_size=S, deterministic_size=D,
+                              hidden_size=Hd)
+    model.load_state_dict(O.expand_aliases(w))
+    model = model.to(cuda).train()
+    with precision(prec), noise.injected(eps_prior=[nz["eps_prior_obs"], nz["eps_prior_img"]],
+                                         eps_post=[nz["eps_post_obs"]], noise_act=[nz["noise_act"]]):
+        ml, al, vl, _ = dreamer_loss(model, None, action.to(cuda), reward.to(cuda), None, horizon=H,
+                                     obs_embed=embed.to(cuda))
+        ml.backward(); al.backward(); vl.backward()
+    for got, want in ((ml, ref["model_loss"]), (al, ref["actor_loss"]), (vl, ref["value_loss"])):
+        assert rel_err(got, want) < tol
+    cg = _canon_grads(model)
+    for k, gr in rgrads.items():
+        if gr is not None:
+            assert rel_err(cg[k], gr) < tol, (k, rel_err(cg[k], gr))
