@@ -262,6 +262,8 @@ __device__ __forceinline__ void cta_linear_narrow(const float* __restrict__ W, i
 // Rows-per-CTA dispatch: instantiate kernels for these tile heights only.
 #define DRM_DISPATCH_R(Rv, ...)                                \
     switch (Rv) {                                              \
+        case 1:  { constexpr int R = 1;  __VA_ARGS__; } break; \
+        case 2:  { constexpr int R = 2;  __VA_ARGS__; } break; \
         case 4:  { constexpr int R = 4;  __VA_ARGS__; } break; \
         case 8:  { constexpr int R = 8;  __VA_ARGS__; } break; \
         case 12: { constexpr int R = 12; __VA_ARGS__; } break; \
@@ -275,11 +277,11 @@ __device__ __forceinline__ void cta_linear_narrow(const float* __restrict__ W, i
 // Picks the tile height: the smallest supported R that covers ceil(n / num_sms()) rows (so one
 // wave of CTAs finishes the job), capped by what fits in shared memory.
 inline int pick_rows(int n, size_t smem_bytes_per_row, size_t smem_fixed) {
-    static const int opts[] = {4, 8, 12, 16, 20, 24, 32};
+    static const int opts[] = {1, 2, 4, 8, 12, 16, 20, 24, 32};
     const int sms = num_sms();
     int want = (n + sms - 1) / sms;
     int best = 0;
-    for (int i = 0; i < 7; ++i) {
+    for (int i = 0; i < 9; ++i) {
         int R = opts[i];
         if (smem_fixed + (size_t)R * smem_bytes_per_row > (size_t)kMaxSmem) break;
         best = R;

@@ -343,7 +343,7 @@ int launch_linear_dx(const float* dy, int M, int nout, const float* W, int w_ld,
     return launch_mlp_kernel(p, true, stream);
 }
 
-void warm_mlp() { warm_kernel(mlp_fwd_kernel<4>); warm_kernel(mlp_fwd_kernel<8>); warm_kernel(mlp_fwd_kernel<12>); warm_kernel(mlp_fwd_kernel<16>); warm_kernel(mlp_fwd_kernel<20>); warm_kernel(mlp_fwd_kernel<24>); warm_kernel(mlp_fwd_kernel<32>); warm_kernel(mlp_bwd_kernel<4>); warm_kernel(mlp_bwd_kernel<8>); warm_kernel(mlp_bwd_kernel<12>); warm_kernel(mlp_bwd_kernel<16>); warm_kernel(mlp_bwd_kernel<20>); warm_kernel(mlp_bwd_kernel<24>); warm_kernel(mlp_bwd_kernel<32>); warm_kernel(wgrad_kernel); }
+void warm_mlp() { warm_kernel(mlp_fwd_kernel<1>); warm_kernel(mlp_fwd_kernel<2>); warm_kernel(mlp_bwd_kernel<1>); warm_kernel(mlp_bwd_kernel<2>); warm_kernel(mlp_fwd_kernel<4>); warm_kernel(mlp_fwd_kernel<8>); warm_kernel(mlp_fwd_kernel<12>); warm_kernel(mlp_fwd_kernel<16>); warm_kernel(mlp_fwd_kernel<20>); warm_kernel(mlp_fwd_kernel<24>); warm_kernel(mlp_fwd_kernel<32>); warm_kernel(mlp_bwd_kernel<4>); warm_kernel(mlp_bwd_kernel<8>); warm_kernel(mlp_bwd_kernel<12>); warm_kernel(mlp_bwd_kernel<16>); warm_kernel(mlp_bwd_kernel<20>); warm_kernel(mlp_bwd_kernel<24>); warm_kernel(mlp_bwd_kernel<32>); warm_kernel(wgrad_kernel); }
 
 }  // namespace drm
 

@@ -286,6 +286,6 @@ int launch_rollout_fwd(const RollDev& p, cudaStream_t stream) {
     return DRM_OK;
 }
 
-void warm_rollout_fwd() { warm_kernel(rollout_fwd_kernel<4>); warm_kernel(rollout_fwd_kernel<8>); warm_kernel(rollout_fwd_kernel<12>); warm_kernel(rollout_fwd_kernel<16>); warm_kernel(rollout_fwd_kernel<20>); warm_kernel(rollout_fwd_kernel<24>); warm_kernel(rollout_fwd_kernel<32>); }
+void warm_rollout_fwd() { warm_kernel(rollout_fwd_kernel<1>); warm_kernel(rollout_fwd_kernel<2>); warm_kernel(rollout_fwd_kernel<4>); warm_kernel(rollout_fwd_kernel<8>); warm_kernel(rollout_fwd_kernel<12>); warm_kernel(rollout_fwd_kernel<16>); warm_kernel(rollout_fwd_kernel<20>); warm_kernel(rollout_fwd_kernel<24>); warm_kernel(rollout_fwd_kernel<32>); }
 
 }  // namespace drm
