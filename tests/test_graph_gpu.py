@@ -174,5 +174,16 @@ def test_whole_update_graph_matches_eager_update(use_pcont):
     for (k, pg), (_, pe) in zip(m_graph.named_parameters(), m_eager.named_parameters()):
         # the first Adam steps move every weight by ~lr * sign(g): fp32-atomic reordering of a near-zero gradient shows up
         # as a few 1e-5 of the largest weight
-        # (conv weights: cuDNN's weight-gradient kernels reduce with atomics too, a few 1e-4)
-        assert rel_err(pg, pe) < (1e-3 if k.startswith("observation_") else 1e-4), k
+        if not k.startswith("observation_"):
+            assert rel_err(pg, pe) < 1e-4, k
+            continue
+        # conv stack (cuDNN, outside the hot path): its weight-gradient kernels reduce with atomics and may pick another
+        # algorithm under capture, so gradients carry ~1e-3 relative noise.  Comparing PARAMETERS after Adam is then
+        # ill-conditioned exactly where |g| is at that noise level: Adam's first updates are lr * sign(g), a flipped sign
+        # moves the weight by 2 lr per update (a normwise 1.2e-3 was observed on the decoder's Linear with ~0.1 % of its
+        # elements flipped).  What must hold: no element further apart than two Adam trajectories can get in two updates
+        # (2 x 2 lr), and all but a small fraction of the elements much closer than one update.
+        lr = 6e-4
+        d = (pg.detach() - pe.detach()).abs()
+        assert float(d.max()) <= 4.04 * lr, (k, float(d.max()))
+        assert float((d > 0.1 * lr).float().mean()) < 0.01, (k, float((d > 0.1 * lr).float().mean()))
