@@ -126,6 +126,8 @@ class drm_replay_gather_call(C.Structure):
 STRUCTS = {s.__name__: s for s in (drm_replay_gather_call, drm_policy_mode_call, drm_image_logprob_call, drm_clip_adam_call, drm_mlp, drm_mlp_grad, drm_rssm, drm_rssm_grad, drm_rollout, drm_rollout_grad,
                                    drm_mlp_call, drm_mlp_bwd_call, drm_returns_loss_call, drm_kl_call)}
 
+NOALLOC_SCRATCH_BYTES = 2 << 20  # DRM_NOALLOC_SCRATCH_BYTES
+
 # every symbol include/dreamer_b200.h declares: name -> (restype, argtypes)
 SYMBOLS = {
     "drm_version": (C.c_int, []),
@@ -145,6 +147,8 @@ SYMBOLS = {
     "drm_mlp_workspace_bytes": (C.c_size_t, [C.POINTER(drm_mlp_call)]),
     "drm_mlp_fwd": (C.c_int, [C.POINTER(drm_mlp_call), P]),
     "drm_mlp_bwd": (C.c_int, [C.POINTER(drm_mlp_bwd_call), P]),
+    "drm_mlp_noalloc_scratch_bytes": (C.c_size_t, [C.POINTER(drm_mlp_call)]),
+    "drm_mlp_fwd_noalloc": (C.c_int, [C.POINTER(drm_mlp_call), P]),
     "drm_returns_loss": (C.c_int, [C.POINTER(drm_returns_loss_call), P]),
     "drm_clip_adam": (C.c_int, [C.POINTER(drm_clip_adam_call), P]),
     "drm_image_logprob_fwd": (C.c_int, [C.POINTER(drm_image_logprob_call), P]),

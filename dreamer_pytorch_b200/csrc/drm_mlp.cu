@@ -1,6 +1,7 @@
 // Batched MLP (DenseModel / ActionDecoder feed-forward stack) forward, data-gradient backward and
 // the weight-gradient GEMM.  fp32 FFMA path.  Reference: dreamer/models/dense.py:28-43.
 #include "drm_mlp.cuh"
+#include <mutex>
 
 namespace drm {
 
@@ -493,6 +494,84 @@ int drm_mlp_bwd(const drm_mlp_bwd_call* bc, void* stream_) {
         }
     }
     return DRM_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// drm_mlp_fwd_noalloc: the fp32 inference forward of drm_mlp_fwd for callers that cannot allocate device memory (code
+// under CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The only scratch the fp32 forward needs -- the re-laid (packed) weight
+// matrices -- lives in a file-scope __device__ array instead of a caller-provided workspace: DRM_NOALLOC_SCRATCH_BYTES per
+// GPU that loads the library, held until the process exits.  Every call on a device shares that array, so calls that
+// overlap on the GPU (two streams, two threads) race; issue them in one stream order.  The array keeps the previous
+// call's contents; nothing needs to start at zero, because the packing launch rewrites every float (padding included)
+// of the region the MLP kernel then reads.
+// ---------------------------------------------------------------------------------------------
+namespace drm {
+constexpr size_t kNoAllocScratchFloats = DRM_NOALLOC_SCRATCH_BYTES / sizeof(float);
+static __device__ __align__(256) float g_noalloc_scratch[kNoAllocScratchFloats];
+
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol, not a device address: the address is looked up
+// once per device, with that device current, and cached.
+constexpr int kNoAllocMaxDevices = 64;
+static float* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+static std::mutex g_noalloc_mu;
+
+static int noalloc_scratch(float** out) {
+    int dev = 0;
+    DRM_CUDA_OK(cudaGetDevice(&dev));
+    DRM_REQUIRE(dev >= 0 && dev < kNoAllocMaxDevices, DRM_E_ARG, "device ordinal beyond 63");
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (g_noalloc_ptr[dev] == nullptr) {
+        float* ptr = nullptr;
+        DRM_CUDA_OK(cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch));
+        DRM_REQUIRE(ptr != nullptr && ((size_t)ptr & 255) == 0, DRM_E_CUDA, "bad address for the static scratch array");
+        g_noalloc_ptr[dev] = ptr;
+    }
+    *out = g_noalloc_ptr[dev];
+    return DRM_OK;
+}
+}  // namespace drm
+
+extern "C" {
+
+size_t drm_mlp_noalloc_scratch_bytes(const drm_mlp_call* c) { return c ? fwd_pack_floats(c) * sizeof(float) : 0; }
+
+int drm_mlp_fwd_noalloc(const drm_mlp_call* c, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    int rc = validate(c); if (rc) return rc;
+    rc = check_device(); if (rc) return rc;
+    const drm_mlp& m = c->mlp;
+    DRM_REQUIRE(c->precision == DRM_FP32, DRM_E_ARG, "drm_mlp_fwd_noalloc runs the fp32 kernels only");
+    DRM_REQUIRE(!c->training, DRM_E_ARG, "drm_mlp_fwd_noalloc is inference only (training = 0, no save buffer)");
+    DRM_REQUIRE(c->wait_flags == nullptr, DRM_E_ARG, "drm_mlp_fwd_noalloc does not take producer gating");
+    const size_t need = fwd_pack_floats(c);
+    if (need > kNoAllocScratchFloats) {
+        set_error("drm_mlp_fwd_noalloc: packed weights need %zu bytes, the static scratch holds %zu "
+                  "(DRM_NOALLOC_SCRATCH_BYTES); use drm_mlp_fwd with a caller workspace", need * sizeof(float),
+                  (size_t)DRM_NOALLOC_SCRATCH_BYTES);
+        return DRM_E_WORKSPACE;
+    }
+    if (c->M == 0) return DRM_OK;
+    DRM_REQUIRE(c->x0 && c->y && (c->k1 == 0 || c->x1), DRM_E_ARG, "null io pointer");
+    float* scratch = nullptr;
+    rc = noalloc_scratch(&scratch); if (rc) return rc;
+    MlpDev p; fill_common(p, c);
+    Packer pk(scratch);
+    for (int l = 0; l < m.n_linear; ++l) {
+        const int nout = l == m.n_linear - 1 ? m.out_dim : m.hidden;
+        if (l == 0) {
+            p.Wp[0] = pk.fwd(m.W[0], m.in_dim, 0, nout, 0, c->k0);
+            if (c->k1 > 0) pk.fwd(m.W[0], m.in_dim, 0, nout, c->k0, c->k1);
+        } else {
+            p.Wp[l] = pk.fwd(m.W[l], m.hidden, 0, nout, 0, m.hidden);
+        }
+        p.ldw[l] = rup(nout, 32);
+    }
+    DRM_REQUIRE(pk.off <= kNoAllocScratchFloats, DRM_E_WORKSPACE, "packed weights overflow the static scratch");
+    rc = launch_pack(pk.jobs, stream); if (rc) return rc;
+    return launch_mlp_kernel(p, false, stream);
 }
 
 }  // extern "C"

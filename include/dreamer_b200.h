@@ -321,6 +321,21 @@ size_t drm_mlp_workspace_bytes(const drm_mlp_call* c);
 int drm_mlp_fwd(const drm_mlp_call* c, void* stream);
 int drm_mlp_bwd(const drm_mlp_bwd_call* c, void* stream);
 
+/* drm_mlp_fwd_noalloc -- NO COUNTERPART IN THE REFERENCE; added for callers that
+ * cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ * Same result as drm_mlp_fwd for an fp32 inference forward (precision = DRM_FP32, training = 0, wait_flags = NULL), but
+ * c->workspace / c->save are IGNORED: the packed-weight scratch is a static __device__ array of
+ * DRM_NOALLOC_SCRATCH_BYTES inside the library (held by every GPU that loads it, until exit).  The call allocates
+ * nothing (no cudaMalloc / cudaFree / allocating library routine).  Returns DRM_E_WORKSPACE, with the sizes in
+ * drm_last_error(), when drm_mlp_noalloc_scratch_bytes(c) exceeds the limit (the reference's widest head,
+ * 230 -> 3 x 300 -> 1, needs 1.05 MiB).  All calls on a device share the array: calls that overlap on the GPU (different
+ * streams or threads) race -- keep them in one stream order.  Nothing has to be cleared between calls (the packing
+ * launch rewrites every float the MLP kernel reads).  drm_prof_enable(1) makes the diagnostics create CUDA events;
+ * leave it off where event creation is forbidden too. */
+#define DRM_NOALLOC_SCRATCH_BYTES (2u << 20)
+size_t drm_mlp_noalloc_scratch_bytes(const drm_mlp_call* c);
+int drm_mlp_fwd_noalloc(const drm_mlp_call* c, void* stream);
+
 int drm_returns_loss(const drm_returns_loss_call* c, void* stream);
 
 /* ---- optimizer tail of one parameter group: clip_grad_norm_ + Adam.step ---------------------------

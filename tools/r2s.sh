@@ -1,0 +1,3 @@
+#!/bin/bash
+echo "== alone, fresh process"; python -m pytest tests/test_zz_no_alloc.py -m gpu -q 2>&1 | tail -8
+echo "== whole suite"; python -m pytest tests -m gpu -q -x 2>&1 | tail -8
