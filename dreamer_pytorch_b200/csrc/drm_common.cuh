@@ -216,14 +216,95 @@ __device__ __forceinline__ void cta_linear_splitk(const Seg& s0, const Seg& s1, 
         epi(r, c, v);
     }
 }
-// floats of scratch a wide CTA needs: one [R][32] block per (K part, column block) slot, at most 2 x warps slots
-__host__ __device__ inline int splitk_scratch_floats(int R) { return 2 * (kWideThreads / 32) * R * 32; }
+// Very few rows per CTA (R <= 4; the observation rollout runs ONE row per CTA): the 32-column form above keeps at most
+// 8 x 128 B of weights in flight per warp and was bound by L2 latency (ncu: 59 % of issue slots, long-scoreboard stalls).
+// Here a lane owns FOUR adjacent columns (one 16-byte load per k), a warp a 128-column block, and K is split over all the
+// other warps (200 outputs: 2 column blocks x 16 K parts of ~12 k each), so that every weight byte of a layer is requested
+// within the first few instructions of the call and the layer costs about one L2 round trip.  Scratch [warp][R][128].
+template <int R>
+__device__ __forceinline__ void seg_accumulate4(float (&acc)[R][4], const Seg& s, int ldw, int col) {
+    const float* __restrict__ wp = s.W + col;
+    const float* __restrict__ xp = s.X;
+    const int ldx = s.ldx;
+#pragma unroll(R <= 2 ? 3 : 1)
+    for (int k = 0; k < s.K4; k += 4) {
+        const float4 w0 = __ldg(reinterpret_cast<const float4*>(wp + (size_t)(k + 0) * ldw));
+        const float4 w1 = __ldg(reinterpret_cast<const float4*>(wp + (size_t)(k + 1) * ldw));
+        const float4 w2 = __ldg(reinterpret_cast<const float4*>(wp + (size_t)(k + 2) * ldw));
+        const float4 w3 = __ldg(reinterpret_cast<const float4*>(wp + (size_t)(k + 3) * ldw));
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const float4 x = *reinterpret_cast<const float4*>(xp + r * ldx + k);
+            acc[r][0] = fmaf(x.w, w3.x, fmaf(x.z, w2.x, fmaf(x.y, w1.x, fmaf(x.x, w0.x, acc[r][0]))));
+            acc[r][1] = fmaf(x.w, w3.y, fmaf(x.z, w2.y, fmaf(x.y, w1.y, fmaf(x.x, w0.y, acc[r][1]))));
+            acc[r][2] = fmaf(x.w, w3.z, fmaf(x.z, w2.z, fmaf(x.y, w1.z, fmaf(x.x, w0.z, acc[r][2]))));
+            acc[r][3] = fmaf(x.w, w3.w, fmaf(x.z, w2.w, fmaf(x.y, w1.w, fmaf(x.x, w0.w, acc[r][3]))));
+        }
+    }
+}
+
+template <int R, class Epi>
+__device__ __forceinline__ void cta_linear_splitk4(const Seg& s0, const Seg& s1, int ldw, int nout, Epi epi, float* scratch) {
+    const int nwarps = blockDim.x >> 5;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int CB = (nout + 127) >> 7;                    // column blocks of 128
+    const int per = CB < nwarps ? CB : nwarps;           // column blocks per round (one round unless nout > 128 x warps)
+    const int ksplit = nwarps / per;                     // K parts
+    const int Ktot = s0.K4 + s1.K4;
+    for (int cb0 = 0; cb0 < CB; cb0 += per) {
+        __syncthreads();                                 // scratch may still be read by the previous reduction
+        const int cbl = warp % per, ks = warp / per;
+        const int col = (cb0 + cbl) * 128 + lane * 4;
+        if (ks < ksplit && cb0 + cbl < CB) {
+            float acc[R][4];
+#pragma unroll
+            for (int r = 0; r < R; ++r) { acc[r][0] = acc[r][1] = acc[r][2] = acc[r][3] = 0.f; }
+            if (col < ldw) {                             // ldw is a multiple of 32: a float4 at col < ldw stays inside the row
+                int kbeg = (int)(((long long)Ktot * ks / ksplit) & ~3LL), kend = (int)(((long long)Ktot * (ks + 1) / ksplit) & ~3LL);
+                if (ks == ksplit - 1) kend = Ktot;
+                if (kbeg < s0.K4) {
+                    Seg p = s0;
+                    const int e = kend < s0.K4 ? kend : s0.K4;
+                    p.W = s0.W + (size_t)kbeg * ldw; p.X = s0.X + kbeg; p.K4 = e - kbeg;
+                    seg_accumulate4<R>(acc, p, ldw, col);
+                }
+                if (kend > s0.K4 && s1.K4 > 0) {
+                    Seg p = s1;
+                    const int b = kbeg > s0.K4 ? kbeg - s0.K4 : 0;
+                    p.W = s1.W + (size_t)b * ldw; p.X = s1.X + b; p.K4 = kend - s0.K4 - b;
+                    seg_accumulate4<R>(acc, p, ldw, col);
+                }
+            }
+            float* dst = scratch + (size_t)warp * R * 128 + lane * 4;
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                *reinterpret_cast<float4*>(dst + r * 128) = make_float4(acc[r][0], acc[r][1], acc[r][2], acc[r][3]);
+        }
+        __syncthreads();
+        const int ncol = (CB - cb0 < per ? CB - cb0 : per) * 128;
+        for (int idx = threadIdx.x; idx < R * ncol; idx += blockDim.x) {
+            const int r = idx / ncol, cl = idx - r * ncol;
+            const int c = cb0 * 128 + cl;
+            if (c >= nout) continue;
+            const int cbl2 = cl >> 7, ln = cl & 127;
+            float v = 0.f;
+            for (int k2 = 0; k2 < ksplit; ++k2) v += scratch[((size_t)(k2 * per + cbl2) * R + r) * 128 + ln];
+            epi(r, c, v);
+        }
+    }
+}
+// floats of scratch a wide CTA needs.  R <= 4: [warp][R][128] (cta_linear_splitk4); R = 8: one [R][32] block per
+// (K part, column block) slot, at most 2 x warps slots (cta_linear_splitk)
+__host__ __device__ inline int splitk_scratch_floats(int R) {
+    return R <= 4 ? (kWideThreads / 32) * R * 128 : 2 * (kWideThreads / 32) * R * 32;
+}
 
 template <int R, class Epi>
 __device__ __forceinline__ void cta_linear(const Seg& s0, const Seg& s1, int ldw, int nout, Epi epi, float* scratch = nullptr) {
     if constexpr (R <= 8) {
         if (scratch != nullptr && blockDim.x > kThreads) {
-            cta_linear_splitk<R>(s0, s1, ldw, nout, epi, scratch);
+            if constexpr (R <= 4) cta_linear_splitk4<R>(s0, s1, ldw, nout, epi, scratch);
+            else cta_linear_splitk<R>(s0, s1, ldw, nout, epi, scratch);
             return;
         }
     }

@@ -277,7 +277,7 @@ int launch_rollout_bwd(const RollDev& p, cudaStream_t stream) {
     const size_t per_row = (size_t)bwd_smem_floats_per_row(p) * sizeof(float);
     const int Rv = pick_rows(p.n, per_row, 0);
     DRM_REQUIRE(Rv > 0, DRM_E_SHAPE, "model too wide for shared memory");
-    const bool wide = Rv <= 8;
+    const bool wide = Rv <= 8 && per_row * Rv + (size_t)splitk_scratch_floats(Rv) * sizeof(float) <= (size_t)kMaxSmem;
     const size_t smem = per_row * Rv + (wide ? (size_t)splitk_scratch_floats(Rv) * sizeof(float) : 0);
     const int nthreads = wide ? kWideThreads : kThreads;
     const int tiles = (p.n + Rv - 1) / Rv;
