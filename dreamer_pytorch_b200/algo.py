@@ -68,6 +68,35 @@ def _overlap_ok(key) -> bool:
     return _WARM.get(key, 0) >= 1
 
 
+# Single tenant: kernels that run beside each other count on the SMs their producers leave idle, and the side streams are
+# per device.  A pass issued on ANOTHER stream while the previous pass on this device may still be running must not
+# make the same assumption (two sets of spinning consumers could keep each other's producers off the SMs until the
+# bounded spin traps): it is demoted to plain stream order, which never waits on anything but its own stream.
+# Passes on one stream (every training loop, every graph) are ordered by the stream and never take this branch.
+_LAST_PASS = {}     # device index -> (cuda_stream handle, end-of-pass event)
+demoted_passes = 0  # forward / backward halves demoted to plain order because of a pass in flight on another stream
+
+
+def _exclusive(device) -> bool:
+    global demoted_passes
+    if torch.cuda.is_current_stream_capturing():
+        return True  # a capture owns its streams; replays of one graph are ordered by the stream they are launched on
+    last = _LAST_PASS.get(device.index)
+    if last is None or last[0] == torch.cuda.current_stream(device).cuda_stream or last[1].query():
+        return True
+    demoted_passes += 1
+    return False
+
+
+def _mark_pass(device):
+    if torch.cuda.is_current_stream_capturing():
+        return
+    cur = torch.cuda.current_stream(device)
+    ev = torch.cuda.Event()
+    ev.record(cur)
+    _LAST_PASS[device.index] = (cur.cuda_stream, ev)
+
+
 def _side_stream(device, k: int = 0) -> "torch.cuda.Stream":
     key = (device.type, device.index, k)
     if key not in _SIDE:
@@ -109,7 +138,7 @@ class _ActorLossFn(torch.autograd.Function):
         ctx.set_materialize_grads(False)  # 12 by-products: no zero tensors for their (unused) gradients
         flags = tiles = fork = None
         wkey = _warm_key(stoch_dev(t), prec, cfg, pcont_w)
-        warm = _overlap_ok(wkey)
+        warm = _overlap_ok(wkey) and _exclusive(stoch_dev(t))
         pipe_heads, prepare = _PIPELINE_HEADS and warm, _PREPARE_BACKWARD and warm
         if prec == "bf16" and pipe_heads:
             # zero-filled on the main stream BEFORE the fork: the head kernels on the side streams poll these counters
@@ -172,6 +201,7 @@ class _ActorLossFn(torch.autograd.Function):
                                lambda_)
         ctx.pack = (cfg, t, rssm, actor, save, reward_w, value_w, pcont_w, rsave, vsave, psave, out, x0, x1, prec, shared,
                     plans, tiles[0] if tiles else 0, wkey)
+        _mark_pass(x0.device)
         aux = (t["prior_mean"], t["prior_std"], t["prior_stoch"], t["deter"], t["action_out"], reward.view(H, N, 1),
                value.view(H, N, 1), out["returns"].view(H - 1, N, 1), out["disc"].view(H - 1, N, 1),
                out["losses"][1].clone(), out["d_value_pred"], vsave if vsave is not None else torch.empty(0))
@@ -207,7 +237,7 @@ class _ActorLossFn(torch.autograd.Function):
         # rollout kernel waits on (step_rows_done / g_wait_flags).  Grids are capped so that all of them are resident.
         free = (_sm_count(g_loss.device) - roll_tiles) // len(heads) if roll_tiles > 0 else 0
         g_wait = None
-        if prec == "bf16" and _PIPELINE_BACKWARD and free >= 16 and _overlap_ok(wkey):
+        if prec == "bf16" and _PIPELINE_BACKWARD and free >= 16 and _overlap_ok(wkey) and _exclusive(g_loss.device):
             mlp_tiles = (H * N + 127) // 128
             cnt = torch.zeros(len(heads) * mlp_tiles + H, dtype=torch.int32, device=g_loss.device)
             steps_done = cnt[len(heads) * mlp_tiles:]
@@ -252,6 +282,7 @@ class _ActorLossFn(torch.autograd.Function):
         if follow is not None:
             main.wait_stream(side)
         _WARM[wkey] = _WARM.get(wkey, 0) + 1
+        _mark_pass(g_loss.device)
         return (None, *gactor)
 
 

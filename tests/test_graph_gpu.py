@@ -105,6 +105,68 @@ def test_kernels_beside_each_other_match_stream_order(use_pcont):
             assert rel_err(ga, gb) < 1e-4, mode                                 # fp32 atomics reorder between runs
 
 
+def test_two_passes_on_two_streams_of_one_device():
+    """Single-tenant rule: a pass issued on another stream while the previous pass on the device is
+    still in flight must not also count on idle SMs -- it is demoted to plain stream order (algo._exclusive) and both
+    passes finish with the results they give alone; no bounded-spin trap, no hang."""
+    from dreamer_pytorch_b200 import algo, noise
+    from dreamer_pytorch_b200.dropin.agent import AtariDreamerModel
+    from dreamer_pytorch_b200.dropin.rnns import RSSMState
+    from dreamer_pytorch_b200.precision import precision
+
+    dev = torch.device("cuda:0")
+    torch.manual_seed(5)
+    A, N, H = 6, 2500, 15
+    model = AtariDreamerModel(action_shape=(A,), action_dist="tanh_normal").to(dev).train()
+    actor_p, value_p = list(model.action_decoder.parameters()), list(model.value_model.parameters())
+    g = torch.Generator().manual_seed(6)
+    inputs = []
+    for _ in range(2):
+        inputs.append((torch.randn(N, 30, generator=g).to(dev), torch.tanh(torch.randn(N, 200, generator=g)).to(dev),
+                       torch.randn(H, N, 30, generator=g).to(dev), torch.randn(H, N, A, generator=g).to(dev)))
+
+    def forward(i):
+        stoch, deter, eps, nza = inputs[i]
+        with noise.injected(eps_prior=[eps], noise_act=[nza]):
+            return algo.imagination_losses(model, RSSMState(stoch, stoch, stoch, deter), H)
+
+    def backward(al, vl):
+        return torch.autograd.grad(al, actor_p) + torch.autograd.grad(vl, value_p)
+
+    with precision("bf16"):
+        for _ in range(2):  # first pass of a configuration is plain anyway (algo._WARM); second one overlapped
+            al, vl, _ = forward(0)
+            backward(al, vl)
+        alone = []
+        for i in range(2):
+            al, vl, info = forward(i)
+            alone.append((al.detach().clone(), vl.detach().clone(), info.reward.clone(), backward(al, vl)))
+        torch.cuda.synchronize()
+        before = algo.demoted_passes
+        s = [torch.cuda.Stream(), torch.cuda.Stream()]
+        torch.cuda._sleep(200_000_000)  # ~0.1 s on the default stream: both streams start together, behind it
+        for st in s:
+            st.wait_stream(torch.cuda.current_stream())
+        out = [None, None]
+        for i in range(2):  # both forwards, then both backwards: everything is enqueued before anything runs
+            with torch.cuda.stream(s[i]):
+                out[i] = forward(i)
+        grads = [None, None]
+        for i in range(2):
+            with torch.cuda.stream(s[i]):
+                grads[i] = backward(out[i][0], out[i][1])
+        for st in s:
+            torch.cuda.current_stream().wait_stream(st)
+        torch.cuda.synchronize()  # a trap in a spinning kernel would surface here as a CUDA error
+    assert algo.demoted_passes - before >= 2  # the second stream's forward and at least one backward went plain
+    for i in range(2):
+        al, vl, info = out[i]
+        assert torch.equal(info.reward, alone[i][2])  # head outputs: bit-identical whatever the schedule
+        assert rel_err(al, alone[i][0]) < 1e-6 and rel_err(vl, alone[i][1]) < 1e-6
+        for ga, gb in zip(grads[i], alone[i][3]):
+            assert rel_err(ga, gb) < 1e-4  # fp32 atomics reorder between runs
+
+
 @pytest.mark.parametrize("use_pcont", [False, True])
 def test_whole_update_graph_matches_eager_update(use_pcont):
     """UpdateGraph (Dreamer.loss + 3 backwards + clip + Adam of the three groups, conv stack included, one replay) against the
