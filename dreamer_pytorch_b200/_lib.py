@@ -53,7 +53,7 @@ class drm_rollout(C.Structure):
         + [(k, P) for k in ("start_stoch", "start_deter", "action_in", "obs_embed", "eps_prior", "eps_post",
                             "noise_act", "prior_mean", "prior_std", "prior_stoch", "deter", "post_mean", "post_std",
                             "post_stoch", "action_out")]
-        + [("save", P), ("save_bytes", C.c_size_t), ("workspace", P), ("workspace_bytes", C.c_size_t), ("step_flags", P)]
+        + [("save", P), ("save_bytes", C.c_size_t), ("workspace", P), ("workspace_bytes", C.c_size_t), ("step_flags", P), ("noise_pair", P)]
     )
 
 
@@ -123,7 +123,18 @@ class drm_replay_gather_call(C.Structure):
                 ("t_offset", C.c_int32), ("row_bytes", C.c_int64), ("src", P), ("dst", P), ("t0", P), ("b", P)]
 
 
-STRUCTS = {s.__name__: s for s in (drm_replay_gather_call, drm_policy_mode_call, drm_image_logprob_call, drm_clip_adam_call, drm_mlp, drm_mlp_grad, drm_rssm, drm_rssm_grad, drm_rollout, drm_rollout_grad,
+MAX_NOISE_BLOCKS = 4
+NOISE_NORMAL, NOISE_GUMBEL = 0, 1
+NOISE_STREAMS = {"eps_prior": 0, "eps_post": 1, "noise_act": 2, "mode_noise": 3}
+
+
+class drm_noise_fill_call(C.Structure):
+    _fields_ = [("state", P), ("pair", P), ("pair_out", P), ("n_blocks", C.c_int32), ("pad_", C.c_int32),
+                ("out", P * MAX_NOISE_BLOCKS), ("numel", C.c_int64 * MAX_NOISE_BLOCKS),
+                ("stream_id", C.c_int32 * MAX_NOISE_BLOCKS), ("kind", C.c_int32 * MAX_NOISE_BLOCKS)]
+
+
+STRUCTS = {s.__name__: s for s in (drm_noise_fill_call, drm_replay_gather_call, drm_policy_mode_call, drm_image_logprob_call, drm_clip_adam_call, drm_mlp, drm_mlp_grad, drm_rssm, drm_rssm_grad, drm_rollout, drm_rollout_grad,
                                    drm_mlp_call, drm_mlp_bwd_call, drm_returns_loss_call, drm_kl_call)}
 
 NOALLOC_SCRATCH_BYTES = 2 << 20  # DRM_NOALLOC_SCRATCH_BYTES
@@ -155,6 +166,9 @@ SYMBOLS = {
     "drm_image_logprob_bwd": (C.c_int, [C.POINTER(drm_image_logprob_call), P]),
     "drm_policy_mode": (C.c_int, [C.POINTER(drm_policy_mode_call), P]),
     "drm_replay_gather": (C.c_int, [C.POINTER(drm_replay_gather_call), P]),
+    "drm_noise_next": (C.c_int, [P, P, P]),
+    "drm_noise_fill": (C.c_int, [C.POINTER(drm_noise_fill_call), P]),
+    "drm_noise_words": (C.c_int, [P, C.c_int, C.c_ulonglong, C.c_int, P, P]),
     "drm_kl_fwd": (C.c_int, [C.POINTER(drm_kl_call), P]),
     "drm_kl_bwd": (C.c_int, [C.POINTER(drm_kl_call), P]),
 }

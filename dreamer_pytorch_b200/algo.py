@@ -279,8 +279,10 @@ class _ActorLossFn(torch.autograd.Function):
                                             want_actor=True, phase=ph, plan=proll, g_wait=g_wait, wgrad_stream=follow)
         for hs in joins:
             main.wait_stream(hs)
-        if follow is not None:
-            main.wait_stream(side)
+        # always joined: the side stream's value pass reads tensors owned by the main stream's allocator pool (x0 / x1 /
+        # vsave / d_value_pred / the prepared workspace); after the join none of them can be recycled under it, whether or
+        # not value_loss.backward() is ever called
+        main.wait_stream(side)
         _WARM[wkey] = _WARM.get(wkey, 0) + 1
         _mark_pass(g_loss.device)
         return (None, *gactor)
@@ -340,17 +342,15 @@ def imagination_losses(model, start_state: RSSMState, horizon: int, discount: fl
     cfg = RolloutCfg(_lib.MODE_POLICY, horizon, N, model.transition.dims(), act_dist=model.action_dist,
                      mean_scale=float(dec.mean_scale), raw_init_std=float(dec.raw_init_std),
                      act_min_std=float(dec.min_std))
-    if model.action_dist == "tanh_normal" and not noise.is_injected("noise_act", "eps_prior") and (horizon * N * A) % 4 == 0:
-        # both N(0,1) blocks from one generator launch (two 16-byte aligned views of one buffer)
-        flat = torch.randn(horizon * N * (A + S), dtype=torch.float32, device=dev)
-        noise_act = flat[:horizon * N * A].view(horizon, N, A)
-        eps = flat[horizon * N * A:].view(horizon, N, S)
+    if (model.action_dist == "tanh_normal" and get_precision() == "bf16"
+            and not noise.is_injected("noise_act", "eps_prior")):
+        # tensor-core rollout: both N(0,1) blocks from ONE launch of the Philox kernel (which also advances the offset)
+        noise_act, eps = noise.fill(dev, [("noise_act", (horizon, N, A), "normal"), ("eps_prior", (horizon, N, S), "normal")])
     else:
-        if model.action_dist == "tanh_normal":
-            noise_act = noise.normal("noise_act", (horizon, N, A), dev)
-        else:
-            noise_act = noise.gumbel("noise_act", (horizon, N, A), dev)
-        eps = noise.normal("eps_prior", (horizon, N, S), dev)
+        # fp32 kernels: a {seed, offset} pair; forward and backward generate the values where they would have loaded them
+        draw = noise.normal if model.action_dist == "tanh_normal" else noise.gumbel
+        noise_act = draw("noise_act", (horizon, N, A), dev, lazy=True)
+        eps = noise.normal("eps_prior", (horizon, N, S), dev, lazy=True, pair=noise_act if noise.is_pair(noise_act) else None)
     t = dict(start_stoch=stoch, start_deter=deter, eps_prior=eps, noise_act=noise_act)
     frozen = lambda ws: [_f32c(w.detach()) for w in ws]
     rssm = frozen(model.transition.weights()) + [None] * 4

@@ -27,7 +27,7 @@ inline void warm_kernel(K kernel) {
 }
 // per translation unit: load every kernel it defines (drm_init)
 void warm_util(); void warm_mlp(); void warm_mlp_tc(); void warm_wgrad_tc(); void warm_rollout_fwd(); void warm_rollout_bwd();
-void warm_rollout_tc(); void warm_loss(); void warm_optim(); void warm_policy(); void warm_replay();
+void warm_rollout_tc(); void warm_loss(); void warm_optim(); void warm_policy(); void warm_replay(); void warm_noise();
 
 // Diagnostics (drm_launch_count / drm_prof_*): every kernel launch site bumps the counter and,
 // when profiling is on, is bracketed by a cudaEvent pair on the launching stream.
@@ -243,16 +243,28 @@ __device__ __forceinline__ void seg_accumulate4(float (&acc)[R][4], const Seg& s
     }
 }
 
+// Scratch handed to cta_linear by the wide kernels: pointer + size (the K split adapts to what fits).
+struct KScratch {
+    float* p;
+    int floats;
+};
+// Threads per CTA of the rollout kernels by tile height: <= 8 rows 1 024 (split K over the idle warps), 12..20 rows 512
+// (same, float4 form; 128 registers per thread hold the [R][4] accumulators), more rows 256 (classic form).
+__host__ __device__ constexpr int rollout_threads(int R) { return R <= 8 ? 1024 : R <= 20 ? 512 : kThreads; }
+
 template <int R, class Epi>
-__device__ __forceinline__ void cta_linear_splitk4(const Seg& s0, const Seg& s1, int ldw, int nout, Epi epi, float* scratch) {
+__device__ __forceinline__ void cta_linear_splitk4(const Seg& s0, const Seg& s1, int ldw, int nout, Epi epi, KScratch sc) {
     const int nwarps = blockDim.x >> 5;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int CB = (nout + 127) >> 7;                    // column blocks of 128
     const int per = CB < nwarps ? CB : nwarps;           // column blocks per round (one round unless nout > 128 x warps)
-    const int ksplit = nwarps / per;                     // K parts
+    int ksplit = nwarps / per;                           // K parts: as many as there are warps ...
+    const int fit = sc.p ? sc.floats / (per * R * 128) : 0;  // ... and scratch slots [K part][column block][R][128]
+    if (ksplit > fit) ksplit = fit;
+    if (ksplit < 2) ksplit = 1;
     const int Ktot = s0.K4 + s1.K4;
     for (int cb0 = 0; cb0 < CB; cb0 += per) {
-        __syncthreads();                                 // scratch may still be read by the previous reduction
+        if (ksplit > 1) __syncthreads();                 // scratch may still be read by the previous reduction
         const int cbl = warp % per, ks = warp / per;
         const int col = (cb0 + cbl) * 128 + lane * 4;
         if (ks < ksplit && cb0 + cbl < CB) {
@@ -275,11 +287,21 @@ __device__ __forceinline__ void cta_linear_splitk4(const Seg& s0, const Seg& s1,
                     seg_accumulate4<R>(acc, p, ldw, col);
                 }
             }
-            float* dst = scratch + (size_t)warp * R * 128 + lane * 4;
+            if (ksplit == 1) {                           // whole dot products in registers: no scratch, no barriers
 #pragma unroll
-            for (int r = 0; r < R; ++r)
-                *reinterpret_cast<float4*>(dst + r * 128) = make_float4(acc[r][0], acc[r][1], acc[r][2], acc[r][3]);
+                for (int r = 0; r < R; ++r) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        if (col + j < nout) epi(r, col + j, acc[r][j]);
+                }
+            } else {
+                float* dst = sc.p + (size_t)(ks * per + cbl) * R * 128 + lane * 4;
+#pragma unroll
+                for (int r = 0; r < R; ++r)
+                    *reinterpret_cast<float4*>(dst + r * 128) = make_float4(acc[r][0], acc[r][1], acc[r][2], acc[r][3]);
+            }
         }
+        if (ksplit == 1) continue;
         __syncthreads();
         const int ncol = (CB - cb0 < per ? CB - cb0 : per) * 128;
         for (int idx = threadIdx.x; idx < R * ncol; idx += blockDim.x) {
@@ -288,28 +310,34 @@ __device__ __forceinline__ void cta_linear_splitk4(const Seg& s0, const Seg& s1,
             if (c >= nout) continue;
             const int cbl2 = cl >> 7, ln = cl & 127;
             float v = 0.f;
-            for (int k2 = 0; k2 < ksplit; ++k2) v += scratch[((size_t)(k2 * per + cbl2) * R + r) * 128 + ln];
+            for (int k2 = 0; k2 < ksplit; ++k2) v += sc.p[((size_t)(k2 * per + cbl2) * R + r) * 128 + ln];
             epi(r, c, v);
         }
     }
 }
-// floats of scratch a wide CTA needs.  R <= 4: [warp][R][128] (cta_linear_splitk4); R = 8: one [R][32] block per
-// (K part, column block) slot, at most 2 x warps slots (cta_linear_splitk)
+// floats of scratch a wide CTA would like to have (the launch code gives it what is left of shared memory, at most this).
+// R <= 4 and 12..20: [warp][R][128] (cta_linear_splitk4); R = 8: one [R][32] block per (K part, column block) slot, at
+// most 2 x warps slots (cta_linear_splitk)
 __host__ __device__ inline int splitk_scratch_floats(int R) {
-    return R <= 4 ? (kWideThreads / 32) * R * 128 : 2 * (kWideThreads / 32) * R * 32;
+    return R == 8 ? 2 * (rollout_threads(R) / 32) * R * 32 : R <= 20 ? (rollout_threads(R) / 32) * R * 128 : 0;
 }
 
 template <int R, class Epi>
-__device__ __forceinline__ void cta_linear(const Seg& s0, const Seg& s1, int ldw, int nout, Epi epi, float* scratch = nullptr) {
-    if constexpr (R <= 8) {
-        if (scratch != nullptr && blockDim.x > kThreads) {
-            if constexpr (R <= 4) cta_linear_splitk4<R>(s0, s1, ldw, nout, epi, scratch);
-            else cta_linear_splitk<R>(s0, s1, ldw, nout, epi, scratch);
-            return;
+__device__ __forceinline__ void cta_linear(const Seg& s0, const Seg& s1, int ldw, int nout, Epi epi,
+                                           KScratch scratch = KScratch{nullptr, 0}) {
+    if constexpr (R <= 20) {
+        if (blockDim.x > kThreads) {  // wide CTA of a rollout kernel
+            if constexpr (R == 8) {
+                if (scratch.p != nullptr) { cta_linear_splitk<R>(s0, s1, ldw, nout, epi, scratch.p); return; }
+            } else {
+                cta_linear_splitk4<R>(s0, s1, ldw, nout, epi, scratch);
+                return;
+            }
         }
     }
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int c0 = warp * 32; c0 < nout; c0 += kWarps * 32) {
+    const int nwarps = blockDim.x >> 5;
+    for (int c0 = warp * 32; c0 < nout; c0 += nwarps * 32) {
         const int col = c0 + lane;  // < ldw always (ldw is nout rounded up to 32)
         float acc[R];
 #pragma unroll

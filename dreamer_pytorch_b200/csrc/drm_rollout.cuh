@@ -50,6 +50,7 @@ struct RollDev {
     const float* Wa_last;
     // io
     const float *start_stoch, *start_deter, *action_in, *embproj, *eps_prior, *eps_post, *noise_act;
+    const unsigned long long* nz;  // {seed, offset} of the in-kernel noise streams (drm_philox.cuh) for NULL eps / noise pointers
     float *prior_mean, *prior_std, *prior_stoch, *deter, *post_mean, *post_std, *post_stoch, *action_out;
     RollSave sv;
     // backward

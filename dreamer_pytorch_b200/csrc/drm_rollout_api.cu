@@ -15,7 +15,9 @@ static int validate(const drm_rollout* r) {
     DRM_REQUIRE(r->precision == DRM_FP32 || r->precision == DRM_BF16, DRM_E_SHAPE, "unknown precision");
     DRM_REQUIRE(w.W_in && w.b_in && w.W_ih && w.W_hh && w.b_ih && w.b_hh && w.W_p1 && w.b_p1 && w.W_p2 && w.b_p2,
                 DRM_E_ARG, "null transition weight");
-    DRM_REQUIRE(r->start_stoch && r->start_deter && r->eps_prior, DRM_E_ARG, "null input");
+    DRM_REQUIRE(r->start_stoch && r->start_deter, DRM_E_ARG, "null input");
+    // noise: a tensor, or -- fp32 kernels -- generated in the kernel from noise_pair (drm_philox.cuh)
+    DRM_REQUIRE(r->eps_prior || r->noise_pair, DRM_E_ARG, "eps_prior is NULL and there is no noise_pair to generate it from");
     DRM_REQUIRE(r->prior_mean && r->prior_std && r->prior_stoch && r->deter, DRM_E_ARG, "null output");
     if (r->mode == DRM_MODE_POLICY) {
         const drm_mlp& a = r->actor;
@@ -26,14 +28,14 @@ static int validate(const drm_rollout* r) {
         DRM_REQUIRE(r->act_dist >= 0 && r->act_dist <= 2, DRM_E_ARG, "bad action distribution");
         DRM_REQUIRE(a.out_dim == aout, DRM_E_SHAPE, "actor out_dim does not match the action distribution");
         for (int l = 0; l < a.n_linear; ++l) DRM_REQUIRE(a.W[l] && a.b[l], DRM_E_ARG, "null actor weight");
-        DRM_REQUIRE(r->noise_act && r->action_out, DRM_E_ARG, "null policy io");
+        DRM_REQUIRE((r->noise_act || r->noise_pair) && r->action_out, DRM_E_ARG, "null policy io");
     } else {
         DRM_REQUIRE(r->action_in, DRM_E_ARG, "null action_in");
     }
     if (r->mode == DRM_MODE_REPRESENTATION) {
         DRM_REQUIRE(w.E >= 4 && w.E % 4 == 0, DRM_E_SHAPE, "obs embed size must be a multiple of 4");
         DRM_REQUIRE(w.W_q1 && w.b_q1 && w.W_q2 && w.b_q2, DRM_E_ARG, "null posterior weight");
-        DRM_REQUIRE(r->obs_embed && r->eps_post && r->post_mean && r->post_std && r->post_stoch, DRM_E_ARG,
+        DRM_REQUIRE(r->obs_embed && (r->eps_post || r->noise_pair) && r->post_mean && r->post_std && r->post_stoch, DRM_E_ARG,
                     "null representation io");
     }
     return DRM_OK;
@@ -160,7 +162,7 @@ static void fill_io(const drm_rollout* r, RollDev& p) {
     for (int l = 0; l < DRM_MAX_LINEAR; ++l) p.ba[l] = (r->mode == DRM_MODE_POLICY && l < r->actor.n_linear) ? r->actor.b[l] : nullptr;
     p.Wa_last = r->mode == DRM_MODE_POLICY ? r->actor.W[r->actor.n_linear - 1] : nullptr;
     p.start_stoch = r->start_stoch; p.start_deter = r->start_deter; p.action_in = r->action_in;
-    p.eps_prior = r->eps_prior; p.eps_post = r->eps_post; p.noise_act = r->noise_act;
+    p.eps_prior = r->eps_prior; p.eps_post = r->eps_post; p.noise_act = r->noise_act; p.nz = r->noise_pair;
     p.prior_mean = r->prior_mean; p.prior_std = r->prior_std; p.prior_stoch = r->prior_stoch; p.deter = r->deter;
     p.post_mean = r->post_mean; p.post_std = r->post_std; p.post_stoch = r->post_stoch; p.action_out = r->action_out;
 }
@@ -217,7 +219,11 @@ int drm_rollout_fwd(const drm_rollout* r, void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     int rc = validate(r); if (rc) return rc;
     rc = check_device(); if (rc) return rc;
-    if (use_tc(r)) return tc::rollout_tc_fwd(r, stream);
+    if (use_tc(r)) {
+        DRM_REQUIRE(r->eps_prior && r->noise_act, DRM_E_ARG,
+                    "the bf16 tensor-core rollout takes materialised noise tensors (drm_noise_fill)");
+        return tc::rollout_tc_fwd(r, stream);
+    }
     RollDev p{}; dims(r, p);
     DRM_REQUIRE(r->workspace && r->workspace_bytes >= fwd_ws_floats(r, p) * sizeof(float), DRM_E_WORKSPACE,
                 "workspace too small");
@@ -251,7 +257,11 @@ int drm_rollout_bwd(const drm_rollout* r, const drm_rollout_grad* g, void* strea
     DRM_REQUIRE(g != nullptr, DRM_E_ARG, "null grad block");
     rc = check_device(); if (rc) return rc;
     DRM_REQUIRE(g->phase >= DRM_PHASE_ALL && g->phase <= DRM_PHASE_RUN, DRM_E_ARG, "bad phase");
-    if (use_tc(r)) return tc::rollout_tc_bwd(r, g, stream);
+    if (use_tc(r)) {
+        DRM_REQUIRE(r->eps_prior && r->noise_act, DRM_E_ARG,
+                    "the bf16 tensor-core rollout takes materialised noise tensors (drm_noise_fill)");
+        return tc::rollout_tc_bwd(r, g, stream);
+    }
     if (g->phase == DRM_PHASE_PREPARE) return DRM_OK;  // fp32: everything happens in RUN
     DRM_REQUIRE(!g->g_wait_flags, DRM_E_ARG, "g_wait_flags is honoured by the bf16 policy rollout only");
     RollDev p{}; dims(r, p);

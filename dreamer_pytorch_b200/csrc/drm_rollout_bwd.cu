@@ -4,11 +4,12 @@
 // weight-gradient GEMMs (drm_mlp.cu: wgrad_kernel) consume afterwards.
 // Mirrors autograd through rnns.py:98-107,149-159,224-244, action.py:51-66, agent.py:101-117.
 #include "drm_rollout.cuh"
+#include "drm_philox.cuh"
 
 namespace drm {
 
 template <int R>
-__global__ void __launch_bounds__(R <= 8 ? kWideThreads : kThreads) rollout_bwd_kernel(const RollDev p) {
+__global__ void __launch_bounds__(rollout_threads(R)) rollout_bwd_kernel(const RollDev p) {
     extern __shared__ __align__(16) float smem[];
     const int S = p.S, D = p.D, Hd = p.Hd, A = p.A, U = p.U;
     float* cS = smem;                 // [R][S4]   carried d stoch
@@ -23,9 +24,15 @@ __global__ void __launch_bounds__(R <= 8 ? kWideThreads : kThreads) rollout_bwd_
     const bool policy = p.mode == DRM_MODE_POLICY;
     const bool repr = p.mode == DRM_MODE_REPRESENTATION;
     const Seg none{nullptr, nullptr, 0, 0};
+    const NoiseKey nk = p.nz ? load_noise_key(p.nz) : NoiseKey{0u, 0u, 0u, 0u};
 
     // wide CTAs (few rows): split-K scratch behind the row buffers, see cta_linear_splitk
-    float* ksc = (R <= 8 && blockDim.x > kThreads) ? smem + R * bwd_smem_floats_per_row(p) : nullptr;
+    // wide CTAs: whatever the launch left of shared memory behind the row buffers is split-K scratch (cta_linear)
+    unsigned dyn_bytes;
+    asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dyn_bytes));
+    const int row_floats = R * bwd_smem_floats_per_row(p);
+    const KScratch ksc = (R <= 20 && blockDim.x > kThreads && (int)(dyn_bytes / 4) > row_floats)
+                             ? KScratch{smem + row_floats, (int)(dyn_bytes / 4) - row_floats} : KScratch{nullptr, 0};
     for (int tile = blockIdx.x; tile * R < p.n; tile += gridDim.x) {
         const int row0 = tile * R;
         const int total = R * bwd_smem_floats_per_row(p);
@@ -43,7 +50,7 @@ __global__ void __launch_bounds__(R <= 8 ? kWideThreads : kThreads) rollout_bwd_
                         const size_t o = (trow0 + r) * S + c;
                         const float dst = (p.g_post_stoch ? p.g_post_stoch[o] : 0.f) + cS[r * p.S4 + c];
                         dm = (p.g_post_mean ? p.g_post_mean[o] : 0.f) + dst;
-                        const float dsd = (p.g_post_std ? p.g_post_std[o] : 0.f) + dst * p.eps_post[o];
+                        const float dsd = (p.g_post_std ? p.g_post_std[o] : 0.f) + dst * noise_at(p.eps_post, nk, NZ_EPS_POST, NZ_NORMAL, o);
                         ds = dsd * (1.f - expf(-(p.post_std[o] - p.min_std)));  // sigmoid(raw) from softplus(raw)
                         if (p.want_rssm_dy) {
                             p.dy.q2[(trow0 + r) * 2 * S + c] = dm;
@@ -82,7 +89,7 @@ __global__ void __launch_bounds__(R <= 8 ? kWideThreads : kThreads) rollout_bwd_
                     const size_t o = (trow0 + r) * S + c;
                     const float dst = (p.g_prior_stoch ? p.g_prior_stoch[o] : 0.f) + (repr ? 0.f : cS[r * p.S4 + c]);
                     dm = (p.g_prior_mean ? p.g_prior_mean[o] : 0.f) + dst;
-                    const float dsd = (p.g_prior_std ? p.g_prior_std[o] : 0.f) + dst * p.eps_prior[o];
+                    const float dsd = (p.g_prior_std ? p.g_prior_std[o] : 0.f) + dst * noise_at(p.eps_prior, nk, NZ_EPS_PRIOR, NZ_NORMAL, o);
                     ds = dsd * (1.f - expf(-(p.prior_std[o] - p.min_std)));
                     if (p.want_rssm_dy) {
                         p.dy.p2[(trow0 + r) * 2 * S + c] = dm;
@@ -192,7 +199,7 @@ __global__ void __launch_bounds__(R <= 8 ? kWideThreads : kThreads) rollout_bwd_
                             const float rs = p.sv.raw[(trow0 + r) * p.Aout + A + j];
                             const float th = tanhf(rm / p.mean_scale);
                             dm = dpre * (1.f - th * th);
-                            ds = dpre * p.noise_act[o] * sigmoidf_(rs + p.raw_init_std);
+                            ds = dpre * noise_at(p.noise_act, nk, NZ_NOISE_ACT, NZ_NORMAL, o) * sigmoidf_(rs + p.raw_init_std);
                             p.dy.a[last][(trow0 + r) * p.Aout + j] = dm;
                             p.dy.a[last][(trow0 + r) * p.Aout + A + j] = ds;
                         }
@@ -277,9 +284,13 @@ int launch_rollout_bwd(const RollDev& p, cudaStream_t stream) {
     const size_t per_row = (size_t)bwd_smem_floats_per_row(p) * sizeof(float);
     const int Rv = pick_rows(p.n, per_row, 0);
     DRM_REQUIRE(Rv > 0, DRM_E_SHAPE, "model too wide for shared memory");
-    const bool wide = Rv <= 8 && per_row * Rv + (size_t)splitk_scratch_floats(Rv) * sizeof(float) <= (size_t)kMaxSmem;
-    const size_t smem = per_row * Rv + (wide ? (size_t)splitk_scratch_floats(Rv) * sizeof(float) : 0);
-    const int nthreads = wide ? kWideThreads : kThreads;
+    // wide CTAs (<= 20 rows) take split-K scratch behind the row buffers: as much as they can use, or what is left
+    size_t scratch = (size_t)splitk_scratch_floats(Rv) * sizeof(float);
+    if (per_row * Rv + scratch > (size_t)kMaxSmem) scratch = ((size_t)kMaxSmem - per_row * Rv) & ~(size_t)15;
+    if (Rv == 8 && scratch < (size_t)splitk_scratch_floats(Rv) * sizeof(float)) scratch = 0;  // the 32-column form wants all of it
+    const bool wide = Rv <= 20 && (Rv != 8 || scratch > 0);
+    const size_t smem = per_row * Rv + (wide ? scratch : 0);
+    const int nthreads = wide ? rollout_threads(Rv) : kThreads;
     const int tiles = (p.n + Rv - 1) / Rv;
     const int grid = tiles < num_sms() ? tiles : num_sms();
     ProfScope prof(PROF_ROLLOUT_BWD, stream);

@@ -5,11 +5,12 @@
 // for a tile of R rows per CTA.  The recurrent state (stoch, deter) never leaves shared memory
 // between steps; weights stream from L2 (packed, coalesced).  fp32 FFMA path.
 #include "drm_rollout.cuh"
+#include "drm_philox.cuh"
 
 namespace drm {
 
 template <int R>
-__global__ void __launch_bounds__(R <= 8 ? kWideThreads : kThreads) rollout_fwd_kernel(const RollDev p) {
+__global__ void __launch_bounds__(rollout_threads(R)) rollout_fwd_kernel(const RollDev p) {
     extern __shared__ __align__(16) float smem[];
     const int S = p.S, D = p.D, Hd = p.Hd, A = p.A;
     const int ldXH = Hd + D;
@@ -25,9 +26,15 @@ __global__ void __launch_bounds__(R <= 8 ? kWideThreads : kThreads) rollout_fwd_
     const bool repr = p.mode == DRM_MODE_REPRESENTATION;
     const bool save = p.training != 0;
     const Seg none{nullptr, nullptr, 0, 0};
+    const NoiseKey nk = p.nz ? load_noise_key(p.nz) : NoiseKey{0u, 0u, 0u, 0u};
 
     // wide CTAs (few rows): split-K scratch behind the row buffers, see cta_linear_splitk
-    float* ksc = (R <= 8 && blockDim.x > kThreads) ? smem + R * fwd_smem_floats_per_row(p) : nullptr;
+    // wide CTAs: whatever the launch left of shared memory behind the row buffers is split-K scratch (cta_linear)
+    unsigned dyn_bytes;
+    asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dyn_bytes));
+    const int row_floats = R * fwd_smem_floats_per_row(p);
+    const KScratch ksc = (R <= 20 && blockDim.x > kThreads && (int)(dyn_bytes / 4) > row_floats)
+                             ? KScratch{smem + row_floats, (int)(dyn_bytes / 4) - row_floats} : KScratch{nullptr, 0};
     for (int tile = blockIdx.x; tile * R < p.n; tile += gridDim.x) {
         const int row0 = tile * R;
         const int total = R * fwd_smem_floats_per_row(p);
@@ -97,7 +104,7 @@ __global__ void __launch_bounds__(R <= 8 ? kWideThreads : kThreads) rollout_fwd_
                         const float rm = sRaw[r * p.Aout4 + j], rs = sRaw[r * p.Aout4 + A + j];
                         const float mean = p.mean_scale * tanhf(rm / p.mean_scale);
                         const float std = softplusf_(rs + p.raw_init_std) + p.act_min_std;
-                        const float e = ok ? p.noise_act[(trow0 + r) * A + j] : 0.f;
+                        const float e = ok ? noise_at(p.noise_act, nk, NZ_NOISE_ACT, NZ_NORMAL, (trow0 + r) * A + j) : 0.f;
                         const float a = tanhf(mean + std * e);
                         sAct[r * p.A4 + j] = a;
                         if (ok) {
@@ -113,7 +120,7 @@ __global__ void __launch_bounds__(R <= 8 ? kWideThreads : kThreads) rollout_fwd_
                     for (int r = threadIdx.x; r < R; r += blockDim.x) {
                         const bool ok = row0 + r < p.n;
                         const float* lg = sRaw + r * p.Aout4;
-                        const float* gz = p.noise_act + (trow0 + r) * A;
+                        auto gz = [&](int j) { return noise_at(p.noise_act, nk, NZ_NOISE_ACT, NZ_GUMBEL, (trow0 + r) * A + j); };
                         float mx = -INFINITY;
                         for (int j = 0; j < A; ++j) mx = fmaxf(mx, lg[j]);
                         if (p.act_dist == DRM_DIST_ONE_HOT) {
@@ -121,7 +128,7 @@ __global__ void __launch_bounds__(R <= 8 ? kWideThreads : kThreads) rollout_fwd_
                             for (int j = 0; j < A; ++j) den += expf(lg[j] - mx);
                             int best = 0; float bv = -INFINITY;
                             for (int j = 0; j < A; ++j) {
-                                const float s = lg[j] + (ok ? gz[j] : 0.f);
+                                const float s = lg[j] + (ok ? gz(j) : 0.f);
                                 if (s > bv) { bv = s; best = j; }
                             }
                             for (int j = 0; j < A; ++j) {
@@ -136,11 +143,11 @@ __global__ void __launch_bounds__(R <= 8 ? kWideThreads : kThreads) rollout_fwd_
                             }
                         } else {  // relaxed one-hot: softmax((logits + g) / temperature)
                             float smx = -INFINITY;
-                            for (int j = 0; j < A; ++j) smx = fmaxf(smx, (lg[j] + (ok ? gz[j] : 0.f)) / p.temperature);
+                            for (int j = 0; j < A; ++j) smx = fmaxf(smx, (lg[j] + (ok ? gz(j) : 0.f)) / p.temperature);
                             float den = 0.f;
-                            for (int j = 0; j < A; ++j) den += expf((lg[j] + (ok ? gz[j] : 0.f)) / p.temperature - smx);
+                            for (int j = 0; j < A; ++j) den += expf((lg[j] + (ok ? gz(j) : 0.f)) / p.temperature - smx);
                             for (int j = 0; j < A; ++j) {
-                                const float a = expf((lg[j] + (ok ? gz[j] : 0.f)) / p.temperature - smx) / den;
+                                const float a = expf((lg[j] + (ok ? gz(j) : 0.f)) / p.temperature - smx) / den;
                                 sAct[r * p.A4 + j] = a;
                                 if (ok) {
                                     p.action_out[(trow0 + r) * A + j] = a;
@@ -223,7 +230,7 @@ __global__ void __launch_bounds__(R <= 8 ? kWideThreads : kThreads) rollout_fwd_
                 const float mean = sMS[r * p.MS4 + c];
                 const float std = softplusf_(sMS[r * p.MS4 + S + c]) + p.min_std;
                 const size_t o = (trow0 + r) * S + c;
-                const float e = ok ? p.eps_prior[o] : 0.f;
+                const float e = ok ? noise_at(p.eps_prior, nk, NZ_EPS_PRIOR, NZ_NORMAL, o) : 0.f;
                 const float st = mean + std * e;
                 if (!repr) sS[r * p.S4 + c] = st;
                 if (ok) { p.prior_mean[o] = mean; p.prior_std[o] = std; p.prior_stoch[o] = st; }
@@ -256,7 +263,7 @@ __global__ void __launch_bounds__(R <= 8 ? kWideThreads : kThreads) rollout_fwd_
                     const float mean = sMS[r * p.MS4 + c];
                     const float std = softplusf_(sMS[r * p.MS4 + S + c]) + p.min_std;
                     const size_t o = (trow0 + r) * S + c;
-                    const float e = ok ? p.eps_post[o] : 0.f;
+                    const float e = ok ? noise_at(p.eps_post, nk, NZ_EPS_POST, NZ_NORMAL, o) : 0.f;
                     const float st = mean + std * e;
                     sS[r * p.S4 + c] = st;
                     if (ok) { p.post_mean[o] = mean; p.post_std[o] = std; p.post_stoch[o] = st; }
@@ -272,9 +279,13 @@ int launch_rollout_fwd(const RollDev& p, cudaStream_t stream) {
     const size_t per_row = (size_t)fwd_smem_floats_per_row(p) * sizeof(float);
     const int Rv = pick_rows(p.n, per_row, 0);
     DRM_REQUIRE(Rv > 0, DRM_E_SHAPE, "model too wide for shared memory");
-    const bool wide = Rv <= 8 && per_row * Rv + (size_t)splitk_scratch_floats(Rv) * sizeof(float) <= (size_t)kMaxSmem;
-    const size_t smem = per_row * Rv + (wide ? (size_t)splitk_scratch_floats(Rv) * sizeof(float) : 0);
-    const int nthreads = wide ? kWideThreads : kThreads;
+    // wide CTAs (<= 20 rows) take split-K scratch behind the row buffers: as much as they can use, or what is left
+    size_t scratch = (size_t)splitk_scratch_floats(Rv) * sizeof(float);
+    if (per_row * Rv + scratch > (size_t)kMaxSmem) scratch = ((size_t)kMaxSmem - per_row * Rv) & ~(size_t)15;
+    if (Rv == 8 && scratch < (size_t)splitk_scratch_floats(Rv) * sizeof(float)) scratch = 0;  // the 32-column form wants all of it
+    const bool wide = Rv <= 20 && (Rv != 8 || scratch > 0);
+    const size_t smem = per_row * Rv + (wide ? scratch : 0);
+    const int nthreads = wide ? rollout_threads(Rv) : kThreads;
     const int tiles = (p.n + Rv - 1) / Rv;
     const int grid = tiles < num_sms() ? tiles : num_sms();
     ProfScope prof(PROF_ROLLOUT_FWD, stream);

@@ -73,11 +73,10 @@ class AgentModel(nn.Module):
         cfg = RolloutCfg(_lib.MODE_POLICY, steps, n, self.transition.dims(), act_dist=self.action_dist,
                          mean_scale=float(dec.mean_scale), raw_init_std=float(dec.raw_init_std),
                          act_min_std=float(dec.min_std))
-        if self.action_dist == "tanh_normal":
-            noise_act = noise.normal("noise_act", (steps, n, A), dev)
-        else:
-            noise_act = noise.gumbel("noise_act", (steps, n, A), dev)
-        eps = noise.normal("eps_prior", (steps, n, self.stochastic_size), dev)
+        draw = noise.normal if self.action_dist == "tanh_normal" else noise.gumbel
+        noise_act = draw("noise_act", (steps, n, A), dev, lazy=True)
+        eps = noise.normal("eps_prior", (steps, n, self.stochastic_size), dev, lazy=True,
+                           pair=noise_act if noise.is_pair(noise_act) else None)
         mean, std, stoch, deter, action = RolloutFn.apply(
             cfg, state.stoch, state.deter, None, None, eps, None, noise_act,
             *self.transition.weights(), None, None, None, None, *dec.weights())

@@ -93,7 +93,7 @@ class RSSMTransition(TransitionBase):
         """[steps,n,A] actions -> stacked prior states; one launch (rollout_transition, rnns.py:207-222)."""
         n = prev_state.stoch.shape[0]
         cfg = RolloutCfg(_lib.MODE_TRANSITION, steps, n, self.dims())
-        eps = noise.normal("eps_prior", (steps, n, self._stoch_size), prev_state.stoch.device)
+        eps = noise.normal("eps_prior", (steps, n, self._stoch_size), prev_state.stoch.device, lazy=True)
         mean, std, stoch, deter = RolloutFn.apply(cfg, prev_state.stoch, prev_state.deter, action, None, eps, None,
                                                   None, *self.weights(), None, None, None, None)
         return RSSMState(mean, std, stoch, deter)
@@ -139,8 +139,10 @@ class RSSMRepresentation(RepresentationBase):
         cfg = RolloutCfg(_lib.MODE_REPRESENTATION, steps, n, self._transition_model.dims(self._obs_embed_size))
         S = self._stoch_size
         # the reference draws prior eps then posterior eps at every step
-        eps_prior = noise.normal("eps_prior", (steps, n, S), dev)
-        eps_post = noise.normal("eps_post", (steps, n, S), dev)
+        # (production: one {seed, offset} pair, the kernel generates both streams itself, noise.py)
+        eps_prior = noise.normal("eps_prior", (steps, n, S), dev, lazy=True)
+        eps_post = noise.normal("eps_post", (steps, n, S), dev, lazy=True,
+                                pair=eps_prior if noise.is_pair(eps_prior) else None)
         pm, ps, pst, deter, qm, qs, qst = RolloutFn.apply(cfg, prev_state.stoch, prev_state.deter, action, obs_embed,
                                                           eps_prior, eps_post, None, *self.weights())
         return RSSMState(pm, ps, pst, deter), RSSMState(qm, qs, qst, deter)

@@ -15,7 +15,7 @@ from typing import List, Optional, Sequence
 import torch
 from torch.autograd.function import once_differentiable
 
-from . import _lib
+from . import _lib, noise
 from .precision import get_precision
 from ._lib import MAXL
 
@@ -114,8 +114,38 @@ def _build_rollout(cfg: RolloutCfg, t: dict, rssm, actor, training: bool) -> _li
         _fill_mlp(r.actor, actor, cfg.dims[1] + cfg.dims[2])
     for k in ("start_stoch", "start_deter", "action_in", "obs_embed", "eps_prior", "eps_post", "noise_act",
               "prior_mean", "prior_std", "prior_stoch", "deter", "post_mean", "post_std", "post_stoch", "action_out"):
-        setattr(r, k, _lib.ptr(t.get(k)))
+        x = t.get(k)
+        if noise.is_pair(x):
+            # {seed, offset} instead of a tensor: the fp32 kernels generate this stream themselves (drm_rollout.noise_pair)
+            if r.noise_pair not in (None, 0) and r.noise_pair != x.data_ptr():
+                raise RuntimeError("one rollout takes one noise pair: pass the same pair for every generated stream")
+            r.noise_pair = x.data_ptr()
+            continue
+        setattr(r, k, _lib.ptr(x))
     return r
+
+
+def _noise_arg(x):
+    return x if noise.is_pair(x) else _f32c(x)
+
+
+def _resolve_noise(cfg: RolloutCfg, t: dict):
+    """Pair tensors stay pairs where the fp32 kernels will run; the bf16 tensor-core rollout (tanh-normal policy rollouts
+    under precision("bf16")) takes tensors, so its pairs are materialised here -- with the values the kernels would have
+    generated -- in one launch.  The dict keeps the tensors: the backward pass sees the same ones."""
+    names = [k for k in ("eps_prior", "eps_post", "noise_act") if noise.is_pair(t.get(k))]
+    if not names:
+        return
+    pairs = {t[k].data_ptr() for k in names}
+    if len(pairs) > 1:
+        raise RuntimeError("one rollout takes one noise pair: pass the same pair for every generated stream")
+    if not (cfg.precision == "bf16" and cfg.mode == _lib.MODE_POLICY and cfg.act_dist == "tanh_normal"):
+        return
+    A, S = cfg.dims[0], cfg.dims[1]
+    width = dict(eps_prior=S, eps_post=S, noise_act=A)
+    outs = noise.fill(t[names[0]].device, [(k, (cfg.steps, cfg.n, width[k]), "normal") for k in names], pair=t[names[0]])
+    for k, x in zip(names, outs):
+        t[k] = x
 
 
 def _check_shape(name, t, shape):
@@ -144,14 +174,18 @@ def rollout_forward_raw(cfg: RolloutCfg, t: dict, rssm, actor, training: bool, s
     dev = t["start_stoch"].device
     _check_shape("start_stoch", t["start_stoch"], (n, S))
     _check_shape("start_deter", t["start_deter"], (n, D))
-    _check_shape("eps_prior", t["eps_prior"], (T, n, S))
+    _resolve_noise(cfg, t)
+    if not noise.is_pair(t["eps_prior"]):
+        _check_shape("eps_prior", t["eps_prior"], (T, n, S))
     if cfg.mode == _lib.MODE_POLICY:
-        _check_shape("noise_act", t["noise_act"], (T, n, A))
+        if not noise.is_pair(t["noise_act"]):
+            _check_shape("noise_act", t["noise_act"], (T, n, A))
     else:
         _check_shape("action", t["action_in"], (T, n, A))
     if cfg.mode == _lib.MODE_REPRESENTATION:
         _check_shape("obs_embed", t["obs_embed"], (T, n, E))
-        _check_shape("eps_post", t["eps_post"], (T, n, S))
+        if not noise.is_pair(t["eps_post"]):
+            _check_shape("eps_post", t["eps_post"], (T, n, S))
     new = lambda w: torch.empty(T, n, w, dtype=torch.float32, device=dev)
     t.update(prior_mean=new(S), prior_std=new(S), prior_stoch=new(S), deter=new(D))
     if cfg.mode == _lib.MODE_REPRESENTATION:
@@ -254,8 +288,8 @@ class RolloutFn(torch.autograd.Function):
         rssm = [_f32c(w) for w in weights[:14]]
         actor = [_f32c(w) for w in weights[14:]]
         t = dict(start_stoch=_f32c(start_stoch), start_deter=_f32c(start_deter), action_in=_f32c(action_in),
-                 obs_embed=_f32c(obs_embed), eps_prior=_f32c(eps_prior), eps_post=_f32c(eps_post),
-                 noise_act=_f32c(noise_act))
+                 obs_embed=_f32c(obs_embed), eps_prior=_noise_arg(eps_prior), eps_post=_noise_arg(eps_post),
+                 noise_act=_noise_arg(noise_act))
         training = any(ctx.needs_input_grad)
         n_rssm = 14 if cfg.mode == _lib.MODE_REPRESENTATION else 10
         if get_precision() == "bf16" and any(ctx.needs_input_grad[8 + i] for i in range(n_rssm)):

@@ -136,6 +136,14 @@ typedef struct drm_rollout {
        running BESIDE the rollout (drm_mlp_call.wait_flags) can start on step t while step t+1 is computed.
        drm_rollout_tiles() is the count each flag reaches. */
     int32_t* step_flags;
+    /* Production noise (last sentence; the reference draws torch.randn per step, rnns.py:104,155 /
+       action.py:58-65).  Device pointer to uint64 {seed, offset} (drm_noise_next), or NULL.  When it is set, any of
+       eps_prior / eps_post / noise_act may be NULL: the fp32 kernels then GENERATE that value in the kernel -- Philox4x32-10
+       keyed on (seed, offset, stream, element index), forward and again backward, nothing goes through HBM.  The value of
+       element e is exactly what drm_noise_fill writes at index e for the same pair and stream (0 eps_prior, 1 eps_post,
+       2 noise_act; noise_act is Gumbel(0,1) for the categorical policies, N(0,1) otherwise).  The bf16 tensor-core
+       kernels take materialised tensors only (DRM_E_ARG otherwise): fill them with drm_noise_fill. */
+    const unsigned long long* noise_pair;
 } drm_rollout;
 
 /* Backward calls in two halves.  A backward pass first re-packs the (unchanged) weights for the transposed products and
@@ -288,6 +296,35 @@ typedef struct drm_replay_gather_call {
     const int64_t* b;    /* [batch] environment indices (device) */
 } drm_replay_gather_call;
 int drm_replay_gather(const drm_replay_gather_call* c, void* stream);
+
+/* Production noise: counter-based N(0,1) / Gumbel(0,1) streams (Philox4x32-10) keyed on (seed, offset, stream, element).
+ * Replaces the reference's per-step torch.randn / OneHotCategorical.sample draws (rnns.py:104,155, action.py:58-65,
+ * distribution.py:27) with one launch per rollout -- or none, see drm_rollout.noise_pair.
+ *   state: device uint64[4] {seed, offset, ticket (0), unused}, one per device, owned by the caller.
+ *   drm_noise_next   pair_out = {seed, offset}; offset += 1.  One tiny launch, recordable into a CUDA graph (every replay
+ *                    then draws fresh noise without the host).
+ *   drm_noise_fill   writes up to 4 blocks (e.g. noise_act and eps_prior of one imagination pass) in ONE launch, keyed
+ *                    either on a frozen `pair` or on `state` -- then the offset is bumped by the last CTA to finish and
+ *                    the {seed, offset} used is stored to pair_out (may be NULL). */
+#define DRM_MAX_NOISE_BLOCKS 4
+#define DRM_NOISE_NORMAL 0
+#define DRM_NOISE_GUMBEL 1
+typedef struct drm_noise_fill_call {
+    unsigned long long* state;        /* exactly one of state / pair */
+    const unsigned long long* pair;
+    unsigned long long* pair_out;     /* with `state`: receives the pair used, or NULL */
+    int32_t n_blocks;
+    int32_t pad_;
+    float* out[DRM_MAX_NOISE_BLOCKS];
+    int64_t numel[DRM_MAX_NOISE_BLOCKS];
+    int32_t stream_id[DRM_MAX_NOISE_BLOCKS]; /* 0 eps_prior, 1 eps_post, 2 noise_act, 3 SampleDist.mode draws, .. 255 */
+    int32_t kind[DRM_MAX_NOISE_BLOCKS];      /* DRM_NOISE_* */
+} drm_noise_fill_call;
+int drm_noise_next(unsigned long long* state, unsigned long long* pair_out, void* stream);
+int drm_noise_fill(const drm_noise_fill_call* c, void* stream);
+/* Diagnostics / known-answer tests: the raw Philox words of groups [group0, group0 + n_groups) of a stream -> out[4 n]. */
+int drm_noise_words(const unsigned long long* pair, int stream_id, unsigned long long group0, int n_groups,
+                    unsigned int* out, void* stream);
 
 int drm_version(void);
 /* Once per device, before the first compute call (the ctypes binding does it at load time): checks the architecture and

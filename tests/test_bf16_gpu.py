@@ -244,3 +244,62 @@ def test_full_size_loss_section_bf16(cuda):
     print(f"[margin] full-size bf16 loss section: worst {worst} {errs[worst]:.2e}")
     assert not bad, bad
     assert len(errs) > 30
+
+
+def test_config4_65536_start_states_equal_their_shards(cuda):
+    """BASELINE.json configs[3] at full size (65 536 start states x H = 15, bf16) through size-independent properties,
+    because no oracle finishes that size in seconds: rows are independent, so (a) the rollout of all rows, restricted to
+    a shard, is the rollout of that shard (bit for bit when both use the same tile height; the multi-GPU split relies on
+    it), and (b) the two losses and every actor / value gradient of the whole batch are the mean over equal shards."""
+    from dreamer_pytorch_b200 import noise
+    from dreamer_pytorch_b200.algo import imagination_losses
+    from dreamer_pytorch_b200.dropin.agent import AtariDreamerModel
+    from dreamer_pytorch_b200.dropin.rnns import RSSMState
+    from dreamer_pytorch_b200.precision import precision
+
+    torch.manual_seed(0)
+    N, H, A, K = 65536, 15, 6, 4
+    model = AtariDreamerModel(action_shape=(A,), action_dist="tanh_normal").to(cuda).train()
+    g = torch.Generator(device=cuda).manual_seed(9)
+    stoch = torch.randn(N, 30, generator=g, device=cuda)
+    deter = torch.tanh(torch.randn(N, 200, generator=g, device=cuda))
+    na = torch.randn(H, N, A, generator=g, device=cuda)
+    ep = torch.randn(H, N, 30, generator=g, device=cuda)
+    actor_p, value_p = list(model.action_decoder.parameters()), list(model.value_model.parameters())
+
+    def err(x, ref):  # normwise, on the device (the tensors are up to 200 M elements)
+        return float((x.double() - ref.double()).abs().max() / ref.double().abs().max())
+
+    def run(lo, hi):
+        st = RSSMState(stoch[lo:hi], stoch[lo:hi], stoch[lo:hi], deter[lo:hi])
+        with noise.injected(noise_act=[na[:, lo:hi].contiguous()], eps_prior=[ep[:, lo:hi].contiguous()]):
+            al, vl, info = imagination_losses(model, st, H)
+        grads = torch.autograd.grad(al, actor_p) + torch.autograd.grad(vl, value_p)
+        return al.detach(), vl.detach(), info, [x.clone() for x in grads]
+
+    with precision("bf16"):
+        al, vl, info, grads = run(0, N)
+        assert torch.isfinite(info.imag.deter).all() and (info.actions.abs() <= 1).all()
+        full = (info.imag.stoch.clone(), info.imag.deter.clone(), info.actions.clone(), info.value.clone())
+        del info
+        sh = N // K  # 16 384 rows: 128-row tiles as well? no -- 64-row tiles (tile_rows_for); values then agree to rounding
+        acc_al, acc_vl, acc_g = 0.0, 0.0, [torch.zeros_like(x) for x in grads]
+        for k in range(K):
+            lo, hi = k * sh, (k + 1) * sh
+            a, v, inf, gs = run(lo, hi)
+            acc_al, acc_vl = acc_al + a / K, acc_vl + v / K
+            for t, x in zip(acc_g, gs):
+                t += x / K
+            for whole, part in zip(full, (inf.imag.stoch, inf.imag.deter, inf.actions, inf.value)):
+                assert err(part, whole[:, lo:hi]) < BF16_TOL  # other tile height: same math, other rounding order
+        # (a) bit for bit with the same tile height: a shard of >= 148 x 128 rows also runs 128-row tiles
+        lo, hi = 128 * 100, 128 * 100 + 148 * 128
+        _, _, inf, _ = run(lo, hi)
+        for whole, part in zip(full, (inf.imag.stoch, inf.imag.deter, inf.actions, inf.value)):
+            assert torch.equal(part, whole[:, lo:hi])
+    # (b) linearity over equal shards (the shards ran on the other tile height: bf16 rounding differs row by row, the
+    # means over 245 760 states agree far inside the bf16 budget)
+    assert err(acc_al, al) < 1e-3 and err(acc_vl, vl) < 1e-3
+    worst = max(err(t, x) for t, x in zip(acc_g, grads))
+    print(f"[margin] 65 536 start states: gradients vs mean of {K} shards {worst:.2e}")
+    assert worst < BF16_TOL

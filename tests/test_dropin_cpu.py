@@ -87,7 +87,8 @@ def test_noise_injection_order_and_leftovers():
     with noise.injected(eps_prior=[a, b]):
         assert torch.equal(noise.normal("eps_prior", (2, 3), "cpu"), a)
         assert torch.equal(noise.normal("eps_prior", (2, 3), "cpu"), b)
-        assert noise.normal("eps_post", (4,), "cpu").shape == (4,)  # not injected: fresh draw
+        with pytest.raises(RuntimeError, match="no CPU fallback"):  # not injected: a fresh draw is a CUDA kernel
+            noise.normal("eps_post", (4,), "cpu")
     with pytest.raises(AssertionError):
         with noise.injected(eps_prior=[a]):
             pass

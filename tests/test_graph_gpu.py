@@ -236,11 +236,12 @@ def test_whole_update_graph_matches_eager_update(use_pcont):
     for (k, pg), (_, pe) in zip(m_graph.named_parameters(), m_eager.named_parameters()):
         # the first Adam steps move every weight by ~lr * sign(g): fp32-atomic reordering of a near-zero gradient shows up
         # as a few 1e-5 of the largest weight
-        if not k.startswith("observation_"):
+        if k.startswith(("action_decoder", "value_model")):
             assert rel_err(pg, pe) < 1e-4, k
             continue
-        # conv stack (cuDNN, outside the hot path): its weight-gradient kernels reduce with atomics and may pick another
-        # algorithm under capture, so gradients carry ~1e-3 relative noise.  Comparing PARAMETERS after Adam is then
+        # World-model group: every gradient in it flows through the conv decoder / encoder (cuDNN, outside the hot path),
+        # whose kernels reduce with atomics and may pick another algorithm under capture, so those gradients carry ~1e-3
+        # relative noise (5.9e-4 normwise was seen on transition._cell.weight_ih).  Comparing PARAMETERS after Adam is then
         # ill-conditioned exactly where |g| is at that noise level: Adam's first updates are lr * sign(g), a flipped sign
         # moves the weight by 2 lr per update (a normwise 1.2e-3 was observed on the decoder's Linear with ~0.1 % of its
         # elements flipped).  What must hold: no element further apart than two Adam trajectories can get in two updates
