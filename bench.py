@@ -526,7 +526,10 @@ def run_b200(args):
         "scaling": w["scaling"], "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
         "config": {"workload": workload_string(w),
                    "states_per_gpu_per_step": N * H, "global_states_per_step": N * H * world,
-                   "parallelism": f"dp{world} over start states ({N} per GPU); NCCL all-reduce of actor+value grads"
+                   "parallelism": f"dp{world} over start states ({N} per GPU); "
+                                  + ("one-shot all-reduce of the actor+value gradient bucket over NVLink peer memory (drm_allreduce)"
+                                     if (run.graph is not None and getattr(run.graph, "allreduce_kind", None) == "peer_oneshot")
+                                     else "NCCL all-reduce of actor+value grads")
                                   + (" inside the step's CUDA graph" if (run.graph is not None and run.graph.allreduce_in_graph) else ""),
                    "l2": "512 MiB buffer written between timed steps (L2 flush); per-step CUDA events",
                    "launch": "eager" if run.graph is None else "one CUDA graph replay per step (ImaginationGraph)",

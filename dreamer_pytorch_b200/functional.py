@@ -42,11 +42,32 @@ def _f32c(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
     return t.contiguous()
 
 
+_bucket_provider = None  # callable(tensors) -> flat fp32 buffer of sum(rup4(numel)) floats, or None
+
+
+class bucket_provider:
+    """Context manager: gradient buckets handed out by flat_like come from `fn` (parallel.PeerBucket.provide) instead of
+    torch.empty -- the backward kernels then write weight gradients straight into peer-mapped memory."""
+
+    def __init__(self, fn):
+        self.fn = fn
+
+    def __enter__(self):
+        global _bucket_provider
+        self.old, _bucket_provider = _bucket_provider, self.fn
+
+    def __exit__(self, *exc):
+        global _bucket_provider
+        _bucket_provider = self.old
+
+
 def flat_like(tensors: Sequence[torch.Tensor]) -> List[torch.Tensor]:
     """Fresh fp32 tensors shaped like `tensors`, carved as 16-byte aligned views out of ONE flat buffer (``out[0]._base``):
     the gradient bucket of an optimizer group.  The <= 3 padding floats between pieces are never read."""
     sizes = [(w.numel() + 3) // 4 * 4 for w in tensors]
-    flat = torch.empty(sum(sizes), dtype=torch.float32, device=tensors[0].device)
+    flat = _bucket_provider(tensors) if _bucket_provider is not None else None  # e.g. a slice of peer-mapped memory
+    if flat is None:
+        flat = torch.empty(sum(sizes), dtype=torch.float32, device=tensors[0].device)
     out, o = [], 0
     for w, n in zip(tensors, sizes):
         out.append(flat[o:o + w.numel()].view(w.shape))

@@ -19,12 +19,14 @@ import torch
 
 from . import _lib
 from .algo import imagination_losses
+from .dropin.dense import mlp_weights
 from .dropin.rnns import RSSMState
 
 
 class ImaginationGraph:
     def __init__(self, model, n_states: int, horizon: int, discount: float = 0.99, discount_lambda: float = 0.95,
-                 use_pcont: bool = False, warmup: int = 3, actor_opt=None, value_opt=None, allreduce: bool = False):
+                 use_pcont: bool = False, warmup: int = 3, actor_opt=None, value_opt=None, allreduce: bool = False,
+                 peer_allreduce: bool = True):
         """actor_opt / value_opt: optional ``optim.ClipAdam(..., capturable=True)`` over the action decoder's / the value
         model's parameters.  Their step() (clip_grad_norm_ + Adam, dreamer_algo.py:182-194) is then recorded behind the
         backward pass, so that one replay is one whole actor + value update.  Parameters and optimizer state are restored
@@ -50,6 +52,12 @@ class ImaginationGraph:
 
         self._dist = dist if (allreduce and dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1) else None
         self.allreduce_in_graph = self._dist is not None
+        self._coalesce = True
+        self._peer, self.allreduce_kind = None, None
+        if self._dist is not None and peer_allreduce:
+            from .parallel import PeerBucket
+
+            self._peer = PeerBucket.create([list(model.action_decoder.weights()), list(mlp_weights(model.value_model.model))])
         self.opts = [(o, ps) for o, ps in ((actor_opt, self.actor_params), (value_opt, self.value_params)) if o is not None]
         for o, ps in self.opts:
             if getattr(o, "step_dev", None) is None:
@@ -94,22 +102,43 @@ class ImaginationGraph:
 
     def _eager(self):
         start = RSSMState(self.stoch, self.stoch, self.stoch, self.deter)  # mean / std of a start state are never read
-        actor_loss, value_loss, _ = imagination_losses(self.model, start, self.horizon, **self._kw)
-        # autograd.grad rather than .backward(): no AccumulateGrad nodes (they remember the stream they were created
-        # on, which breaks capture when the model has been used on the default stream before)
-        ga = torch.autograd.grad(actor_loss, self.actor_params)
-        gv = torch.autograd.grad(value_loss, self.value_params)
+        from .functional import bucket_provider
+
+        # with a peer bucket, the backward kernels write both groups' weight gradients straight into peer-mapped memory
+        # (the sinks are allocated as early as the forward pass: the PREPARE half of the backward runs beside it)
+        with bucket_provider(self._peer.provide if self._peer is not None else None):
+            actor_loss, value_loss, _ = imagination_losses(self.model, start, self.horizon, **self._kw)
+            # autograd.grad rather than .backward(): no AccumulateGrad nodes (they remember the stream they were created
+            # on, which breaks capture when the model has been used on the default stream before)
+            ga = torch.autograd.grad(actor_loss, self.actor_params)
+            gv = torch.autograd.grad(value_loss, self.value_params)
         grads = list(ga) + list(gv)
-        if self._dist is not None:
+        if self._peer is not None and self._peer.owns(ga) and self._peer.owns(gv):
+            # ... and one launch of this library's one-shot kernel averages it over NVLink (parallel.PeerBucket)
+            self._peer.allreduce()
+            self.allreduce_kind = "peer_oneshot"
+        elif self._dist is not None:
+            self.allreduce_kind = "nccl"
             # equal shards: the mean of the shard means is the global mean.  Each group's gradients are
             # views of one flat bucket written by the backward kernels themselves (functional.flat_like).
+            # Both buckets go out as ONE grouped NCCL launch (ncclGroupStart / End through torch's coalescing manager):
+            # at ~0.5 MB each the cost is launch + handshake latency, not bandwidth.
+            bufs = []
             for group in (ga, gv):
                 base = group[0]._base
-                if base is not None and all(g._base is base for g in group):
-                    self._dist.all_reduce(base, op=self._dist.ReduceOp.AVG)
-                else:
-                    for g in group:
-                        self._dist.all_reduce(g, op=self._dist.ReduceOp.AVG)
+                bufs += [base] if base is not None and all(g._base is base for g in group) else list(group)
+            try:
+                if self._coalesce:
+                    with self._dist._coalescing_manager(device=bufs[0].device):
+                        for b in bufs:
+                            self._dist.all_reduce(b, op=self._dist.ReduceOp.AVG)
+            except Exception:  # pragma: no cover  (a backend without the grouped fast path)
+                if torch.cuda.is_current_stream_capturing():
+                    raise
+                self._coalesce = False
+            if not self._coalesce:
+                for b in bufs:
+                    self._dist.all_reduce(b, op=self._dist.ReduceOp.AVG)
         if self.opts:
             for p, g in zip(self.params, grads):
                 p.grad = g

@@ -326,6 +326,29 @@ int drm_noise_fill(const drm_noise_fill_call* c, void* stream);
 int drm_noise_words(const unsigned long long* pair, int stream_id, unsigned long long group0, int n_groups,
                     unsigned int* out, void* stream);
 
+/* ---- multi-GPU: one-shot all-reduce (mean) of the flat gradient bucket over NVLink peer memory ------------
+ * The reference is single-GPU; a data-parallel run of it would average the gradients of dreamer_algo.py:174-180 with
+ * torch's NCCL all-reduce.  Here the backward kernels write the actor / value weight gradients straight into one flat
+ * fp32 bucket in symmetric (peer-mapped) memory and ONE kernel averages it in place with P2P loads: two flag
+ * hand-shakes + one pass of 16-byte loads, recordable into the step's CUDA graph.  All ranks call it with the same
+ * numel / ctas, in the same order, each on its own device.  Results are bit-identical on every rank (rank-order sums).
+ *   buf[r]      rank r's bucket as mapped into THIS process (buf[rank] = the local one), 16-byte aligned
+ *   signal[r]   rank r's signal pad (uint32 [2][ctas][DRM_MAX_RANKS], zero-filled once before the first call)
+ *   staging     local scratch of numel floats;  epoch: local uint64[2] = {0, 0} before the first call */
+#define DRM_MAX_RANKS 8
+#define DRM_AR_MAX_CTAS 64
+typedef struct drm_allreduce_call {
+    int32_t world, rank;
+    int32_t ctas;      /* CTAs per rank (same on every rank) */
+    float scale;       /* 1 / world for the mean */
+    int64_t numel;     /* floats, multiple of 4 */
+    void* buf[DRM_MAX_RANKS];
+    void* signal[DRM_MAX_RANKS];
+    float* staging;
+    unsigned long long* epoch;
+} drm_allreduce_call;
+int drm_allreduce(const drm_allreduce_call* c, void* stream);
+
 int drm_version(void);
 /* Once per device, before the first compute call (the ctypes binding does it at load time): checks the architecture and
  * loads every kernel of the library (CUDA would otherwise load a kernel lazily at its first launch, and that load may
