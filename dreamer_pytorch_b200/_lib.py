@@ -134,6 +134,11 @@ class drm_noise_fill_call(C.Structure):
                 ("stream_id", C.c_int32 * MAX_NOISE_BLOCKS), ("kind", C.c_int32 * MAX_NOISE_BLOCKS)]
 
 
+class drm_bias_act_call(C.Structure):
+    _fields_ = [("rows", C.c_int64), ("C", C.c_int32), ("relu", C.c_int32), ("x", P), ("bias", P), ("g", P), ("y", P),
+                ("g_pre", P), ("dbias", P)]
+
+
 MAX_RANKS, AR_MAX_CTAS = 8, 64
 
 
@@ -142,7 +147,7 @@ class drm_allreduce_call(C.Structure):
                 ("buf", P * MAX_RANKS), ("signal", P * MAX_RANKS), ("staging", P), ("epoch", P)]
 
 
-STRUCTS = {s.__name__: s for s in (drm_allreduce_call, drm_noise_fill_call, drm_replay_gather_call, drm_policy_mode_call, drm_image_logprob_call, drm_clip_adam_call, drm_mlp, drm_mlp_grad, drm_rssm, drm_rssm_grad, drm_rollout, drm_rollout_grad,
+STRUCTS = {s.__name__: s for s in (drm_bias_act_call, drm_allreduce_call, drm_noise_fill_call, drm_replay_gather_call, drm_policy_mode_call, drm_image_logprob_call, drm_clip_adam_call, drm_mlp, drm_mlp_grad, drm_rssm, drm_rssm_grad, drm_rollout, drm_rollout_grad,
                                    drm_mlp_call, drm_mlp_bwd_call, drm_returns_loss_call, drm_kl_call)}
 
 NOALLOC_SCRATCH_BYTES = 2 << 20  # DRM_NOALLOC_SCRATCH_BYTES
@@ -175,6 +180,8 @@ SYMBOLS = {
     "drm_policy_mode": (C.c_int, [C.POINTER(drm_policy_mode_call), P]),
     "drm_replay_gather": (C.c_int, [C.POINTER(drm_replay_gather_call), P]),
     "drm_allreduce": (C.c_int, [C.POINTER(drm_allreduce_call), P]),
+    "drm_bias_act_fwd": (C.c_int, [C.POINTER(drm_bias_act_call), P]),
+    "drm_bias_act_bwd": (C.c_int, [C.POINTER(drm_bias_act_call), P]),
     "drm_noise_next": (C.c_int, [P, P, P]),
     "drm_noise_fill": (C.c_int, [C.POINTER(drm_noise_fill_call), P]),
     "drm_noise_words": (C.c_int, [P, C.c_int, C.c_ulonglong, C.c_int, P, P]),

@@ -27,7 +27,7 @@ inline void warm_kernel(K kernel) {
 }
 // per translation unit: load every kernel it defines (drm_init)
 void warm_util(); void warm_mlp(); void warm_mlp_tc(); void warm_wgrad_tc(); void warm_rollout_fwd(); void warm_rollout_bwd();
-void warm_rollout_tc(); void warm_loss(); void warm_optim(); void warm_policy(); void warm_replay(); void warm_noise(); void warm_allreduce();
+void warm_rollout_tc(); void warm_loss(); void warm_optim(); void warm_policy(); void warm_replay(); void warm_noise(); void warm_allreduce(); void warm_conv_glue();
 
 // Diagnostics (drm_launch_count / drm_prof_*): every kernel launch site bumps the counter and,
 // when profiling is on, is bracketed by a cudaEvent pair on the launching stream.

@@ -110,7 +110,7 @@ int drm_init(void) {
     DRM_CUDA_OK(cudaGetDevice(&dev));
     if (dev == done_dev) return DRM_OK;
     drm::warm_util(); drm::warm_mlp(); drm::warm_mlp_tc(); drm::warm_wgrad_tc(); drm::warm_rollout_fwd();
-    drm::warm_rollout_bwd(); drm::warm_rollout_tc(); drm::warm_loss(); drm::warm_optim(); drm::warm_policy(); drm::warm_replay(); drm::warm_noise(); drm::warm_allreduce();
+    drm::warm_rollout_bwd(); drm::warm_rollout_tc(); drm::warm_loss(); drm::warm_optim(); drm::warm_policy(); drm::warm_replay(); drm::warm_noise(); drm::warm_allreduce(); drm::warm_conv_glue();
     DRM_CUDA_OK(cudaGetLastError());
     done_dev = dev;
     return DRM_OK;
@@ -161,6 +161,7 @@ size_t drm_sizeof(const char* name) {
     DRM_SZ(drm_replay_gather_call)
     DRM_SZ(drm_noise_fill_call)
     DRM_SZ(drm_allreduce_call)
+    DRM_SZ(drm_bias_act_call)
 #undef DRM_SZ
     return 0;
 }

@@ -49,6 +49,38 @@ class ImageNormal(td.Independent):
         return super().log_prob(value)
 
 
+def _run_conv_stack(mods, x):
+    """A Sequential of Conv2d / ConvTranspose2d (+ ReLU) on a channels-last fp32 tensor: the convolution is called without
+    bias and bias + ReLU run as ONE in-place pass of this library (functional.BiasActFn), where the layer qualifies
+    (fp32, channels a multiple of 4: every layer but the decoder's 3-channel output); anything else runs as the module."""
+    import torch.nn.functional as F
+
+    from ..functional import BiasActFn
+
+    mods = list(mods)
+    i = 0
+    while i < len(mods):
+        m = mods[i]
+        relu = i + 1 < len(mods) and type(mods[i + 1]) is nn.ReLU
+        y = None
+        bias = getattr(m, "bias", None)
+        if bias is not None and bias.shape[0] % 4 == 0 and x.dtype == torch.float32 and not torch.is_autocast_enabled():
+            if type(m) is nn.Conv2d and m.padding_mode == "zeros":
+                y = F.conv2d(x, m.weight, None, m.stride, m.padding, m.dilation, m.groups)
+            elif type(m) is nn.ConvTranspose2d:
+                y = F.conv_transpose2d(x, m.weight, None, m.stride, m.padding, m.output_padding, m.groups, m.dilation)
+        if y is not None and BiasActFn.eligible(y, m.bias):
+            x = BiasActFn.apply(y, m.bias, relu)
+            i += 2 if relu else 1
+        elif y is not None:
+            x = y + m.bias.view(1, -1, 1, 1)
+            i += 1
+        else:
+            x = m(x)
+            i += 1
+    return x
+
+
 def conv_out(h_in, padding, kernel_size, stride):
     return int((h_in + 2.0 * padding - (kernel_size - 1.0) - 1.0) / stride + 1.0)
 
@@ -84,7 +116,7 @@ class ObservationEncoder(nn.Module):
                 self.convolutions.to(memory_format=torch.channels_last)  # in place: same Parameter objects
                 self._cl = True
             with _cast(mode):
-                x = self.convolutions(x.contiguous(memory_format=torch.channels_last))
+                x = _run_conv_stack(self.convolutions, x.contiguous(memory_format=torch.channels_last))
             return x.float().reshape(*lead, -1)  # logical NCHW order, like the reference's flatten
         x = self.convolutions(x)
         return x.reshape(*lead, -1)
@@ -129,7 +161,7 @@ class ObservationDecoder(nn.Module):
                 self._cl = True
             with _cast(mode):
                 y = self.linear(flat).reshape(flat.shape[0], *self.conv_shape)
-                mean = self.decoder(y.contiguous(memory_format=torch.channels_last))
+                mean = _run_conv_stack(self.decoder, y.contiguous(memory_format=torch.channels_last))
             mean = mean.contiguous().reshape(*lead, *self.shape)  # NCHW order (bf16 or fp32): what the log-prob kernel reads
         else:
             y = self.linear(flat).reshape(flat.shape[0], *self.conv_shape)

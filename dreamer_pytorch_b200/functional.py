@@ -586,6 +586,56 @@ class ImageLogProbFn(torch.autograd.Function):
 # ------------------------------------------------------------------------------------------------
 # environment-time policy head
 # ------------------------------------------------------------------------------------------------
+class BiasActFn(torch.autograd.Function):
+    """``act(x + bias[c])`` IN PLACE on a channels-last fp32 conv output ``x`` [N,C,H,W] that was computed without bias
+    (observation.py:18-25,83-93).  One pass instead of torch's broadcast add + ReLU; the backward is one
+    pass too: ``g * (y > 0)`` with the bias gradient reduced on the way (drm_bias_act_fwd / _bwd)."""
+
+    @staticmethod
+    def eligible(x: torch.Tensor, bias) -> bool:
+        if bias is None or not x.is_cuda or x.dtype != torch.float32 or x.dim() != 4 or bias.dtype != torch.float32:
+            return False
+        C = x.shape[1]
+        return (C % 4 == 0 and C <= 1024 and 256 % (C // 4) == 0 and x.numel() > 0
+                and x.is_contiguous(memory_format=torch.channels_last))
+
+    @staticmethod
+    def forward(ctx, x, bias, relu: bool):
+        lib = _lib.load()
+        c = _lib.drm_bias_act_call()
+        c.rows, c.C, c.relu = x.numel() // x.shape[1], x.shape[1], 1 if relu else 0
+        c.x, c.bias = x.data_ptr(), _f32c(bias).data_ptr()
+        _lib.check(lib.drm_bias_act_fwd(C.byref(c), _stream()), "drm_bias_act_fwd")
+        _count()
+        ctx.mark_dirty(x)
+        ctx.relu = bool(relu)
+        if relu:
+            ctx.save_for_backward(x)
+        return x
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g):
+        lib = _lib.load()
+        g = g.contiguous(memory_format=torch.channels_last)
+        c = _lib.drm_bias_act_call()
+        c.rows, c.C, c.relu = g.numel() // g.shape[1], g.shape[1], 1 if ctx.relu else 0
+        c.g = g.data_ptr()
+        out = g
+        if ctx.relu:
+            (y,) = ctx.saved_tensors
+            out = torch.empty_like(g, memory_format=torch.channels_last)
+            c.y, c.g_pre = y.data_ptr(), out.data_ptr()
+        db = None
+        if ctx.needs_input_grad[1]:
+            db = torch.empty(g.shape[1], dtype=torch.float32, device=g.device)
+            c.dbias = db.data_ptr()
+        if ctx.relu or db is not None:
+            _lib.check(lib.drm_bias_act_bwd(C.byref(c), _stream()), "drm_bias_act_bwd")
+            _count()
+        return (out if ctx.needs_input_grad[0] else None), db, None
+
+
 def policy_mode(raw: torch.Tensor, samples: int, mean_scale: float, raw_init_std: float, min_std: float,
                 return_logp: bool = False):
     """SampleDist.mode() of the tanh-Normal action distribution (distribution.py:24-35) from the actor MLP's output

@@ -265,6 +265,24 @@ typedef struct drm_image_logprob_call {
     const float* g;        /* [rows]   upstream gradient of logp (bwd) */
     void* dmean;           /* [rows, D] same dtype as mean (bwd) */
 } drm_image_logprob_call;
+/* Pointwise glue of the conv stack (dreamer/models/observation.py:18-25,83-93: Conv2d / ConvTranspose2d + ReLU) on
+ * channels-last fp32 activations viewed as [rows = N*H*W, C]; the convolution itself is called without bias (cuDNN).
+ *   fwd: x = act(x + bias[c]) in place                     (replaces torch's broadcast add + ReLU: two passes -> one)
+ *   bwd: g_pre = g * (y > 0),  dbias[c] = sum_rows g_pre    (replaces threshold_backward + the bias-gradient reduction)
+ * C must be a multiple of 4 whose quarter divides 256 (the reference's 32 / 64 / 128 / 256 channels). */
+typedef struct drm_bias_act_call {
+    int64_t rows;
+    int32_t C;
+    int32_t relu;       /* 1: ReLU, 0: bias only (then bwd writes no g_pre, only dbias) */
+    float* x;           /* fwd: [rows, C] in place */
+    const float* bias;  /* fwd: [C] */
+    const float* g;     /* bwd: upstream gradient [rows, C] */
+    const float* y;     /* bwd: forward output [rows, C] (relu = 1) */
+    float* g_pre;       /* bwd: out [rows, C] (relu = 1) */
+    float* dbias;       /* bwd: out [C] or NULL; zero-filled by the call */
+} drm_bias_act_call;
+int drm_bias_act_fwd(const drm_bias_act_call* c, void* stream);
+int drm_bias_act_bwd(const drm_bias_act_call* c, void* stream);
 int drm_image_logprob_fwd(const drm_image_logprob_call* c, void* stream);
 int drm_image_logprob_bwd(const drm_image_logprob_call* c, void* stream);
 

@@ -65,3 +65,35 @@ def test_bf16_channels_last_conv_stack_tracks_fp32(cuda):
     for p in list(enc.parameters()) + list(dec.parameters()):
         assert p.grad is not None and p.grad.dtype == torch.float32 and torch.isfinite(p.grad).all()
         assert p.shape == p.grad.shape
+
+
+def test_fused_bias_relu_conv_stack_matches_torch_modules(cuda):
+    """conv_mode("channels_last"): convolutions without bias + this library's in-place bias/ReLU pass (forward) and
+    ReLU-mask + bias-gradient pass (backward) against the plain torch modules on the same parameters (fp32 NCHW)."""
+    from dreamer_pytorch_b200 import _lib
+    from dreamer_pytorch_b200.dropin.observation import ObservationDecoder, ObservationEncoder
+    from dreamer_pytorch_b200.precision import conv_mode, precision
+
+    torch.manual_seed(1)
+    enc, dec = ObservationEncoder().to(cuda), ObservationDecoder(embed_size=230).to(cuda)
+    params = list(enc.parameters()) + list(dec.parameters())
+    obs = torch.rand(3, 7, 3, 64, 64, device=cuda) - 0.5
+    feat = torch.randn(3, 7, 230, device=cuda)
+
+    def run():
+        e = enc(obs)
+        lp = dec(feat).log_prob(obs)
+        loss = -lp.mean() + e.square().mean()
+        return e.detach(), lp.detach(), torch.autograd.grad(loss, params)
+
+    with precision("fp32"), conv_mode("nchw"):
+        e0, lp0, g0 = run()
+    n0 = _lib.load().drm_launch_count()
+    with precision("fp32"), conv_mode("channels_last"):
+        e1, lp1, g1 = run()
+    assert _lib.load().drm_launch_count() - n0 >= 2 * 7 + 2  # 7 fused layers fwd + bwd, image log-prob fwd + bwd
+    assert rel_err(e1, e0) < 1e-4 and rel_err(lp1, lp0) < 1e-4
+    for p, a, b in zip(params, g1, g0):
+        assert a.shape == p.shape and rel_err(a, b) < 2e-3, tuple(p.shape)  # cuDNN picks other algorithms per layout
+    with torch.no_grad(), precision("fp32"), conv_mode("channels_last"):
+        assert rel_err(enc(obs), e0) < 1e-4  # inference path (no autograd graph): same kernels
