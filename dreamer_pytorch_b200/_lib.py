@@ -144,7 +144,7 @@ MAX_RANKS, AR_MAX_CTAS = 8, 64
 
 class drm_allreduce_call(C.Structure):
     _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("ctas", C.c_int32), ("scale", C.c_float), ("numel", C.c_int64),
-                ("buf", P * MAX_RANKS), ("signal", P * MAX_RANKS), ("staging", P), ("epoch", P)]
+                ("algo", C.c_int32), ("pad_", C.c_int32), ("buf", P * MAX_RANKS), ("signal", P * MAX_RANKS), ("staging", P), ("epoch", P)]
 
 
 STRUCTS = {s.__name__: s for s in (drm_bias_act_call, drm_allreduce_call, drm_noise_fill_call, drm_replay_gather_call, drm_policy_mode_call, drm_image_logprob_call, drm_clip_adam_call, drm_mlp, drm_mlp_grad, drm_rssm, drm_rssm_grad, drm_rollout, drm_rollout_grad,

@@ -12,6 +12,7 @@
 //   reduce      slice of this CTA from all peers -> local staging buffer (scaled by 1 / world)
 //   barrier B   "I have finished reading your bucket" -> every peer; wait (only then may a bucket be overwritten)
 //   copy        staging -> local bucket
+// (2 or 3 ranks; from 4 ranks on the two-shot form below moves less data.)
 //
 // Flags are epoch numbers (monotonic, never reset): slot [phase][cta][source rank] of the destination rank's signal pad.
 // The epoch lives on the device and is advanced by the last CTA to finish, so the call can be recorded into a CUDA graph.
@@ -92,7 +93,58 @@ __global__ void __launch_bounds__(kArThreads) allreduce_oneshot_kernel(const drm
     }
 }
 
-void warm_allreduce() { warm_kernel(allreduce_oneshot_kernel); }
+// Two-shot form for world >= 4 (one-shot makes every GPU read world x the bucket: 8 MB per rank at 8 GPUs, ~27 us of
+// NVLink time for a 1 MB bucket; here a rank reads 2 x (world - 1) / world of it):
+//   barrier A;  rank r reduces slice r of every peer's bucket into slice r of its OWN bucket (rank order, scaled);
+//   barrier B;  rank r copies slice s of rank s's bucket (the reduced one) into its own slice s, for every s != r;
+//   barrier C   (nobody overwrites a reduced slice -- the next step's gradients -- while a peer still reads it).
+// Slice r of rank p's bucket is read only by rank r in the first phase and written only by rank p in the second, after
+// barrier B, so no staging buffer is needed.  Every slice is reduced exactly once: results are bit-identical everywhere.
+__global__ void __launch_bounds__(kArThreads) allreduce_twoshot_kernel(const drm_allreduce_call c) {
+    const unsigned int epoch = (unsigned int)(c.epoch[0] + 1ull);
+    peer_barrier(c, 0, epoch);
+    const long long n4 = c.numel >> 2;
+    const long long per = (n4 + c.world - 1) / c.world;
+    const float* src[DRM_MAX_RANKS];
+#pragma unroll
+    for (int r = 0; r < DRM_MAX_RANKS; ++r) src[r] = reinterpret_cast<const float*>(c.buf[r < c.world ? r : 0]);
+    float4* mine = reinterpret_cast<float4*>(c.buf[c.rank]);
+    {
+        const long long lo = per * c.rank, hi = lo + per < n4 ? lo + per : n4;
+        for (long long i = lo + (long long)blockIdx.x * kArThreads + threadIdx.x; i < hi; i += (long long)gridDim.x * kArThreads) {
+            float4 v[DRM_MAX_RANKS];
+#pragma unroll
+            for (int r = 0; r < DRM_MAX_RANKS; ++r)
+                if (r < c.world) v[r] = ld_peer4(src[r] + 4 * i);
+            float4 a = v[0];
+#pragma unroll
+            for (int r = 1; r < DRM_MAX_RANKS; ++r)
+                if (r < c.world) { a.x += v[r].x; a.y += v[r].y; a.z += v[r].z; a.w += v[r].w; }
+            a.x *= c.scale; a.y *= c.scale; a.z *= c.scale; a.w *= c.scale;
+            mine[i] = a;
+        }
+    }
+    __threadfence_system();
+    peer_barrier(c, 1, epoch);
+    for (int k = 1; k < c.world; ++k) {
+        const int s = (c.rank + k) % c.world;  // staggered: the ranks do not all pull from the same peer at once
+        const long long lo = per * s, hi = lo + per < n4 ? lo + per : n4;
+        for (long long i = lo + (long long)blockIdx.x * kArThreads + threadIdx.x; i < hi; i += (long long)gridDim.x * kArThreads)
+            mine[i] = ld_peer4(src[s] + 4 * i);
+    }
+    peer_barrier(c, 2, epoch);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const unsigned long long t = atomicAdd(c.epoch + 1, 1ull);
+        if (t == (unsigned long long)gridDim.x - 1ull) {
+            c.epoch[1] = 0ull;
+            c.epoch[0] = c.epoch[0] + 1ull;
+        }
+    }
+}
+
+void warm_allreduce() { warm_kernel(allreduce_oneshot_kernel); warm_kernel(allreduce_twoshot_kernel); }
 
 }  // namespace drm
 
@@ -112,7 +164,10 @@ extern "C" int drm_allreduce(const drm_allreduce_call* c, void* stream_) {
     }
     int rc = check_device(); if (rc) return rc;
     ProfScope prof(PROF_LOSS, stream);
-    allreduce_oneshot_kernel<<<c->ctas, kArThreads, 0, stream>>>(*c);
+    DRM_REQUIRE(c->algo >= 0 && c->algo <= 2 && (c->algo != 2 || c->world >= 3), DRM_E_ARG, "bad algo");
+    const bool two_shot = c->algo == 2 || (c->algo == 0 && c->world >= 4 && c->numel >= (1 << 20));
+    if (two_shot) allreduce_twoshot_kernel<<<c->ctas, kArThreads, 0, stream>>>(*c);
+    else allreduce_oneshot_kernel<<<c->ctas, kArThreads, 0, stream>>>(*c);
     DRM_CUDA_OK(cudaGetLastError());
     return DRM_OK;
 }

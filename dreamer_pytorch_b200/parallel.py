@@ -119,7 +119,7 @@ def finish_allreduce(pending) -> None:
 # ------------------------------------------------------------------------------------------------------------------
 # One-shot all-reduce over NVLink peer memory (csrc/drm_allreduce.cu)
 # ------------------------------------------------------------------------------------------------------------------
-_PAD_WORDS = 2 * 64 * 8  # signal pad in front of the bucket: uint32 [2 phases][<= 64 CTAs][8 ranks]
+_PAD_WORDS = 4 * 64 * 8  # signal pad in front of the bucket: uint32 [<= 3 phases][<= 64 CTAs][8 ranks] (+ spare)
 
 
 def _agree(ok: bool, device) -> bool:
@@ -150,7 +150,8 @@ class PeerBucket:
         return tuple(tuple(t.shape) for t in tensors)
 
     @classmethod
-    def create(cls, groups: Sequence[Sequence[torch.Tensor]], ctas: int = 16) -> Optional["PeerBucket"]:
+    def create(cls, groups: Sequence[Sequence[torch.Tensor]], ctas: int = 16, algo: int = 0) -> Optional["PeerBucket"]:
+        """algo: 0 auto, 1 one-shot, 2 two-shot (drm_allreduce_call.algo)."""
         from . import _lib
 
         if not (dist.is_available() and dist.is_initialized()) or dist.get_backend() != "nccl":
@@ -204,6 +205,7 @@ class PeerBucket:
         self.epoch = torch.zeros(2, dtype=torch.int64, device=dev)
         c = _lib.drm_allreduce_call()
         c.world, c.rank, c.ctas, c.scale, c.numel = world, rank, int(ctas), 1.0 / world, self.flat.numel()
+        c.algo = int(algo)
         for r in range(world):
             c.signal[r] = ptrs[r]
             c.buf[r] = ptrs[r] + 4 * _PAD_WORDS

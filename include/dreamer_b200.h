@@ -348,10 +348,11 @@ int drm_noise_words(const unsigned long long* pair, int stream_id, unsigned long
  * The reference is single-GPU; a data-parallel run of it would average the gradients of dreamer_algo.py:174-180 with
  * torch's NCCL all-reduce.  Here the backward kernels write the actor / value weight gradients straight into one flat
  * fp32 bucket in symmetric (peer-mapped) memory and ONE kernel averages it in place with P2P loads: two flag
- * hand-shakes + one pass of 16-byte loads, recordable into the step's CUDA graph.  All ranks call it with the same
+ * hand-shakes + one pass of 16-byte loads (one-shot; from 4 ranks on reduce-scatter + all-gather over the same
+ * loads, three hand-shakes), recordable into the step's CUDA graph.  All ranks call it with the same
  * numel / ctas, in the same order, each on its own device.  Results are bit-identical on every rank (rank-order sums).
  *   buf[r]      rank r's bucket as mapped into THIS process (buf[rank] = the local one), 16-byte aligned
- *   signal[r]   rank r's signal pad (uint32 [2][ctas][DRM_MAX_RANKS], zero-filled once before the first call)
+ *   signal[r]   rank r's signal pad (uint32 [3][ctas][DRM_MAX_RANKS], zero-filled once before the first call)
  *   staging     local scratch of numel floats;  epoch: local uint64[2] = {0, 0} before the first call */
 #define DRM_MAX_RANKS 8
 #define DRM_AR_MAX_CTAS 64
@@ -360,6 +361,10 @@ typedef struct drm_allreduce_call {
     int32_t ctas;      /* CTAs per rank (same on every rank) */
     float scale;       /* 1 / world for the mean */
     int64_t numel;     /* floats, multiple of 4 */
+    int32_t algo;      /* 0 auto, 1 one-shot, 2 two-shot (reduce-scatter + all-gather; needs world >= 3).  Auto picks two-shot
+                          for world >= 4 and buckets >= 4 MB: measured at 8 GPUs on the 1 MB actor+value bucket, the
+                          third hand-shake costs more than the 7 MB of peer reads it saves (1.153 vs 1.140 ms per step) */
+    int32_t pad_;
     void* buf[DRM_MAX_RANKS];
     void* signal[DRM_MAX_RANKS];
     float* staging;

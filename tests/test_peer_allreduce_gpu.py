@@ -1,4 +1,4 @@
-"""drm_allreduce (one-shot mean over NVLink peer memory) against NCCL, 2 ranks on one box.  Needs two GPUs:
+"""drm_allreduce (mean over NVLink peer memory) against NCCL, 2 and 4 ranks on one box.  Needs that many GPUs:
 skipped on the single-GPU test box (bench.py --gpus N exercises it at N = 2 .. 8; PeerBucket.create runs the same
 comparison as a self-test on every start-up and falls back to NCCL on all ranks if it fails)."""
 import os
@@ -19,7 +19,7 @@ from dreamer_pytorch_b200.parallel import PeerBucket
 dev = torch.device("cuda", rank)
 groups = [[torch.empty(200, 230, device=dev), torch.empty(200, device=dev), torch.empty(12, 200, device=dev), torch.empty(12, device=dev)],
           [torch.empty(200, 230, device=dev), torch.empty(200, device=dev), torch.empty(1, 200, device=dev), torch.empty(1, device=dev)]]
-b = PeerBucket.create(groups)
+b = PeerBucket.create(groups, algo=2 if dist.get_world_size() >= 4 else 1)  # 4 ranks: the two-shot kernel
 assert b is not None, "peer mapping unavailable"
 for it in range(5):
     g = torch.Generator(device=dev).manual_seed(it * 10 + rank)
@@ -45,12 +45,14 @@ dist.barrier(); os._exit(0)
 """
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
-def test_peer_allreduce_matches_nccl_two_ranks(tmp_path):
+@pytest.mark.parametrize("ranks", [2, 4])  # 2: one-shot kernel; 4: reduce-scatter + all-gather form
+def test_peer_allreduce_matches_nccl(tmp_path, ranks):
+    if torch.cuda.device_count() < ranks:
+        pytest.skip(f"needs {ranks} GPUs")
     script = tmp_path / "worker.py"
     script.write_text(_WORKER)
     env = dict(os.environ, REPO=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
-                          "--master-addr", "127.0.0.1", "--master-port", "29531", str(script)],
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={ranks}",
+                          "--master-addr", "127.0.0.1", "--master-port", str(29531 + ranks), str(script)],
                          env=env, capture_output=True, text=True, timeout=300)
-    assert out.returncode == 0 and out.stdout.count("PEER_OK") == 2, out.stdout[-2000:] + out.stderr[-3000:]
+    assert out.returncode == 0 and out.stdout.count("PEER_OK") == ranks, out.stdout[-2000:] + out.stderr[-3000:]
