@@ -162,7 +162,7 @@ def test_two_passes_on_two_streams_of_one_device():
     for i in range(2):
         al, vl, info = out[i]
         assert torch.equal(info.reward, alone[i][2])  # head outputs: bit-identical whatever the schedule
-        assert rel_err(al, alone[i][0]) < 1e-6 and rel_err(vl, alone[i][1]) < 1e-6
+        assert rel_err(al, alone[i][0]) < 1e-5 and rel_err(vl, alone[i][1]) < 1e-5  # one float atomic per CTA in the loss kernel
         for ga, gb in zip(grads[i], alone[i][3]):
             assert rel_err(ga, gb) < 1e-4  # fp32 atomics reorder between runs
 
@@ -249,4 +249,4 @@ def test_whole_update_graph_matches_eager_update(use_pcont):
         lr = 6e-4
         d = (pg.detach() - pe.detach()).abs()
         assert float(d.max()) <= 4.04 * lr, (k, float(d.max()))
-        assert float((d > 0.1 * lr).float().mean()) < 0.01, (k, float((d > 0.1 * lr).float().mean()))
+        assert int((d > 0.1 * lr).sum()) <= max(2, d.numel() // 100), (k, int((d > 0.1 * lr).sum()), d.numel())  # biases have 32 elements
