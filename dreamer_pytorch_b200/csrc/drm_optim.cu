@@ -73,11 +73,28 @@ __global__ void __launch_bounds__(kOptThreads) clip_adam_kernel(const drm_clip_a
     if (k > 1) {
         // parameter listed k times (see drm_clip_adam_call.mult): gradient scaled k times, k sequential Adam updates
         const double upd = (double)(c.step_dev ? *c.step_dev : c.update);
+        // the bias corrections of the k sub-steps depend on the step only: once per thread, not per element
+        constexpr int kMaxHoist = 4;
+        float ssr[kMaxHoist], b2r[kMaxHoist];
+#pragma unroll
+        for (int r = 1; r <= kMaxHoist; ++r) {
+            const double st = (upd - 1.0) * k + (r <= k ? r : k);
+            ssr[r - 1] = (float)((double)c.lr / (1.0 - pow(c.beta1_d, st)));
+            b2r[r - 1] = (float)sqrt(1.0 - pow(c.beta2_d, st));
+        }
         for (long long i = ch.lo + threadIdx.x; i < ch.hi; i += kOptThreads) {
             float gi = g[i];
             for (int r = 0; r < k; ++r) gi *= coef;
             float mi = m[i], vi = v[i], pi = p[i];
-            for (int r = 1; r <= k; ++r) {
+#pragma unroll
+            for (int r = 1; r <= kMaxHoist; ++r) {  // unrolled: ssr / b2r stay in registers
+                if (r <= k) {
+                    mi = mi + w1 * (gi - mi);
+                    vi = vi * c.beta2 + w2 * gi * gi;
+                    pi = pi - ssr[r - 1] * (mi / (sqrtf(vi) / b2r[r - 1] + c.eps));
+                }
+            }
+            for (int r = kMaxHoist + 1; r <= k; ++r) {  // a parameter listed more than four times: per element
                 const double st = (upd - 1.0) * k + r;
                 const float ss = (float)((double)c.lr / (1.0 - pow(c.beta1_d, st)));
                 const float b2 = (float)sqrt(1.0 - pow(c.beta2_d, st));
