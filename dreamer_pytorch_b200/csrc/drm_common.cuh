@@ -226,6 +226,36 @@ __device__ __forceinline__ void seg_accumulate4(float (&acc)[R][4], const Seg& s
     const float* __restrict__ wp = s.W + col;
     const float* __restrict__ xp = s.X;
     const int ldx = s.ldx;
+    if constexpr (R >= 12 && R <= 16) {  // (20 rows: the prefetch registers spill)
+        // Mid-height tiles run long K ranges per warp (a 600-wide layer leaves no room to split K): the weights of step
+        // k + 4 are requested before the FFMAs of step k, so one L2 round trip hides under 12-20 rows of math instead of
+        // preceding it.
+        if (s.K4 <= 0) return;
+        float4 w0 = __ldg(reinterpret_cast<const float4*>(wp + (size_t)0 * ldw));
+        float4 w1 = __ldg(reinterpret_cast<const float4*>(wp + (size_t)1 * ldw));
+        float4 w2 = __ldg(reinterpret_cast<const float4*>(wp + (size_t)2 * ldw));
+        float4 w3 = __ldg(reinterpret_cast<const float4*>(wp + (size_t)3 * ldw));
+#pragma unroll 1
+        for (int k = 0; k < s.K4; k += 4) {
+            float4 n0 = w0, n1 = w1, n2 = w2, n3 = w3;
+            if (k + 4 < s.K4) {
+                n0 = __ldg(reinterpret_cast<const float4*>(wp + (size_t)(k + 4) * ldw));
+                n1 = __ldg(reinterpret_cast<const float4*>(wp + (size_t)(k + 5) * ldw));
+                n2 = __ldg(reinterpret_cast<const float4*>(wp + (size_t)(k + 6) * ldw));
+                n3 = __ldg(reinterpret_cast<const float4*>(wp + (size_t)(k + 7) * ldw));
+            }
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const float4 x = *reinterpret_cast<const float4*>(xp + r * ldx + k);
+                acc[r][0] = fmaf(x.w, w3.x, fmaf(x.z, w2.x, fmaf(x.y, w1.x, fmaf(x.x, w0.x, acc[r][0]))));
+                acc[r][1] = fmaf(x.w, w3.y, fmaf(x.z, w2.y, fmaf(x.y, w1.y, fmaf(x.x, w0.y, acc[r][1]))));
+                acc[r][2] = fmaf(x.w, w3.z, fmaf(x.z, w2.z, fmaf(x.y, w1.z, fmaf(x.x, w0.z, acc[r][2]))));
+                acc[r][3] = fmaf(x.w, w3.w, fmaf(x.z, w2.w, fmaf(x.y, w1.w, fmaf(x.x, w0.w, acc[r][3]))));
+            }
+            w0 = n0; w1 = n1; w2 = n2; w3 = n3;
+        }
+        return;
+    }
 #pragma unroll(R <= 2 ? 3 : 1)
     for (int k = 0; k < s.K4; k += 4) {
         const float4 w0 = __ldg(reinterpret_cast<const float4*>(wp + (size_t)(k + 0) * ldw));
