@@ -121,3 +121,38 @@ def test_install_aliases_reference_paths():
         for k in [k for k in sys.modules if k == "dreamer" or k.startswith("dreamer.")]:
             del sys.modules[k]
         sys.modules.update(saved)
+
+
+def test_torch_ops_are_registered_without_a_gpu():
+    """torch.ops.dreamer_b200.* (SURVEY 8(b) torch op layer): registration and schemas need no device."""
+    import dreamer_pytorch_b200.ops as ops
+
+    assert set(ops.OP_NAMES) == {"transition_step", "transition_rollout", "representation_rollout", "policy_rollout", "mlp",
+                                 "kl_entropy", "heads_returns_loss", "image_logprob"}
+    schema = str(torch.ops.dreamer_b200.policy_rollout.default._schema)
+    assert "Tensor[] rssm" in schema and "str act_dist" in schema and schema.endswith("-> Tensor[]")
+    with pytest.raises(RuntimeError):  # CPU tensors: no fallback behind the ops either
+        torch.ops.dreamer_b200.mlp(torch.randn(2, 8), None, [torch.randn(1, 8), torch.randn(1)])
+
+
+def test_gradient_buckets_come_from_the_provider():
+    """functional.flat_like hands out views of ONE flat buffer per group; with a bucket provider (parallel.PeerBucket on a
+    multi-GPU box) the buffer is the provider's, e.g. peer-mapped memory."""
+    from dreamer_pytorch_b200 import functional as F
+
+    ws = [torch.zeros(5, 3), torch.zeros(5), torch.zeros(2, 5), torch.zeros(2)]
+    own = F.flat_like(ws)
+    assert all(g._base is own[0]._base for g in own) and [tuple(g.shape) for g in own] == [tuple(w.shape) for w in ws]
+    assert all(g.data_ptr() % 16 == 0 for g in own)  # 16-byte aligned pieces (vector reductions, one-shot all-reduce)
+    pool = torch.zeros(64)
+    seen = []
+
+    def provide(tensors):
+        seen.append([tuple(t.shape) for t in tensors])
+        return pool[:sum((t.numel() + 3) // 4 * 4 for t in tensors)]
+
+    with F.bucket_provider(provide):
+        got = F.flat_like(ws)
+    got[0].fill_(1.0)
+    assert float(pool[:15].sum()) == 15.0 and seen == [[(5, 3), (5,), (2, 5), (2,)]]
+    assert F.flat_like(ws)[0]._base is not pool  # the provider is gone with the context
