@@ -32,6 +32,10 @@ _SIDE = {}
 import os as _os
 
 _PIPELINE_HEADS = _PREPARE_BACKWARD = _PIPELINE_BACKWARD = _FOLLOW_WGRAD = True
+# SMs per head kernel below which the heads do NOT run beside the rollout (plain stream order instead).  With few SMs the
+# gated head kernels cannot keep up with the rollout and finish long after it: measured with 128-row tiles, ms per step
+# gated / plain at 34 SMs per head 2.35 / 2.48, at 26 SMs 3.48 / 2.67, at 18 SMs 5.43 / 2.91 (profiles/r2_experiments.md).
+_MIN_FREE = int(_os.environ.get("DRM_B200_MIN_FREE", "32"))
 
 
 def set_schedule(spec: str = "heads,prepare,backward") -> str:
@@ -155,7 +159,7 @@ class _ActorLossFn(torch.autograd.Function):
         # heads over all imagined states; hidden activations are kept: the actor path needs their
         # data-gradients, the value loss the value head's weight-gradients
         free = (_sm_count(x0.device) - tiles[0]) // len(heads) if tiles and tiles[0] > 0 else 0
-        if flags is not None and free >= 16:
+        if flags is not None and free >= _MIN_FREE:
             main = torch.cuda.current_stream()
             outs = []
             for i, (w, keep) in enumerate(heads):
@@ -237,7 +241,7 @@ class _ActorLossFn(torch.autograd.Function):
         # rollout kernel waits on (step_rows_done / g_wait_flags).  Grids are capped so that all of them are resident.
         free = (_sm_count(g_loss.device) - roll_tiles) // len(heads) if roll_tiles > 0 else 0
         g_wait = None
-        if prec == "bf16" and _PIPELINE_BACKWARD and free >= 16 and _overlap_ok(wkey) and _exclusive(g_loss.device):
+        if prec == "bf16" and _PIPELINE_BACKWARD and free >= _MIN_FREE and _overlap_ok(wkey) and _exclusive(g_loss.device):
             mlp_tiles = (H * N + 127) // 128
             cnt = torch.zeros(len(heads) * mlp_tiles + H, dtype=torch.int32, device=g_loss.device)
             steps_done = cnt[len(heads) * mlp_tiles:]

@@ -906,19 +906,18 @@ int rollout_tc_supported(const drm_rollout* r) {
 }
 
 // Rows per CTA.  64-row half tiles (see chain_mma) put more CTAs on the SMs than 128-row tiles while the batch is small.
-// One window goes back to 128 rows: when the 64-row tiles would fill the machine in a single wave they leave no SMs for
-// the head kernels that run BESIDE the rollout (algo.py), and half as many 128-row tiles plus overlapped heads win
-// (8 192 start states = one GPU's shard of BASELINE configs[3] at 8 GPUs: 1.89 -> 1.71 ms per step; 4 096: 64 rows stay
-// 1.11 vs 1.45; 12 288: 64 rows stay 3.15 vs 3.42 -- profiles/r2_experiments.md).
+// From the point where the 64-row tiles would (nearly) fill the machine in one wave, 128-row tiles win: they leave SMs
+// for the head kernels that run BESIDE the rollout (algo.py) and never need a second, partly filled wave.  Measured, ms
+// per step 64 / 128 rows (profiles/r2_experiments.md): 4 096 start states 1.11 / 1.45; 8 192 (one GPU's shard of BASELINE
+// configs[3] at 8 GPUs) 1.89 / 1.71; 10 240 3.01 / 2.35; 12 288 3.15 / 2.67; 14 336 3.37 / 2.91; 16 384 3.53 / 3.12;
+// around the switch: 5 000 1.28 / 1.47; 6 000 1.65 / 1.50; 7 000 1.77 / 1.57.
 static int tile_rows_for(int n) {
     static int forced = -1;  // developer / test override DRM_ROLLOUT_TR = 64 | 128, read once
     if (forced < 0) { const char* e = getenv("DRM_ROLLOUT_TR"); forced = e ? atoi(e) : 0; }
     if (forced == 64 || forced == 128) return forced;
     const int sms = num_sms();
-    const int t64 = (n + 63) / 64, t128 = (n + 127) / 128;
-    if (t128 >= sms) return 128;
-    if (t64 > sms - 32 && t64 <= sms) return 128;
-    return 64;
+    const int t64 = (n + 63) / 64;
+    return t64 > sms - 64 ? 128 : 64;  // 64-row tiles as long as they leave 2 x 32 SMs to the head kernels (algo._MIN_FREE)
 }
 static size_t tcm_bytes_r(int tr, size_t tiles, int chunks) { return tiles * (size_t)chunks * tr * 16; }
 
